@@ -1,0 +1,190 @@
+"""ctypes binding of libnerfacc_b200.so (the C ABI declared in include/nerfacc_b200.h).
+
+This module replaces the reference's lazy pybind shim (nerfacc/cuda/__init__.py:8-40 and
+nerfacc/cuda/_backend.py).  There is no CPU fallback and no other backend: if the shared
+library is missing or a tensor is not on a CUDA device, calls raise.
+
+PyTorch is used for plumbing only: it owns every buffer (caching allocator), provides the
+current stream, and its tensors' ``data_ptr()`` are what crosses the boundary.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _build
+
+_LIB: Optional[C.CDLL] = None
+_LOCK = threading.Lock()
+
+c_f32p = C.c_void_p
+c_i64 = C.c_int64
+c_int = C.c_int
+c_u32 = C.c_uint32
+c_f32 = C.c_float
+c_size = C.c_size_t
+c_ptr = C.c_void_p
+
+# name -> argtypes; every function returns int unless listed in _RESTYPES.
+_PROTOS = {
+    "nfb_version": [],
+    "nfb_compiled_arch": [],
+    "nfb_last_error": [],
+    "nfb_launch_count": [],
+    "nfb_workspace_bytes": [c_i64],
+    "nfb_scan_f32": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int, c_int, c_int, c_int,
+                     c_ptr, c_size, c_u32, c_ptr],
+    "nfb_prod_scan_bwd_f32": [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int,
+                              c_ptr, c_size, c_u32, c_ptr],
+    "nfb_render_weight_fwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64,
+                              c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_f32, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_render_weight_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                              c_i64, c_i64, c_i64, c_ptr, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_accumulate_fwd": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int,
+                           c_ptr, c_size, c_u32, c_ptr],
+    "nfb_accumulate_bwd": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
+    "nfb_pack_info": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_size, c_ptr],
+}
+_RESTYPES = {
+    "nfb_last_error": C.c_char_p,
+    "nfb_launch_count": C.c_longlong,
+    "nfb_workspace_bytes": C.c_size_t,
+}
+
+
+def declared_symbols():
+    return sorted(_PROTOS)
+
+
+def lib() -> C.CDLL:
+    """Load (building first if the sources changed and nvcc is present) the CUDA library."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    with _LOCK:
+        if _LIB is not None:
+            return _LIB
+        path = _build.LIB
+        if os.environ.get("NFB_NO_BUILD", "0") != "1":
+            try:
+                if not _build.up_to_date():
+                    _build.build()
+            except Exception as e:  # no nvcc / read-only tree: use what is there
+                if not os.path.exists(path):
+                    raise RuntimeError(
+                        "libnerfacc_b200.so is missing and could not be built "
+                        f"({e}); nerfacc_b200 has no CPU or PyTorch fallback."
+                    ) from e
+        if not os.path.exists(path):
+            raise RuntimeError(
+                f"{path} not found; run `python -m nerfacc_b200._build`. "
+                "nerfacc_b200 has no CPU or PyTorch fallback."
+            )
+        l = C.CDLL(path)
+        for name, argtypes in _PROTOS.items():
+            fn = getattr(l, name)
+            fn.argtypes = argtypes
+            fn.restype = _RESTYPES.get(name, C.c_int)
+        _LIB = l
+    return _LIB
+
+
+def last_error() -> str:
+    msg = lib().nfb_last_error()
+    return msg.decode() if msg else ""
+
+
+def launch_count() -> int:
+    return int(lib().nfb_launch_count())
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"nerfacc_b200.{what} failed (code {rc}): {last_error()}")
+
+
+def require_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError(
+                "nerfacc_b200 only runs on CUDA tensors (no CPU fallback by design); "
+                f"got a tensor on {t.device}"
+            )
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    assert dev is not None
+    return dev
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+# --------------------------------------------------------------------------- workspace
+class _Workspace:
+    """Persistent look-back scratch per (device, stream): zero-filled once, then reused with
+    a fresh epoch per launch so no memset is needed (see nfb_workspace_bytes)."""
+
+    __slots__ = ("buf", "epoch")
+
+    def __init__(self) -> None:
+        self.buf: Optional[torch.Tensor] = None
+        self.epoch = 0
+
+
+_WS: Dict[Tuple[int, int], _Workspace] = {}
+_EPOCH_MAX = (1 << 30) - 2
+
+
+def workspace(device: torch.device, n_elements: int) -> Tuple[torch.Tensor, int, int]:
+    """Returns (buffer, nbytes, epoch) for one flat-kernel launch on the current stream."""
+    need = int(lib().nfb_workspace_bytes(max(int(n_elements), 1)))
+    key = (device.index if device.index is not None else torch.cuda.current_device(),
+           torch.cuda.current_stream(device).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None:
+        ws = _WS[key] = _Workspace()
+    if torch.cuda.is_current_stream_capturing():
+        # graph replays would re-use a baked epoch: let the call clear the scratch itself
+        if ws.buf is None or ws.buf.numel() < need:
+            raise RuntimeError("nerfacc_b200: warm up once outside CUDA-graph capture first")
+        return ws.buf, ws.buf.numel(), 0
+    if ws.buf is None or ws.buf.numel() < need:
+        size = max(need * 2, 1 << 20)
+        ws.buf = torch.zeros(size, dtype=torch.uint8, device=device)
+        ws.epoch = 0
+    ws.epoch += 1
+    if ws.epoch > _EPOCH_MAX:
+        ws.buf.zero_()
+        ws.epoch = 1
+    return ws.buf, ws.buf.numel(), ws.epoch
+
+
+_SCRATCH: Dict[Tuple[int, int, str], torch.Tensor] = {}
+
+
+def scratch(device: torch.device, nbytes: int, tag: str = "ray") -> torch.Tensor:
+    """A persistent uint8 scratch buffer per (device, stream, tag), separate from the look-back
+    workspace (kernels that clear their own scratch must not disturb its epochs)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(),
+           torch.cuda.current_stream(device).cuda_stream, tag)
+    buf = _SCRATCH.get(key)
+    if buf is None or buf.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing() and buf is not None:
+            raise RuntimeError("nerfacc_b200: warm up once outside CUDA-graph capture first")
+        buf = torch.empty(max(int(nbytes) * 2, 1 << 16), dtype=torch.uint8, device=device)
+        _SCRATCH[key] = buf
+    return buf

@@ -1,0 +1,132 @@
+// common.cuh — shared device/host helpers for libnerfacc_b200 (sm_100a only).
+//
+// Nothing here depends on libtorch: the library is plain CUDA behind a C ABI
+// (include/nerfacc_b200.h).  Memory is owned by the caller; kernels launch on the
+// caller's stream and never synchronise.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/nerfacc_b200.h"
+
+#ifndef __CUDA_ARCH__
+#define NFB_ARCH_OK 1
+#elif __CUDA_ARCH__ >= 1000
+#define NFB_ARCH_OK 1
+#else
+#error "libnerfacc_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace nfb {
+
+// ---------------------------------------------------------------- host side
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define NFB_CHECK_ARG(cond, ...)            \
+    do {                                    \
+        if (!(cond)) {                      \
+            ::nfb::set_error(__VA_ARGS__);  \
+            return NFB_ERR_INVALID_ARGUMENT; \
+        }                                   \
+    } while (0)
+
+#define NFB_CHECK_LAUNCH(what)                                                   \
+    do {                                                                         \
+        cudaError_t e__ = cudaGetLastError();                                    \
+        if (e__ != cudaSuccess) {                                                \
+            ::nfb::set_error("%s: %s", what, cudaGetErrorString(e__));           \
+            return NFB_ERR_CUDA;                                                 \
+        }                                                                        \
+    } while (0)
+
+int sm_count();
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <typename T>
+static inline T ceil_div(T a, T b) { return (a + b - 1) / b; }
+
+// ---------------------------------------------------------------- device side
+constexpr int kWarp = 32;
+constexpr unsigned kFull = 0xffffffffu;
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
+
+// Streaming 128-bit / 32-bit accesses: every array on this path is touched once
+// per kernel, so keep it out of L1 (ld.global.nc.L1::no_allocate) and write with
+// st.global.L1::no_allocate; L2 (126 MB) stays the only cache level in play.
+__device__ __forceinline__ float4 ldg_stream4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float ldg_stream(const float* p) {
+    float r;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg_stream4(float* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void stg_stream(float* p, float v) {
+    asm volatile("st.global.L1::no_allocate.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+}
+
+// 64-bit relaxed device-scope accesses for look-back status words.
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// packed_info is int64 [n_rays, 2] = (start, count) interleaved: one 16-byte load.
+struct RayChunk { long long start, cnt; };
+__device__ __forceinline__ RayChunk load_chunk(const int64_t* packed_info, long long r) {
+    const longlong2 v = __ldg(reinterpret_cast<const longlong2*>(packed_info) + r);
+    return RayChunk{v.x, v.y};
+}
+
+// Warp-cooperative 32-ary search: first index r in [0, n) with pred(r) true
+// (pred must be monotone false..true), n if none.  All 32 lanes must call it with
+// the same arguments; every lane returns the same answer.  log32(n) dependent
+// probes instead of log2(n): 4 rounds for 2^20 rays.
+template <typename Pred>
+__device__ __forceinline__ long long warp_search_first(long long n, Pred pred) {
+    long long lo = 0, hi = n;  // answer in [lo, hi]
+    const int lane = lane_id();
+    while (hi - lo > 0) {
+        const long long len = hi - lo;
+        if (len <= 32) {
+            const bool p = (lane < len) ? pred(lo + lane) : true;
+            const unsigned m = __ballot_sync(kFull, p);
+            if (m == 0u) return hi;
+            const int f = __ffs(m) - 1;
+            return (f < len) ? lo + f : hi;
+        }
+        const long long stride = (len + 31) >> 5;
+        long long probe = lo + (long long)(lane + 1) * stride - 1;
+        if (probe > hi - 1) probe = hi - 1;
+        const bool p = pred(probe);
+        const unsigned m = __ballot_sync(kFull, p);
+        if (m == 0) return hi;  // even the last probe (hi-1) is false
+        const int f = __ffs(m) - 1;
+        long long nlo = lo + (long long)f * stride;
+        long long nhi = lo + (long long)(f + 1) * stride - 1;
+        if (nhi > hi - 1) nhi = hi - 1;
+        // pred(nhi) is true, pred(nlo-1) is false: answer in [nlo, nhi]
+        lo = nlo;
+        hi = nhi;
+        if (lo == hi) return lo;
+    }
+    return lo;
+}
+
+}  // namespace nfb

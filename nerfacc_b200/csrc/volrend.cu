@@ -1,0 +1,284 @@
+// volrend.cu — fused volume-rendering weights: alpha / density -> (weights, transmittance,
+// alphas, visibility) forward, and the matching reverse-mode backward, one pass each.
+//
+// The reference composes these from 5-7 elementwise torch kernels around one packed scan
+// (nerfacc/volrend.py:161-480) and lets autograd keep 3-4 sample-sized temporaries.  Here the
+// elementwise math is folded into the load and store of the flat segmented scan tile
+// (seg_tile.cuh):
+//   forward  alpha  : T = exclusive_prod(1-a) [*prefix];           w = T*a        12 B/sample
+//   forward  density: sd = s*(te-ts); a = 1-exp(-sd);
+//                     T = exp(-exclusive_sum(sd)) [*prefix];        w = T*a        24 B/sample
+//   backward alpha  : g_a = g_w*T - revexcl_sum((g_T+g_w*a)*T) / max(1-a,1e-10)    16 B/sample
+//   backward density: g_s = ((g_a+g_w*T)*e - revexcl_sum((g_T+g_w*a)*T)) * (te-ts) 24 B/sample
+// The backward formulas are exactly what torch autograd derives from the reference's
+// composite, including its clamp_min(1e-10) division in the product-scan backward
+// (csrc/scan.cu:299-300), so gradients match the reference, not the "ideal" derivative.
+#include "seg_tile.cuh"
+
+namespace nfb {
+
+struct WeightFwdArgs {
+    const float* alphas;    // alpha mode input
+    const float* t_starts;  // density mode inputs
+    const float* t_ends;
+    const float* sigmas;
+    const float* prefix;    // optional prefix_trans
+    float* weights;         // optional outputs
+    float* trans;
+    float* alphas_out;
+    uint8_t* vis;
+    float early_stop_eps, alpha_thre;
+    SegSpec seg;
+    long long n, n_tiles;
+    unsigned long long* status;
+    uint32_t epoch;
+    bool vec_ok;
+};
+
+template <bool DENSITY>
+__global__ void __launch_bounds__(kThreads) weight_fwd_kernel(const WeightFwdArgs p) {
+    __shared__ TileSmem sm;
+    const TileGeom<false> g(p.n, p.n_tiles);
+    float v[kVec][4];   // scanned quantity: (1-a) or sd
+    float al[kVec][4];  // alphas
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        if (DENSITY) {
+            float ts[4], te[4], s[4];
+            g.load(p.t_starts, p.vec_ok, k, 0.0f, ts);
+            g.load(p.t_ends, p.vec_ok, k, 0.0f, te);
+            g.load(p.sigmas, p.vec_ok, k, 0.0f, s);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                v[k][c] = __fmul_rn(s[c], __fsub_rn(te[c], ts[c]));
+                al[k][c] = __fsub_rn(1.0f, expf(-v[k][c]));
+            }
+        } else {
+            g.load(p.alphas, p.vec_ok, k, 0.0f, al[k]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) v[k][c] = __fsub_rn(1.0f, al[k][c]);
+        }
+    }
+    scatter_heads<false>(p.seg, g.base, p.n, sm.flags, sm.range);
+    uint32_t f[kVec];
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) f[k] = vec_flags(sm.flags, k);
+    float E[kVec];
+    if (DENSITY) tile_segscan<SumOp>(v, f, E, p.status, 0, p.epoch, sm);
+    else tile_segscan<ProdOp>(v, f, E, p.status, 0, p.epoch, sm);
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        float T[4];
+        if (DENSITY) {
+            finish_exclusive<SumOp>(v[k], f[k], E[k], T);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) T[c] = expf(-T[c]);
+        } else {
+            finish_exclusive<ProdOp>(v[k], f[k], E[k], T);
+        }
+        if (p.prefix) {
+            float pf[4];
+            g.load(p.prefix, p.vec_ok, k, 1.0f, pf);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) T[c] = __fmul_rn(T[c], pf[c]);
+        }
+        if (p.trans) g.store(p.trans, p.vec_ok, k, T);
+        if (p.alphas_out) g.store(p.alphas_out, p.vec_ok, k, al[k]);
+        if (p.weights) {
+            float w[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) w[c] = __fmul_rn(T[c], al[k][c]);
+            g.store(p.weights, p.vec_ok, k, w);
+        }
+        if (p.vis) {  // volrend.py:414-417, 476-479: T >= eps [& a >= thre if thre > 0]
+            const long long gi = g.base + g.voff(k);
+            uint8_t m[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                bool ok = T[c] >= p.early_stop_eps;
+                if (p.alpha_thre > 0.0f) ok = ok && (al[k][c] >= p.alpha_thre);
+                m[c] = ok ? 1 : 0;
+            }
+            if (p.vec_ok && gi + 3 < p.n) {
+                *reinterpret_cast<uchar4*>(p.vis + gi) = make_uchar4(m[0], m[1], m[2], m[3]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (gi + c < p.n) p.vis[gi + c] = m[c];
+            }
+        }
+    }
+}
+
+struct WeightBwdArgs {
+    const float* g_weights;  // any of the three upstream grads may be null (= zero)
+    const float* g_trans;
+    const float* g_alphas;
+    const float* alphas;     // alpha mode
+    const float* t_starts;   // density mode
+    const float* t_ends;
+    const float* sigmas;
+    const float* trans;      // saved forward output (prefix already applied)
+    float* g_in;             // grad wrt alphas (alpha mode) or sigmas (density mode)
+    SegSpec seg;
+    long long n, n_tiles;
+    unsigned long long* status;
+    uint32_t epoch;
+    bool vec_ok;
+};
+
+template <bool DENSITY>
+__global__ void __launch_bounds__(kThreads) weight_bwd_kernel(const WeightBwdArgs p) {
+    __shared__ TileSmem sm;
+    const TileGeom<true> g(p.n, p.n_tiles);
+    float v[kVec][4];    // s = (g_T + g_w*a) * T, reverse-exclusive-summed
+    float dir[kVec][4];  // direct term
+    float sc[kVec][4];   // alpha: max(1-a, 1e-10) ; density: te - ts
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        float T[4], gw[4], gT[4], a[4];
+        g.load(p.trans, p.vec_ok, k, 0.0f, T);
+        if (p.g_weights) g.load(p.g_weights, p.vec_ok, k, 0.0f, gw);
+        else { gw[0] = gw[1] = gw[2] = gw[3] = 0.0f; }
+        if (p.g_trans) g.load(p.g_trans, p.vec_ok, k, 0.0f, gT);
+        else { gT[0] = gT[1] = gT[2] = gT[3] = 0.0f; }
+        if (DENSITY) {
+            float ts[4], te[4], s[4], ga[4];
+            g.load(p.t_starts, p.vec_ok, k, 0.0f, ts);
+            g.load(p.t_ends, p.vec_ok, k, 0.0f, te);
+            g.load(p.sigmas, p.vec_ok, k, 0.0f, s);
+            if (p.g_alphas) g.load(p.g_alphas, p.vec_ok, k, 0.0f, ga);
+            else { ga[0] = ga[1] = ga[2] = ga[3] = 0.0f; }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float dt = __fsub_rn(te[c], ts[c]);
+                const float e = expf(-__fmul_rn(s[c], dt));
+                a[c] = __fsub_rn(1.0f, e);
+                sc[k][c] = dt;
+                dir[k][c] = __fmul_rn(__fadd_rn(ga[c], __fmul_rn(gw[c], T[c])), e);
+            }
+        } else {
+            g.load(p.alphas, p.vec_ok, k, 0.0f, a);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                sc[k][c] = fmaxf(__fsub_rn(1.0f, a[c]), 1e-10f);
+                dir[k][c] = __fmul_rn(gw[c], T[c]);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            v[k][c] = __fmul_rn(__fadd_rn(gT[c], __fmul_rn(gw[c], a[c])), T[c]);
+    }
+    scatter_heads<true>(p.seg, g.base, p.n, sm.flags, sm.range);
+    uint32_t f[kVec];
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) f[k] = vec_flags(sm.flags, k);
+    float E[kVec];
+    tile_segscan<SumOp>(v, f, E, p.status, 0, p.epoch, sm);
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        float R[4], o[4];
+        finish_exclusive<SumOp>(v[k], f[k], E[k], R);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (DENSITY) o[c] = __fmul_rn(__fsub_rn(dir[k][c], R[c]), sc[k][c]);
+            else o[c] = __fsub_rn(dir[k][c], __fdiv_rn(R[c], sc[k][c]));
+        }
+        g.store(p.g_in, p.vec_ok, k, o);
+    }
+}
+
+static int prep_ws(void* ws, size_t ws_bytes, long long n, uint32_t& epoch, cudaStream_t s) {
+    const size_t need = nfb_workspace_bytes(n);
+    if (ws == nullptr || ws_bytes < need) {
+        set_error("workspace too small: need %zu bytes, got %zu", need, ws_bytes);
+        return NFB_ERR_WORKSPACE;
+    }
+    if (epoch == 0) {
+        if (cudaMemsetAsync(ws, 0, need, s) != cudaSuccess) {
+            set_error("workspace memset failed");
+            return NFB_ERR_CUDA;
+        }
+        epoch = kEpochMemset;
+    } else if (epoch >= kEpochMemset) {
+        set_error("epoch must be in [1, 2^30-2]");
+        return NFB_ERR_INVALID_ARGUMENT;
+    }
+    return NFB_OK;
+}
+
+static bool all_aligned16(std::initializer_list<const void*> ps) {
+    for (const void* q : ps)
+        if (q != nullptr && !aligned16(q)) return false;
+    return true;
+}
+
+}  // namespace nfb
+
+extern "C" {
+
+NFB_API int nfb_render_weight_fwd(int from_density, const float* alphas, const float* t_starts,
+                                  const float* t_ends, const float* sigmas, const float* prefix_trans,
+                                  const int64_t* packed_info, int64_t n_rays, int64_t uniform_len,
+                                  int64_t n, float* weights, float* trans, float* alphas_out,
+                                  uint8_t* vis, float early_stop_eps, float alpha_thre,
+                                  void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                  nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0 && n_rays >= 0, "negative size");
+    if (n == 0) return NFB_OK;
+    NFB_CHECK_ARG(packed_info != nullptr || uniform_len > 0, "need packed_info or uniform_len");
+    NFB_CHECK_ARG(packed_info == nullptr || aligned16(packed_info), "packed_info must be 16-byte aligned");
+    if (from_density) NFB_CHECK_ARG(t_starts && t_ends && sigmas, "density mode needs t_starts, t_ends, sigmas");
+    else NFB_CHECK_ARG(alphas != nullptr, "alpha mode needs alphas");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = prep_ws(workspace, workspace_bytes, n, epoch, s);
+    if (rc != NFB_OK) return rc;
+    WeightFwdArgs a{};
+    a.alphas = alphas; a.t_starts = t_starts; a.t_ends = t_ends; a.sigmas = sigmas; a.prefix = prefix_trans;
+    a.weights = weights; a.trans = trans; a.alphas_out = alphas_out; a.vis = vis;
+    a.early_stop_eps = early_stop_eps; a.alpha_thre = alpha_thre;
+    a.seg = SegSpec{packed_info, n_rays, uniform_len};
+    a.n = n; a.n_tiles = num_tiles(n);
+    a.status = static_cast<unsigned long long*>(workspace); a.epoch = epoch;
+    a.vec_ok = all_aligned16({alphas, t_starts, t_ends, sigmas, prefix_trans, weights, trans, alphas_out}) &&
+               (vis == nullptr || (reinterpret_cast<uintptr_t>(vis) & 3u) == 0);
+    if (from_density) weight_fwd_kernel<true><<<(unsigned)a.n_tiles, kThreads, 0, s>>>(a);
+    else weight_fwd_kernel<false><<<(unsigned)a.n_tiles, kThreads, 0, s>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("render_weight_fwd");
+    return NFB_OK;
+}
+
+NFB_API int nfb_render_weight_bwd(int from_density, const float* g_weights, const float* g_trans,
+                                  const float* g_alphas, const float* alphas, const float* t_starts,
+                                  const float* t_ends, const float* sigmas, const float* trans,
+                                  const int64_t* packed_info, int64_t n_rays, int64_t uniform_len,
+                                  int64_t n, float* g_in, void* workspace, size_t workspace_bytes,
+                                  uint32_t epoch, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0 && n_rays >= 0, "negative size");
+    if (n == 0) return NFB_OK;
+    NFB_CHECK_ARG(packed_info != nullptr || uniform_len > 0, "need packed_info or uniform_len");
+    NFB_CHECK_ARG(packed_info == nullptr || aligned16(packed_info), "packed_info must be 16-byte aligned");
+    NFB_CHECK_ARG(trans && g_in, "null pointer");
+    if (from_density) NFB_CHECK_ARG(t_starts && t_ends && sigmas, "density mode needs t_starts, t_ends, sigmas");
+    else NFB_CHECK_ARG(alphas != nullptr, "alpha mode needs alphas");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = prep_ws(workspace, workspace_bytes, n, epoch, s);
+    if (rc != NFB_OK) return rc;
+    WeightBwdArgs a{};
+    a.g_weights = g_weights; a.g_trans = g_trans; a.g_alphas = g_alphas; a.alphas = alphas;
+    a.t_starts = t_starts; a.t_ends = t_ends; a.sigmas = sigmas; a.trans = trans; a.g_in = g_in;
+    a.seg = SegSpec{packed_info, n_rays, uniform_len};
+    a.n = n; a.n_tiles = num_tiles(n);
+    a.status = static_cast<unsigned long long*>(workspace); a.epoch = epoch;
+    a.vec_ok = all_aligned16({g_weights, g_trans, g_alphas, alphas, t_starts, t_ends, sigmas, trans, g_in});
+    if (from_density) weight_bwd_kernel<true><<<(unsigned)a.n_tiles, kThreads, 0, s>>>(a);
+    else weight_bwd_kernel<false><<<(unsigned)a.n_tiles, kThreads, 0, s>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("render_weight_bwd");
+    return NFB_OK;
+}
+
+}  // extern "C"

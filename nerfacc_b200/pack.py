@@ -1,0 +1,55 @@
+"""pack_info — drop-in for nerfacc/pack.py (reference nerfacc/pack.py:11-49)."""
+from typing import Optional
+
+import torch
+from torch import Tensor
+
+from . import _C
+from ._packing import mark_canonical, recall_packed_info, remember_packed_info
+
+
+@torch.no_grad()
+def pack_info(ray_indices: Tensor, n_rays: Optional[int] = None) -> Tensor:
+    """Pack `ray_indices` to `packed_info`. Useful for converting per sample data to per ray data.
+
+    Note:
+        this function is not differentiable to any inputs.
+
+    Args:
+        ray_indices: Ray indices of the samples. LongTensor with shape (n_sample).
+        n_rays: Number of rays. If None, it is inferred from `ray_indices`. Default is None.
+
+    Returns:
+        A LongTensor of shape (n_rays, 2) that specifies the start and count
+        of each chunk in the flattened input tensor, with in total n_rays chunks.
+
+    >>> ray_indices = torch.tensor([0, 0, 1, 1, 1, 2, 2, 2, 2], device="cuda")
+    >>> pack_info(ray_indices, n_rays=3)
+    tensor([[0, 2], [2, 3], [5, 4]], device='cuda:0')
+    """
+    assert (
+        ray_indices.dim() == 1
+    ), "ray_indices must be a 1D tensor with shape (n_samples)."
+    if not ray_indices.is_cuda:
+        raise NotImplementedError("Only support cuda inputs.")
+    known = recall_packed_info(ray_indices, n_rays)
+    if known is not None:
+        return known
+    device = ray_indices.device
+    if n_rays is None:
+        n_rays = int(ray_indices.max().item()) + 1
+    out_dtype = ray_indices.dtype
+    ri = ray_indices if ray_indices.dtype == torch.long else ray_indices.long()
+    ri = ri.contiguous()
+    packed_info = torch.empty((n_rays, 2), dtype=torch.long, device=device)
+    if n_rays > 0:
+        with torch.cuda.device(device):
+            ws = _C.scratch(device, 8 * (n_rays // 2048 + 2))
+            rc = _C.lib().nfb_pack_info(ri.data_ptr(), ri.numel(), n_rays, packed_info.data_ptr(),
+                                        ws.data_ptr(), ws.numel(), _C.stream_ptr(device))
+        _C.check(rc, "pack_info")
+    if out_dtype != torch.long:
+        return packed_info.to(out_dtype)
+    mark_canonical(packed_info)
+    remember_packed_info(ray_indices, packed_info, n_rays)
+    return packed_info
