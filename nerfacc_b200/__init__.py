@@ -1,0 +1,16 @@
+"""nerfacc_b200 — B200-native (sm_100a) implementation of nerfacc's rendering hot path behind
+nerfacc's own Python API (reference nerfacc/__init__.py:23-46).  No CPU fallback for packed ops."""
+from .pack import pack_info
+from .scan import exclusive_prod, exclusive_sum, inclusive_prod, inclusive_sum
+from .version import __version__
+from .volrend import (
+    accumulate_along_rays,
+    accumulate_along_rays_,
+    render_transmittance_from_alpha,
+    render_transmittance_from_density,
+    render_visibility_from_alpha,
+    render_visibility_from_density,
+    render_weight_from_alpha,
+    render_weight_from_density,
+    rendering,
+)

@@ -1,0 +1,188 @@
+"""Thin tensor-level wrappers over the fused rendering entry points of the C ABI
+(nfb_render_weight_fwd/bwd, nfb_accumulate_fwd/bwd) and the autograd Functions built on them.
+
+The public, reference-compatible API lives in volrend.py; this module only marshals
+tensors to pointers.  Segment layout is passed as either a canonical int64 packed_info
+or `uniform_len` (batched [..., n] tensors flattened, every row one segment).
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _C
+
+
+def _p(t: Optional[Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def weight_fwd(from_density: bool, alphas: Optional[Tensor], t_starts: Optional[Tensor],
+               t_ends: Optional[Tensor], sigmas: Optional[Tensor], prefix_trans: Optional[Tensor],
+               packed_info: Optional[Tensor], uniform_len: int, want_weights: bool,
+               want_trans: bool, want_alphas: bool, vis: Optional[Tuple[float, float]] = None):
+    """Returns (weights, trans, alphas_out, vis_mask); entries not asked for are None."""
+    like = sigmas if from_density else alphas
+    dev = _C.require_cuda(like, packed_info)
+    n = like.numel()
+    mk = lambda want: torch.empty_like(like) if want else None
+    weights, trans, alphas_out = mk(want_weights), mk(want_trans), mk(want_alphas and from_density)
+    mask = torch.empty(like.shape, dtype=torch.bool, device=dev) if vis is not None else None
+    if n > 0:
+        eps, thre = (float(vis[0]), float(vis[1])) if vis is not None else (0.0, 0.0)
+        n_rays = packed_info.shape[0] if packed_info is not None else n // max(uniform_len, 1)
+        with torch.cuda.device(dev):
+            ws, ws_bytes, epoch = _C.workspace(dev, n)
+            rc = _C.lib().nfb_render_weight_fwd(
+                int(from_density), _p(alphas), _p(t_starts), _p(t_ends), _p(sigmas),
+                _p(prefix_trans), _p(packed_info), n_rays, int(uniform_len), n, _p(weights),
+                _p(trans), _p(alphas_out), _p(mask), eps, thre, ws.data_ptr(), ws_bytes, epoch,
+                _C.stream_ptr(dev))
+        _C.check(rc, "render_weight_fwd")
+    return weights, trans, alphas_out, mask
+
+
+def weight_bwd(from_density: bool, g_weights: Optional[Tensor], g_trans: Optional[Tensor],
+               g_alphas: Optional[Tensor], alphas: Optional[Tensor], t_starts: Optional[Tensor],
+               t_ends: Optional[Tensor], sigmas: Optional[Tensor], trans: Tensor,
+               packed_info: Optional[Tensor], uniform_len: int) -> Tensor:
+    like = sigmas if from_density else alphas
+    dev = _C.require_cuda(like, trans)
+    n = like.numel()
+    g_in = torch.empty_like(like)
+    if n > 0:
+        n_rays = packed_info.shape[0] if packed_info is not None else n // max(uniform_len, 1)
+        with torch.cuda.device(dev):
+            ws, ws_bytes, epoch = _C.workspace(dev, n)
+            rc = _C.lib().nfb_render_weight_bwd(
+                int(from_density), _p(g_weights), _p(g_trans), _p(g_alphas), _p(alphas),
+                _p(t_starts), _p(t_ends), _p(sigmas), _p(trans), _p(packed_info), n_rays,
+                int(uniform_len), n, _p(g_in), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+        _C.check(rc, "render_weight_bwd")
+    return g_in
+
+
+def _cg(g: Optional[Tensor]) -> Optional[Tensor]:
+    return None if g is None else g.contiguous()
+
+
+class WeightFromAlpha(torch.autograd.Function):
+    """(weights, trans) = f(alphas): fused replacement of volrend.py:161-206, 267-309."""
+
+    @staticmethod
+    def forward(ctx, alphas, prefix_trans, packed_info, uniform_len: int, want_weights: bool):
+        alphas = alphas.contiguous()
+        weights, trans, _, _ = weight_fwd(False, alphas, None, None, None, prefix_trans,
+                                          packed_info, uniform_len, want_weights, True, False)
+        ctx.set_materialize_grads(False)
+        ctx.uniform_len = uniform_len
+        ctx.has_pi = packed_info is not None
+        if ctx.needs_input_grad[0]:
+            ctx.save_for_backward(alphas, trans, *([packed_info] if packed_info is not None else []))
+        if weights is None:
+            weights = trans.new_empty(0)
+            ctx.mark_non_differentiable(weights)
+        return weights, trans
+
+    @staticmethod
+    def backward(ctx, g_weights, g_trans):
+        saved = ctx.saved_tensors
+        alphas, trans = saved[0], saved[1]
+        packed_info = saved[2] if ctx.has_pi else None
+        if g_weights is None and g_trans is None:
+            return torch.zeros_like(alphas), None, None, None, None
+        g = weight_bwd(False, _cg(g_weights), _cg(g_trans), None, alphas, None, None, None,
+                       trans, packed_info, ctx.uniform_len)
+        return g, None, None, None, None
+
+
+class WeightFromDensity(torch.autograd.Function):
+    """(weights, trans, alphas) = f(sigmas): fused replacement of volrend.py:209-264, 312-362."""
+
+    @staticmethod
+    def forward(ctx, sigmas, t_starts, t_ends, prefix_trans, packed_info, uniform_len: int,
+                want_weights: bool):
+        sigmas, t_starts, t_ends = sigmas.contiguous(), t_starts.contiguous(), t_ends.contiguous()
+        weights, trans, alphas, _ = weight_fwd(True, None, t_starts, t_ends, sigmas, prefix_trans,
+                                               packed_info, uniform_len, want_weights, True, True)
+        ctx.set_materialize_grads(False)
+        ctx.uniform_len = uniform_len
+        ctx.has_pi = packed_info is not None
+        if ctx.needs_input_grad[0]:
+            ctx.save_for_backward(sigmas, t_starts, t_ends, trans,
+                                  *([packed_info] if packed_info is not None else []))
+        if weights is None:
+            weights = trans.new_empty(0)
+            ctx.mark_non_differentiable(weights)
+        return weights, trans, alphas
+
+    @staticmethod
+    def backward(ctx, g_weights, g_trans, g_alphas):
+        saved = ctx.saved_tensors
+        sigmas, t_starts, t_ends, trans = saved[:4]
+        packed_info = saved[4] if ctx.has_pi else None
+        if g_weights is None and g_trans is None and g_alphas is None:
+            return (torch.zeros_like(sigmas),) + (None,) * 6
+        g = weight_bwd(True, _cg(g_weights), _cg(g_trans), _cg(g_alphas), None, t_starts, t_ends,
+                       sigmas, trans, packed_info, ctx.uniform_len)
+        return (g,) + (None,) * 6
+
+
+# ----------------------------------------------------------------------------- accumulate
+def accumulate_fwd(weights: Tensor, values: Optional[Tensor], packed_info: Optional[Tensor],
+                   ray_indices: Optional[Tensor], n_rays: int, out: Optional[Tensor] = None) -> Tensor:
+    dev = _C.require_cuda(weights, values, packed_info, ray_indices, out)
+    dim = 1 if values is None else values.shape[-1]
+    add_into = out is not None
+    if out is None:
+        out = torch.empty((n_rays, dim), dtype=weights.dtype, device=dev)
+    n = weights.numel()
+    if n_rays > 0 and dim > 0:
+        with torch.cuda.device(dev):
+            ws, ws_bytes, epoch = _C.workspace(dev, max(n, 1))
+            rc = _C.lib().nfb_accumulate_fwd(
+                _p(weights), _p(values), dim, _p(packed_info), _p(ray_indices), n_rays, n,
+                out.data_ptr(), int(add_into), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+        _C.check(rc, "accumulate_fwd")
+    return out
+
+
+def accumulate_bwd(g_out: Tensor, weights: Tensor, values: Optional[Tensor], ray_indices: Tensor,
+                   need_gw: bool, need_gv: bool):
+    dev = _C.require_cuda(g_out, weights, values, ray_indices)
+    dim = g_out.shape[-1]
+    g_w = torch.empty_like(weights) if need_gw else None
+    g_v = torch.empty_like(values) if (need_gv and values is not None) else None
+    n = weights.numel()
+    if n > 0 and (g_w is not None or g_v is not None):
+        with torch.cuda.device(dev):
+            rc = _C.lib().nfb_accumulate_bwd(g_out.data_ptr(), _p(weights), _p(values), dim,
+                                             ray_indices.data_ptr(), n, _p(g_w), _p(g_v),
+                                             _C.stream_ptr(dev))
+        _C.check(rc, "accumulate_bwd")
+    return g_w, g_v
+
+
+class Accumulate(torch.autograd.Function):
+    """out[n_rays, D] = segmented sum of weights[:, None] * values (volrend.py:532-547)."""
+
+    @staticmethod
+    def forward(ctx, weights, values, packed_info, ray_indices, n_rays: int):
+        weights = weights.contiguous()
+        values = None if values is None else values.contiguous()
+        out = accumulate_fwd(weights, values, packed_info, ray_indices, n_rays)
+        ctx.save_for_backward(weights, *([values] if values is not None else []), ray_indices)
+        ctx.has_values = values is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        saved = ctx.saved_tensors
+        weights = saved[0]
+        values = saved[1] if ctx.has_values else None
+        ray_indices = saved[-1]
+        g_w, g_v = accumulate_bwd(g_out.contiguous(), weights, values, ray_indices,
+                                  ctx.needs_input_grad[0], ctx.has_values and ctx.needs_input_grad[1])
+        return g_w, g_v, None, None, None

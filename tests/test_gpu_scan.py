@@ -1,0 +1,115 @@
+"""Packed scans on the GPU (through the C ABI) against the CPU oracle.
+
+Tolerance: north_star asks for 1e-5 relative in fp32.  Our association differs from the
+reference's 32-wide Blelloch tree, so sums are compared with rtol=1e-5 plus an absolute term
+scaled to the row's magnitude (cancellation in signed rows), and both sides are also checked
+against the oracle's fp64 evaluation.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from tests._util import assert_close, packed_info_from_counts, ragged_counts
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    dict(n_rays=5, counts=[1000] * 5),                      # reference tests/test_scan.py
+    dict(n_rays=3, counts=[2, 3, 4]),                       # docstring vector
+    dict(n_rays=7, counts=[0, 0, 5, 0, 4097, 0, 0]),        # empties at both ends, tile-crossing ray
+    dict(n_rays=4, counts=[4096, 4096, 1, 4095]),           # rays ending exactly on tile edges
+    dict(n_rays=3, counts=[0, 30000, 3]),                   # one ray spanning 8 tiles (look-back chain)
+    dict(n_rays=20000, counts=None),                        # cfg3-shaped ragged mix
+]
+
+
+def _mk(case, seed=0, positive=False):
+    counts = case["counts"]
+    if counts is None:
+        counts = ragged_counts(case["n_rays"], seed=seed, long_rays=[(17, 9000), (18, 0), (19, 5000)])
+    pi = packed_info_from_counts(counts)
+    n = int(pi[:, 1].sum())
+    rng = np.random.default_rng(seed + 1)
+    x = rng.random(n).astype(np.float32) if positive else rng.standard_normal(n).astype(np.float32)
+    return x, pi
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("exclusive", [False, True])
+@pytest.mark.parametrize("reverse", [False, True])
+@pytest.mark.parametrize("canonical", [True, False])
+def test_sum_scan(device, case, exclusive, reverse, canonical):
+    from nerfacc_b200 import scan as S
+    from nerfacc_b200._packing import mark_canonical
+
+    x, pi = _mk(case)
+    xt = torch.from_numpy(x).to(device)
+    pit = torch.from_numpy(pi).to(device)
+    if canonical:
+        mark_canonical(pit)
+    out = S._scan(xt, pit, canonical, 0, exclusive, reverse).cpu().numpy()
+    ref = oracle.scan(x, pi, "sum", exclusive, reverse)
+    ref64 = oracle.scan_f64(x, pi, "sum", exclusive, reverse)
+    scale = float(np.abs(oracle.scan_f64(np.abs(x), pi, "sum", False, reverse)).max()) if x.size else 1.0
+    assert_close(out, ref64, 1e-5, 2e-7 * scale, "ours vs fp64")
+    assert_close(out, ref, 1e-5, 4e-7 * scale, "ours vs oracle fp32")
+
+
+@pytest.mark.parametrize("case", CASES[:5])
+@pytest.mark.parametrize("exclusive", [False, True])
+@pytest.mark.parametrize("canonical", [True, False])
+def test_prod_scan_and_backward(device, case, exclusive, canonical):
+    from nerfacc_b200 import scan as S
+
+    x, pi = _mk(case, positive=True)
+    x = (0.5 + 0.5 * x).astype(np.float32)  # keep long products representable
+    g = np.random.default_rng(5).standard_normal(x.shape[0]).astype(np.float32)
+    xt, gt = torch.from_numpy(x).to(device), torch.from_numpy(g).to(device)
+    pit = torch.from_numpy(pi).to(device)
+    out = S._scan(xt, pit, canonical, 1, exclusive, False)
+    ref = oracle.scan(x, pi, "prod", exclusive)
+    assert_close(out.cpu().numpy(), ref, 2e-5, 1e-30, "prod fwd")
+    gin = S._prod_bwd(gt, xt, out, pit, canonical, exclusive).cpu().numpy()
+    gref = oracle.prod_scan_backward(g, x, out.cpu().numpy(), pi, exclusive)
+    scale = float(np.abs(gref).max()) if gref.size else 1.0
+    assert_close(gin, gref, 2e-5, 2e-6 * scale, "prod bwd")
+
+
+def test_public_api_and_autograd(device):
+    """Same checks as the reference's tests/test_scan.py: packed == batched, forward and grad."""
+    import nerfacc_b200 as nf
+
+    torch.manual_seed(42)
+    for fn, kw in [(nf.inclusive_sum, {}), (nf.exclusive_sum, dict(atol=3e-4)),
+                   (nf.inclusive_prod, {}), (nf.exclusive_prod, {})]:
+        data = torch.rand((5, 1000), device=device, requires_grad=True)
+        o1 = fn(data).flatten()
+        o1.sum().backward()
+        g1 = data.grad.clone()
+        data.grad.zero_()
+        starts = torch.arange(0, data.numel(), data.shape[1], device=device, dtype=torch.long)
+        cnts = torch.full((data.shape[0],), data.shape[1], dtype=torch.long, device=device)
+        o2 = fn(data.flatten(), packed_info=torch.stack([starts, cnts], -1))
+        o2.sum().backward()
+        g2 = data.grad.clone()
+        assert torch.allclose(o1, o2, **kw), fn.__name__
+        assert torch.allclose(g1, g2, rtol=1e-4, atol=1e-5), fn.__name__
+
+
+def test_docstring_vectors(device):
+    import nerfacc_b200 as nf
+
+    x = torch.arange(1, 10, dtype=torch.float32, device=device)
+    pi = torch.tensor([[0, 2], [2, 3], [5, 4]], device=device)
+    assert nf.inclusive_sum(x, pi).tolist() == [1, 3, 3, 7, 12, 6, 13, 21, 30]
+    assert nf.exclusive_sum(x, pi).tolist() == [0, 1, 0, 3, 7, 0, 6, 13, 21]
+    assert nf.inclusive_prod(x, pi).tolist() == [1, 2, 3, 12, 60, 6, 42, 336, 3024]
+    assert nf.exclusive_prod(x, pi).tolist() == [1, 1, 1, 3, 12, 1, 6, 42, 336]
+
+
+def test_cpu_tensor_raises():
+    import nerfacc_b200 as nf
+
+    with pytest.raises(RuntimeError):
+        nf.inclusive_sum(torch.ones(4), torch.tensor([[0, 4]]))
