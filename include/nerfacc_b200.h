@@ -144,6 +144,112 @@ NFB_API int nfb_pack_info(const int64_t* ray_indices, int64_t n, int64_t n_rays,
                           int64_t* packed_info, void* workspace, size_t workspace_bytes,
                           nfb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * Occupancy-grid traversal.
+ * Replaces ray_aabb_intersect and traverse_grids of the reference's extension
+ * (csrc/grid.cu:284-313, 320-519; bound at csrc/nerfacc.cpp:42-70) and the
+ * intersect + cat + sort prologue of nerfacc/grid.py:158-162.
+ */
+typedef struct nfb_rays {
+    const float* rays_o;        /* [n_rays, 3] */
+    const float* rays_d;        /* [n_rays, 3] */
+    const uint8_t* rays_mask;   /* [n_rays] or NULL (honoured like the reference: single-pass mode) */
+    const float* near_planes;   /* [n_rays] or NULL -> near_plane */
+    const float* far_planes;    /* [n_rays] or NULL -> far_plane */
+    float near_plane, far_plane;
+    const float* t_sorted;      /* [n_rays, 2m] precomputed sorted ray/box events, or NULL: computed */
+    const int64_t* t_indices;   /* [n_rays, 2m]   in the kernel (near=-inf, far=inf, miss=inf,   */
+    const uint8_t* hits;        /* [n_rays, m]     stable sort), grid.py:158-162                  */
+    int64_t n_rays;
+} nfb_rays_t;
+
+typedef struct nfb_grid {
+    const uint32_t* occ_bits;   /* bit field from nfb_pack_occupancy: [n_grids*rx*ry*rz] bits */
+    const float* aabbs;         /* [n_grids, 6] */
+    int32_t n_grids;            /* <= 8 (MAX_GRID_LEVELS, csrc/grid.cu:18) */
+    int32_t res[3];
+} nfb_grid_t;
+
+typedef struct nfb_march {
+    float step_size;            /* <= 0: one interval per occupied voxel crossing */
+    float cone_angle;
+    int32_t traverse_steps_limit; /* <= 0: none */
+} nfb_march_t;
+
+/* t_mins/t_maxs [n_rays, n_aabbs] float, hits [n_rays, n_aabbs] bytes. */
+NFB_API int nfb_ray_aabb_intersect(const float* rays_o, const float* rays_d, const float* aabbs,
+                                   int64_t n_rays, int64_t n_aabbs, float near_plane,
+                                   float far_plane, float miss_value, float* t_mins,
+                                   float* t_maxs, uint8_t* hits, nfb_stream_t stream);
+
+/* binaries: 1 byte per cell (torch.bool) -> bits: ceil(n_cells/32) uint32 words. */
+NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int64_t n_cells, uint32_t* bits,
+                               nfb_stream_t stream);
+
+/* Pass 1 (csrc/grid.cu:413-438 + data_spec.hpp:90-93): per-ray counts -> complete, canonical
+ * packed_info for samples and for interval edges (int64 [n_rays,2] each, interval_info may be
+ * NULL), termination planes [n_rays] (may be NULL; defined for every ray), and the grand
+ * totals {n_samples, n_edges} written to totals[0..1] (any device-visible memory, e.g. pinned
+ * host memory: read it after synchronising the stream).  `scratch`: 16 bytes per 2048 rays. */
+NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
+                               const nfb_march_t* march, int64_t* sample_info,
+                               int64_t* interval_info, float* termination_planes,
+                               int64_t* totals, void* scratch, size_t scratch_bytes,
+                               nfb_stream_t stream);
+
+/* Pass 2, OccGridEstimator.sampling outputs (estimators/occ_grid.py:174-177): for every sample,
+ * in packed order, ray_indices, t_starts (= left edge) and t_ends (= right edge). */
+NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t* grid,
+                                       const nfb_march_t* march, const int64_t* sample_info,
+                                       int64_t* ray_indices, float* t_starts, float* t_ends,
+                                       nfb_stream_t stream);
+
+/* Pass 2, traverse_grids outputs (csrc/grid.cu:445-470): interval edges {vals, ray_indices,
+ * is_left, is_right} and samples {vals, ray_indices, is_valid}.
+ * over_allocate == 0: two-pass layout, data at the starts recorded in sample_info/interval_info
+ *   by nfb_traverse_count; every slot is written.
+ * over_allocate == 1 (csrc/grid.cu:364-404): single pass; ray r's data goes to
+ *   sample_starts[r] / interval_starts[r] (the caller's over-allocated layout, arrays must be
+ *   zero-filled), rays_mask is honoured, and sample_info/interval_info/termination_planes/
+ *   totals are produced here with the *compact* starts, as the reference does. */
+NFB_API int nfb_traverse_fill(const nfb_rays_t* rays, const nfb_grid_t* grid,
+                              const nfb_march_t* march, int over_allocate,
+                              const int64_t* sample_starts, const int64_t* interval_starts,
+                              int64_t* sample_info, int64_t* interval_info,
+                              float* termination_planes, int64_t* totals, float* iv_vals,
+                              int64_t* iv_ray_indices, uint8_t* iv_is_left, uint8_t* iv_is_right,
+                              float* sm_vals, int64_t* sm_ray_indices, uint8_t* sm_is_valid,
+                              void* scratch, size_t scratch_bytes, nfb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * Occupancy-grid update (nerfacc/estimators/occ_grid.py:367-404) and visibility compaction
+ * (occ_grid.py:216-220).
+ */
+/* x[i,:] = aabb[:3] + ((ijk(cells[i]) + u[i,:]) / res) * (aabb[3:] - aabb[:3])  (occ_grid.py:385-392).
+ * `res_host` is a HOST pointer to 3 ints; cell id = (i*res_y + j)*res_z + k. */
+NFB_API int nfb_occ_cell_points(const int64_t* cells, const float* u, int64_t n,
+                                const int32_t* res_host, const float* aabb, float* x,
+                                nfb_stream_t stream);
+/* occs[c] = max(occs[c]*decay, max over k in [eval_lo,eval_hi) with cell_ids[k]==c of occ[k-eval_lo])
+ * for every c in cell_ids[0..n): scatter-max semantics of occ_grid.py:395-402, the decay applied
+ * once per touched cell.  `tmp`: n floats of scratch. */
+NFB_API int nfb_occ_ema_update(float* occs, const int64_t* cell_ids, int64_t n, const float* occ,
+                               int64_t eval_lo, int64_t eval_hi, float decay, float* tmp,
+                               nfb_stream_t stream);
+/* thre = min(mean(occs[occs >= 0]), occ_thre); binaries[i] = occs[i] > thre (occ_grid.py:403-404).
+ * thre_out (device, optional) receives the threshold. */
+NFB_API size_t nfb_occ_binarize_workspace_bytes(void);
+NFB_API int nfb_occ_binarize(const float* occs, int64_t n_cells, float occ_thre, uint8_t* binaries,
+                             float* thre_out, void* workspace, size_t workspace_bytes,
+                             nfb_stream_t stream);
+/* Keep the samples with mask[i] != 0, order preserved; *total (device-visible) = how many. */
+NFB_API size_t nfb_compact_workspace_bytes(int64_t n);
+NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
+                                const float* t_starts, const float* t_ends, int64_t n,
+                                int64_t* out_ray_indices, float* out_t_starts, float* out_t_ends,
+                                int64_t* total, void* workspace, size_t workspace_bytes,
+                                nfb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

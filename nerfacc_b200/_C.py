@@ -29,6 +29,26 @@ c_f32 = C.c_float
 c_size = C.c_size_t
 c_ptr = C.c_void_p
 
+
+
+class Rays(C.Structure):
+    """nfb_rays_t"""
+    _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_mask", c_ptr), ("near_planes", c_ptr),
+                ("far_planes", c_ptr), ("near_plane", c_f32), ("far_plane", c_f32),
+                ("t_sorted", c_ptr), ("t_indices", c_ptr), ("hits", c_ptr), ("n_rays", c_i64)]
+
+
+class Grid(C.Structure):
+    """nfb_grid_t"""
+    _fields_ = [("occ_bits", c_ptr), ("aabbs", c_ptr), ("n_grids", C.c_int32), ("res", C.c_int32 * 3)]
+
+
+class March(C.Structure):
+    """nfb_march_t"""
+    _fields_ = [("step_size", c_f32), ("cone_angle", c_f32), ("traverse_steps_limit", C.c_int32)]
+
+
+_sp = C.POINTER
 # name -> argtypes; every function returns int unless listed in _RESTYPES.
 _PROTOS = {
     "nfb_version": [],
@@ -48,11 +68,28 @@ _PROTOS = {
                            c_ptr, c_size, c_u32, c_ptr],
     "nfb_accumulate_bwd": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "nfb_pack_info": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_size, c_ptr],
+    "nfb_ray_aabb_intersect": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_f32, c_f32, c_ptr, c_ptr,
+                               c_ptr, c_ptr],
+    "nfb_pack_occupancy": [c_ptr, c_i64, c_ptr, c_ptr],
+    "nfb_traverse_count": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                           c_size, c_ptr],
+    "nfb_traverse_fill_sampling": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "nfb_occ_cell_points": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
+    "nfb_occ_ema_update": [c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_i64, c_f32, c_ptr, c_ptr],
+    "nfb_occ_binarize_workspace_bytes": [],
+    "nfb_occ_binarize": [c_ptr, c_i64, c_f32, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
+    "nfb_compact_workspace_bytes": [c_i64],
+    "nfb_compact_samples": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                            c_size, c_ptr],
+    "nfb_traverse_fill": [_sp(Rays), _sp(Grid), _sp(March), c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                          c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
 }
 _RESTYPES = {
     "nfb_last_error": C.c_char_p,
     "nfb_launch_count": C.c_longlong,
     "nfb_workspace_bytes": C.c_size_t,
+    "nfb_occ_binarize_workspace_bytes": C.c_size_t,
+    "nfb_compact_workspace_bytes": C.c_size_t,
 }
 
 

@@ -1,5 +1,8 @@
 """nerfacc_b200 — B200-native (sm_100a) implementation of nerfacc's rendering hot path behind
 nerfacc's own Python API (reference nerfacc/__init__.py:23-46).  No CPU fallback for packed ops."""
+from .data_specs import RayIntervals, RaySamples
+from .estimators.occ_grid import OccGridEstimator
+from .grid import ray_aabb_intersect, traverse_grids
 from .pack import pack_info
 from .scan import exclusive_prod, exclusive_sum, inclusive_prod, inclusive_sum
 from .version import __version__

@@ -1,0 +1,156 @@
+"""Tensor-level wrappers over the traversal entry points of the C ABI (nfb_traverse_*,
+nfb_pack_occupancy, nfb_ray_aabb_intersect in include/nerfacc_b200.h)."""
+from __future__ import annotations
+
+import ctypes as C
+import weakref
+from typing import Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _C
+
+_BITS: Dict[int, Tuple[weakref.ref, int, Tensor]] = {}
+
+
+def occupancy_bits(binaries: Tensor) -> Tensor:
+    """Bit-packed copy of a bool grid [m, rx, ry, rz] (int32 words, 32 cells each), cached per
+    tensor object and in-place version so repeated marches through the same grid pack once."""
+    key = id(binaries)
+    ent = _BITS.get(key)
+    if ent is not None and ent[0]() is binaries and ent[1] == binaries._version:
+        return ent[2]
+    dev = _C.require_cuda(binaries)
+    b = binaries.contiguous()
+    if b.dtype != torch.bool:
+        b = b != 0
+    n = b.numel()
+    bits = torch.empty(((n + 31) // 32,), dtype=torch.int32, device=dev)
+    if n:
+        with torch.cuda.device(dev):
+            rc = _C.lib().nfb_pack_occupancy(b.data_ptr(), n, bits.data_ptr(), _C.stream_ptr(dev))
+        _C.check(rc, "pack_occupancy")
+
+    def _drop(_r, key=key):
+        _BITS.pop(key, None)
+
+    _BITS[key] = (weakref.ref(binaries, _drop), binaries._version, bits)
+    return bits
+
+
+_PINNED: Dict[int, Tensor] = {}
+
+
+def _pinned_totals(dev: torch.device) -> Tensor:
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    t = _PINNED.get(idx)
+    if t is None:
+        t = _PINNED[idx] = torch.zeros(2, dtype=torch.long).pin_memory()
+    return t
+
+
+class Marcher:
+    """One traversal problem: keeps the tensors alive and owns the C descriptors."""
+
+    def __init__(self, rays_o: Tensor, rays_d: Tensor, binaries: Tensor, aabbs: Tensor,
+                 near_planes, far_planes, step_size: float, cone_angle: float, limit: int,
+                 rays_mask: Optional[Tensor] = None, t_sorted: Optional[Tensor] = None,
+                 t_indices: Optional[Tensor] = None, hits: Optional[Tensor] = None):
+        self.dev = _C.require_cuda(rays_o, rays_d, binaries, aabbs)
+        f32 = lambda t: t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+        self.rays_o, self.rays_d, self.aabbs = f32(rays_o), f32(rays_d), f32(aabbs)
+        self.n_rays = self.rays_o.shape[0]
+        assert binaries.dim() == 4 and binaries.shape[0] == self.aabbs.shape[0]
+        self.bits = occupancy_bits(binaries)
+        keep = [self.rays_o, self.rays_d, self.aabbs, self.bits]
+        r = _C.Rays()
+        r.rays_o, r.rays_d = self.rays_o.data_ptr(), self.rays_d.data_ptr()
+        r.n_rays = self.n_rays
+        for name, val, default in (("near", near_planes, 0.0), ("far", far_planes, float("inf"))):
+            if isinstance(val, Tensor):
+                t = f32(val)
+                keep.append(t)
+                setattr(r, name + "_planes", t.data_ptr())
+            else:
+                setattr(r, name + "_plane", float(default if val is None else val))
+        if rays_mask is not None:
+            m = rays_mask.contiguous()
+            m = m if m.dtype == torch.bool else (m != 0)
+            keep.append(m)
+            r.rays_mask = m.data_ptr()
+        if t_sorted is not None and t_indices is not None and hits is not None:
+            ts, ti = f32(t_sorted), t_indices.long().contiguous()
+            hh = hits.contiguous() if hits.dtype == torch.bool else (hits != 0).contiguous()
+            keep += [ts, ti, hh]
+            r.t_sorted, r.t_indices, r.hits = ts.data_ptr(), ti.data_ptr(), hh.data_ptr()
+        g = _C.Grid()
+        g.occ_bits, g.aabbs, g.n_grids = self.bits.data_ptr(), self.aabbs.data_ptr(), binaries.shape[0]
+        g.res[0], g.res[1], g.res[2] = binaries.shape[1], binaries.shape[2], binaries.shape[3]
+        self._keep, self.rays, self.grid = keep, r, g
+        self.march = _C.March(float(step_size), float(cone_angle), int(limit))
+
+    def _scratch(self) -> Tensor:
+        return _C.scratch(self.dev, 16 * (self.n_rays // 2048 + 2), "ray")
+
+    def count(self, want_intervals: bool, want_term: bool):
+        """Pass 1.  Returns (sample_info, interval_info|None, termination|None, n_samples, n_edges);
+        synchronises the stream once to learn the totals (the only host sync of a traversal)."""
+        dev, n = self.dev, self.n_rays
+        sample_info = torch.empty((n, 2), dtype=torch.long, device=dev)
+        interval_info = torch.empty((n, 2), dtype=torch.long, device=dev) if want_intervals else None
+        term = torch.empty((n,), dtype=torch.float32, device=dev) if want_term else None
+        if n == 0:
+            return sample_info, interval_info, term, 0, 0
+        totals = _pinned_totals(dev)
+        with torch.cuda.device(dev):
+            sc = self._scratch()
+            rc = _C.lib().nfb_traverse_count(
+                C.byref(self.rays), C.byref(self.grid), C.byref(self.march), sample_info.data_ptr(),
+                None if interval_info is None else interval_info.data_ptr(),
+                None if term is None else term.data_ptr(), totals.data_ptr(), sc.data_ptr(),
+                sc.numel(), _C.stream_ptr(dev))
+            _C.check(rc, "traverse_count")
+            torch.cuda.current_stream(dev).synchronize()
+        return sample_info, interval_info, term, int(totals[0]), int(totals[1])
+
+    def fill_sampling(self, sample_info: Tensor, n_samples: int):
+        dev = self.dev
+        ray_indices = torch.empty((n_samples,), dtype=torch.long, device=dev)
+        t_starts = torch.empty((n_samples,), dtype=torch.float32, device=dev)
+        t_ends = torch.empty((n_samples,), dtype=torch.float32, device=dev)
+        if n_samples > 0:
+            with torch.cuda.device(dev):
+                rc = _C.lib().nfb_traverse_fill_sampling(
+                    C.byref(self.rays), C.byref(self.grid), C.byref(self.march),
+                    sample_info.data_ptr(), ray_indices.data_ptr(), t_starts.data_ptr(),
+                    t_ends.data_ptr(), _C.stream_ptr(dev))
+            _C.check(rc, "traverse_fill_sampling")
+        return ray_indices, t_starts, t_ends
+
+    def fill_full(self, over_allocate: bool, sample_info: Tensor, interval_info: Tensor,
+                  n_samples: int, n_edges: int, sample_starts: Optional[Tensor] = None,
+                  interval_starts: Optional[Tensor] = None, term: Optional[Tensor] = None):
+        dev = self.dev
+        mk = torch.zeros if over_allocate else torch.empty
+        iv = dict(vals=mk((n_edges,), dtype=torch.float32, device=dev),
+                  ray_indices=mk((n_edges,), dtype=torch.long, device=dev),
+                  is_left=mk((n_edges,), dtype=torch.bool, device=dev),
+                  is_right=mk((n_edges,), dtype=torch.bool, device=dev))
+        sm = dict(vals=mk((n_samples,), dtype=torch.float32, device=dev),
+                  ray_indices=mk((n_samples,), dtype=torch.long, device=dev),
+                  is_valid=mk((n_samples,), dtype=torch.bool, device=dev))
+        if self.n_rays > 0 and (over_allocate or n_samples > 0):
+            totals = _pinned_totals(dev)
+            with torch.cuda.device(dev):
+                sc = self._scratch()
+                p = lambda t: None if t is None else t.data_ptr()
+                rc = _C.lib().nfb_traverse_fill(
+                    C.byref(self.rays), C.byref(self.grid), C.byref(self.march), int(over_allocate),
+                    p(sample_starts), p(interval_starts), sample_info.data_ptr(),
+                    interval_info.data_ptr(), p(term), totals.data_ptr(), iv["vals"].data_ptr(),
+                    iv["ray_indices"].data_ptr(), iv["is_left"].data_ptr(), iv["is_right"].data_ptr(),
+                    sm["vals"].data_ptr(), sm["ray_indices"].data_ptr(), sm["is_valid"].data_ptr(),
+                    sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
+            _C.check(rc, "traverse_fill")
+        return iv, sm

@@ -1,0 +1,118 @@
+"""Tensor-level wrappers for the occupancy-grid update / compaction entry points of the C ABI
+and the (single) collective of the hot path: a MAX all-reduce of `occs` across ranks."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Tuple
+
+import torch
+from torch import Tensor
+
+from . import _C
+from ._grid_ops import _pinned_totals
+from .pack import pack_info
+
+
+def dist_info() -> Tuple[int, int]:
+    """(world_size, rank) of the default process group, (1, 0) when not distributed."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(), dist.get_rank()
+    return 1, 0
+
+
+def shard_range(n: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous slice [lo, hi) of n items owned by `rank`."""
+    per = (n + world - 1) // world
+    lo = min(rank * per, n)
+    return lo, min(lo + per, n)
+
+
+def all_reduce_max(occs: Tensor) -> None:
+    """The only collective on the path: every rank decayed the same cells and
+    max-ed in its own shard of evaluations; MAX across ranks completes the scatter-max."""
+    import torch.distributed as dist
+
+    dist.all_reduce(occs, op=dist.ReduceOp.MAX)
+
+
+def cell_points(cells: Tensor, u: Tensor, resolution: Tensor, aabb: Tensor) -> Tensor:
+    """World positions of jittered cell samples (occ_grid.py:385-392)."""
+    n = cells.shape[0]
+    res = [int(v) for v in resolution.tolist()]
+    if not cells.is_cuda:
+        coords = torch.stack([cells // (res[1] * res[2]), (cells // res[2]) % res[1], cells % res[2]], -1)
+        x = (coords + u) / resolution
+        return aabb[:3] + x * (aabb[3:] - aabb[:3])
+    dev = _C.require_cuda(cells, u, aabb)
+    x = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    if n:
+        cells, u, aabb = cells.long().contiguous(), u.float().contiguous(), aabb.float().contiguous()
+        res_host = (C.c_int32 * 3)(*res)
+        with torch.cuda.device(dev):
+            rc = _C.lib().nfb_occ_cell_points(cells.data_ptr(), u.data_ptr(), n, res_host,
+                                              aabb.data_ptr(), x.data_ptr(), _C.stream_ptr(dev))
+        _C.check(rc, "occ_cell_points")
+    return x
+
+
+def ema_update(occs: Tensor, cell_ids: Tensor, occ: Tensor, lo: int, hi: int, decay: float) -> None:
+    """In place: occs[c] = max(occs[c] * decay, new values of c) for the cells in cell_ids;
+    `occ` holds the evaluations of cell_ids[lo:hi]."""
+    n = cell_ids.shape[0]
+    if n == 0:
+        return
+    if not occs.is_cuda:
+        occs[cell_ids] = occs[cell_ids] * decay
+        occs.scatter_reduce_(0, cell_ids[lo:hi], occ.to(occs.dtype), "amax", include_self=True)
+        return
+    dev = _C.require_cuda(occs, cell_ids, occ)
+    assert occs.is_contiguous() and occs.dtype == torch.float32
+    cell_ids = cell_ids.long().contiguous()
+    occ = occ.float().contiguous()
+    assert occ.shape[0] == hi - lo, (occ.shape, lo, hi)
+    tmp = torch.empty((n,), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _C.lib().nfb_occ_ema_update(occs.data_ptr(), cell_ids.data_ptr(), n, occ.data_ptr(), lo, hi,
+                                         float(decay), tmp.data_ptr(), _C.stream_ptr(dev))
+    _C.check(rc, "occ_ema_update")
+
+
+def binarize(occs: Tensor, occ_thre: float) -> Tensor:
+    """bool tensor occs > min(mean(occs[occs >= 0]), occ_thre) (occ_grid.py:403-404)."""
+    if not occs.is_cuda:
+        thre = torch.clamp(occs[occs >= 0].mean(), max=occ_thre)
+        return occs > thre
+    dev = _C.require_cuda(occs)
+    o = occs.contiguous()
+    out = torch.empty(o.shape, dtype=torch.bool, device=dev)
+    with torch.cuda.device(dev):
+        need = int(_C.lib().nfb_occ_binarize_workspace_bytes())
+        ws = _C.scratch(dev, need, "binarize")
+        rc = _C.lib().nfb_occ_binarize(o.data_ptr(), o.numel(), float(occ_thre), out.data_ptr(), None,
+                                       ws.data_ptr(), ws.numel(), _C.stream_ptr(dev))
+    _C.check(rc, "occ_binarize")
+    return out
+
+
+def compact_samples(masks: Tensor, ray_indices: Tensor, t_starts: Tensor, t_ends: Tensor, n_rays: int):
+    """(ray_indices[masks], t_starts[masks], t_ends[masks]) in one pass and one host sync
+    (the reference: three boolean-mask selects, occ_grid.py:216-220)."""
+    n = masks.numel()
+    dev = _C.require_cuda(masks, ray_indices, t_starts, t_ends)
+    if n == 0:
+        return ray_indices, t_starts, t_ends
+    o_ray, o_ts, o_te = torch.empty_like(ray_indices), torch.empty_like(t_starts), torch.empty_like(t_ends)
+    totals = _pinned_totals(dev)
+    with torch.cuda.device(dev):
+        need = int(_C.lib().nfb_compact_workspace_bytes(n))
+        ws = _C.scratch(dev, need, "compact")
+        rc = _C.lib().nfb_compact_samples(masks.data_ptr(), ray_indices.data_ptr(), t_starts.data_ptr(),
+                                          t_ends.data_ptr(), n, o_ray.data_ptr(), o_ts.data_ptr(),
+                                          o_te.data_ptr(), totals.data_ptr(), ws.data_ptr(), ws.numel(),
+                                          _C.stream_ptr(dev))
+        _C.check(rc, "compact_samples")
+        torch.cuda.current_stream(dev).synchronize()
+    k = int(totals[0])
+    return o_ray[:k], o_ts[:k], o_te[:k]

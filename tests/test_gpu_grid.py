@@ -1,0 +1,289 @@
+"""Grid traversal on the GPU against the CPU oracle: ray_indices, packed_info, counts, masks and
+edge values must be BIT-EXACT (same serial float arithmetic), as north_star demands.
+Scenes follow the reference's tests/test_grid.py plus the cases it does not cover
+(cone_angle > 0, step_size <= 0, zero direction components, chunked over-allocate mode)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _enlarge(aabb, f):
+    c, e = (aabb[:3] + aabb[3:]) / 2, (aabb[3:] - aabb[:3]) / 2
+    return np.concatenate([c - e * f, c + e * f]).astype(np.float32)
+
+
+def _nested_scene(n_rays=200, levels=4, res=32, seed=42, p_occ=0.5):
+    rng = np.random.default_rng(seed)
+    o = rng.standard_normal((n_rays, 3)).astype(np.float32)
+    d = rng.standard_normal((n_rays, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    base = np.array([-1, -1, -1, 1, 1, 1], np.float32)
+    aabbs = np.stack([_enlarge(base, 2**i) for i in range(levels)])
+    bins = rng.random((levels, res, res, res)) < p_occ
+    return o, d.astype(np.float32), bins, aabbs
+
+
+def _shell_scene(n_rays=1 << 13, res=128, seed=1234):
+    """thin spherical shell in a 128^3 grid, rays from radius 4 toward the ball."""
+    rng = np.random.default_rng(seed)
+    lin = (np.arange(res) + 0.5) / res * 3.0 - 1.5
+    X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
+    rad = np.sqrt(X**2 + Y**2 + Z**2)
+    bins = ((rad >= 0.8) & (rad <= 0.9))[None]
+    o = rng.standard_normal((n_rays, 3)); o = 4.0 * o / np.linalg.norm(o, axis=-1, keepdims=True)
+    tgt = rng.standard_normal((n_rays, 3)); tgt = tgt / np.linalg.norm(tgt, axis=-1, keepdims=True)
+    tgt *= 1.5 * rng.random((n_rays, 1)) ** (1 / 3)
+    d = tgt - o; d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    aabbs = np.array([[-1.5, -1.5, -1.5, 1.5, 1.5, 1.5]], np.float32)
+    return o.astype(np.float32), d.astype(np.float32), bins, aabbs
+
+
+def _gpu(device, *arrs):
+    return [None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(device) for a in arrs]
+
+
+def _check_equal(got, ref):
+    for part in ("intervals", "samples"):
+        for k, v in ref[part].items():
+            g = getattr(got[part], k).cpu().numpy()
+            assert g.shape == v.shape, (part, k, g.shape, v.shape)
+            assert (g == v).all(), (part, k, int((g != v).sum()))
+
+
+@pytest.mark.parametrize("kw", [
+    dict(),                                         # reference test_traverse_grids
+    dict(step_size=0.013, cone_angle=0.004),        # cone marching
+    dict(step_size=0.0),                            # one interval per voxel crossing
+    dict(step_size=2e-2, traverse_steps_limit=37),  # per-ray sample cap, two-pass
+])
+def test_traverse_grids_matches_oracle(device, kw):
+    import nerfacc_b200 as nf
+
+    o, d, bins, aabbs = _nested_scene()
+    near = np.random.default_rng(1).random(o.shape[0]).astype(np.float32) * 0.2
+    far = np.full(o.shape[0], 6.0, np.float32)
+    ref = oracle.traverse_grids(o, d, bins, aabbs, near, far, **kw)
+    to, td, tb, ta, tn, tf = _gpu(device, o, d, bins, aabbs, near, far)
+    iv, sm, term = nf.traverse_grids(to, td, tb, ta, near_planes=tn, far_planes=tf, **kw)
+    _check_equal(dict(intervals=iv, samples=sm), ref)
+    has = ref["samples"]["packed_info"][:, 1] > 0  # the reference leaves empty rays undefined
+    assert (term.cpu().numpy()[has] == ref["termination_planes"][has]).all()
+    assert ref["samples"]["vals"].shape[0] > 1000
+
+
+def test_traverse_precomputed_events_and_zero_dirs(device):
+    import nerfacc_b200 as nf
+
+    o, d, bins, aabbs = _nested_scene(n_rays=64, levels=3)
+    d[:8] = np.array([1.0, 0.0, 0.0], np.float32)
+    d[8:16] = np.array([0.0, -1.0, 0.0], np.float32)
+    d[16:20] = np.array([0.0, 0.6, 0.8], np.float32)
+    o[:20] = (np.random.default_rng(3).random((20, 3)) * 1.6 - 0.8).astype(np.float32)
+    ref = oracle.traverse_grids(o, d, bins, aabbs, step_size=5e-3)
+    to, td, tb, ta = _gpu(device, o, d, bins, aabbs)
+    iv, sm, _ = nf.traverse_grids(to, td, tb, ta, step_size=5e-3)
+    _check_equal(dict(intervals=iv, samples=sm), ref)
+    # same events handed in explicitly (the reference's call pattern at examples/utils.py:317-361)
+    tmin, tmax, hits = nf.ray_aabb_intersect(to, td, ta)
+    t_sorted, t_idx = torch.sort(torch.cat([tmin, tmax], -1), dim=-1, stable=True)
+    iv2, sm2, _ = nf.traverse_grids(to, td, tb, ta, step_size=5e-3, t_sorted=t_sorted, t_indices=t_idx, hits=hits)
+    _check_equal(dict(intervals=iv2, samples=sm2), ref)
+
+
+def test_ray_aabb_intersect(device):
+    """Reference tests/test_grid.py:8-35 + bit-exactness against the oracle."""
+    import nerfacc_b200 as nf
+    from nerfacc_b200.grid import _ray_aabb_intersect
+
+    rng = np.random.default_rng(42)
+    o = rng.random((1000, 3)).astype(np.float32)
+    d = rng.standard_normal((1000, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    lo = rng.random((100, 3)).astype(np.float32)
+    bb = np.concatenate([lo, lo + rng.random((100, 3)).astype(np.float32)], -1)
+    to, td, tb = _gpu(device, o, d, bb)
+    tmin, tmax, hits = nf.ray_aabb_intersect(to, td, tb)
+    r0, r1, rh = oracle.ray_aabb_intersect(o, d, bb)
+    assert (hits.cpu().numpy() == rh).all()
+    assert (tmin.cpu().numpy() == r0).all() and (tmax.cpu().numpy() == r1).all()
+    _a, _b, _h = _ray_aabb_intersect(to, td, tb)
+    assert torch.allclose(tmin, _a) and torch.allclose(tmax, _b) and (hits == _h).all()
+    tmin, tmax, hits = nf.ray_aabb_intersect(to, td, tb, near_plane=0.1, far_plane=0.7, miss_value=-1.0)
+    r0, r1, rh = oracle.ray_aabb_intersect(o, d, bb, 0.1, 0.7, -1.0)
+    assert (tmin.cpu().numpy() == r0).all() and (tmax.cpu().numpy() == r1).all()
+
+
+def test_near_far_planes_kat(device):
+    """Reference tests/test_grid.py:135-159 (1x1x1 grid)."""
+    import nerfacc_b200 as nf
+
+    rays_o = torch.tensor([[-1.0, 0.0, 0.0]], device=device)
+    rays_d = torch.tensor([[1.0, 0.01, 0.01]], device=device)
+    rays_d = rays_d / rays_d.norm(dim=-1, keepdim=True)
+    binaries = torch.ones((1, 1, 1, 1), dtype=torch.bool, device=device)
+    aabbs = torch.tensor([[0.0, 0.0, 0.0, 1.0, 1.0, 1.0]], device=device)
+    near, far = torch.tensor([1.2], device=device), torch.tensor([1.5], device=device)
+    iv, sm, _ = nf.traverse_grids(rays_o, rays_d, binaries, aabbs, step_size=0.05, near_planes=near, far_planes=far)
+    assert iv.vals.numel() > 0
+    assert (iv.vals >= (near - 0.025)).all() and (iv.vals <= (far + 0.025)).all()
+    ref = oracle.traverse_grids(rays_o.cpu().numpy(), rays_d.cpu().numpy(), binaries.cpu().numpy(),
+                                aabbs.cpu().numpy(), near.cpu().numpy(), far.cpu().numpy(), step_size=0.05)
+    assert (iv.vals.cpu().numpy() == ref["intervals"]["vals"]).all()
+
+
+def test_chunked_test_mode(device):
+    """Reference tests/test_grid.py:72-131: over-allocated, resumable marching reproduces the
+    one-shot result; every chunk is also bit-exact against the oracle."""
+    import nerfacc_b200 as nf
+
+    o, d, bins, aabbs = _nested_scene(n_rays=10)
+    to, td, tb, ta = _gpu(device, o, d, bins, aabbs)
+    iv, sm, _ = nf.traverse_grids(to, td, tb, ta)
+    one_shot = nf.accumulate_along_rays(iv.vals[iv.is_left], None, sm.ray_indices, 10)
+    acc = torch.zeros_like(one_shot)
+    term, mask, term_np, mask_np = None, None, None, None
+    for _ in range(3):
+        _iv, _sm, term = nf.traverse_grids(to, td, tb, ta, near_planes=term, traverse_steps_limit=4000,
+                                           over_allocate=True, rays_mask=mask)
+        ref = oracle.traverse_grids(o, d, bins, aabbs, near_planes=term_np, traverse_steps_limit=4000,
+                                    over_allocate=True, rays_mask=mask_np)
+        _check_equal(dict(intervals=_iv, samples=_sm), ref)
+        alive = ref["samples"]["packed_info"][:, 1] > 0
+        assert (term.cpu().numpy()[alive] == ref["termination_planes"][alive]).all()
+        mask = _sm.packed_info[:, 1] == 4000
+        mask_np, term_np = mask.cpu().numpy(), term.cpu().numpy()
+        nf.accumulate_along_rays_(_iv.vals[_iv.is_left], None, _sm.ray_indices[_sm.is_valid], acc)
+    assert (~mask).all()
+    assert torch.allclose(acc, one_shot, atol=1e-1)
+
+
+@pytest.mark.parametrize("stratified", [False, True])
+def test_sampling_shell_scene(device, stratified):
+    """cfg2-shaped scene at 2^13 rays: ray_indices / t_starts / t_ends / counts bit-exact."""
+    import nerfacc_b200 as nf
+
+    o, d, bins, aabbs = _shell_scene()
+    est = nf.OccGridEstimator(aabbs[0].tolist(), resolution=128, levels=1).to(device)
+    est.binaries = torch.from_numpy(bins).to(device)
+    to, td = _gpu(device, o, d)
+    if stratified:
+        torch.manual_seed(7)
+        jitter = torch.rand(o.shape[0], device=device)
+        torch.manual_seed(7)
+    ri, ts, te = est.sampling(to, td, render_step_size=5e-3, stratified=stratified)
+    near = None
+    if stratified:
+        near = (torch.zeros(o.shape[0], device=device) + jitter * 5e-3).cpu().numpy()
+    r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, aabbs, render_step_size=5e-3, t_min=near)
+    assert ri.shape[0] == r_ri.shape[0] and ri.shape[0] > 100000
+    assert (ri.cpu().numpy() == r_ri).all()
+    assert (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+    assert (nf.pack_info(ri, o.shape[0]).cpu().numpy() == r_pi).all()
+
+
+def test_sampling_with_min_max_and_visibility(device):
+    """Reference tests/test_grid.py:163-203 plus the sigma_fn visibility filter."""
+    import nerfacc_b200 as nf
+
+    rng = np.random.default_rng(42)
+    n_rays, levels, res = 64, 4, 32
+    o = (rng.random((n_rays, 3)) * 2 - 1).astype(np.float32)
+    d = rng.random((n_rays, 3)).astype(np.float32); d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    bins = rng.random((levels, res, res, res)) > 0.5
+    t_min = rng.random(n_rays).astype(np.float32)
+    t_max = (t_min + rng.random(n_rays)).astype(np.float32)
+    est = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=res, levels=levels).to(device)
+    est.binaries = torch.from_numpy(bins).to(device)
+    to, td, tmn, tmx = _gpu(device, o, d, t_min, t_max)
+    ri, ts, te = est.sampling(to, td, near_plane=0.15, far_plane=0.85, t_min=tmn, t_max=tmx, render_step_size=0.01)
+    assert (ts >= (tmn[ri] - 0.005)).all() and (te <= (tmx[ri] + 0.005)).all()
+    aab = est.aabbs.cpu().numpy()
+    r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, aab, 0.15, 0.85, t_min, t_max, 0.01)
+    assert (ri.cpu().numpy() == r_ri).all() and (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+    # visibility filter: sigma = 30 everywhere -> compare with oracle weights + mask
+    est.occs.fill_(1.0)
+    ri2, ts2, te2 = est.sampling(to, td, sigma_fn=lambda a, b, r: torch.full_like(a, 30.0), near_plane=0.15,
+                                 far_plane=0.85, t_min=tmn, t_max=tmx, render_step_size=0.01,
+                                 early_stop_eps=1e-2, alpha_thre=1e-3)
+    w0, T0, a0 = oracle.render_weight_from_density(r_ts, r_te, np.full_like(r_ts, 30.0), r_pi)
+    keep = oracle.visibility(T0, a0, 1e-2, 1e-3)
+    safe = np.abs(T0 - 1e-2) > 1e-6
+    assert safe.all()
+    assert (ri2.cpu().numpy() == r_ri[keep]).all() and (ts2.cpu().numpy() == r_ts[keep]).all()
+    assert (te2.cpu().numpy() == r_te[keep]).all()
+
+
+def test_mark_invisible_cells(device):
+    """Reference tests/test_grid.py:207-233 (exact counts)."""
+    import nerfacc_b200 as nf
+
+    est = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=32, levels=4).to(device)
+    K = torch.tensor([[[100.0, 0, 50.0], [0, 100.0, 50.0], [0, 0, 1]]], device=device)
+    pose = torch.tensor([[[-1.0, 0.0, 0.0, 0.0], [0.0, 1.0, 0.0, 0.0], [0.0, 0.0, -1.0, 2.5]]], device=device)
+    est.mark_invisible_cells(K, pose, 100, 100)
+    assert (est.occs == -1).sum() == 77660
+    assert (est.occs == 0).sum() == 53412
+
+
+def test_update_every_n_steps(device):
+    """EMA update + binarisation against the oracle, with an occ_eval_fn that is constant per
+    cell (so the reference's last-writer-wins and our scatter-max agree)."""
+    import nerfacc_b200 as nf
+
+    res, levels = 32, 2
+    est = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=res, levels=levels).to(device)
+    est.train()
+    aab = est.aabbs.cpu().numpy()
+
+    def occ_fn(x):  # depends only on which level-0-sized cell x is in
+        cell = torch.floor((x + 2.0) / 4.0 * 64).clamp(0, 63)
+        h = (cell[:, 0] * 7 + cell[:, 1] * 13 + cell[:, 2] * 29) % 17
+        return (h[:, None] / 17.0 * 0.05).float()
+
+    occs = np.zeros(levels * res**3, np.float32)
+    for step in (0, 16, 512, 528):  # warm-up and steady-state sampling both run
+        est.update_every_n_steps(step, occ_fn, occ_thre=0.01, ema_decay=0.95, warmup_steps=256)
+    # warm-up steps touch every cell once: closed form check against the oracle
+    est2 = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=res, levels=levels).to(device)
+    est2.train()
+    torch.manual_seed(5)
+    est2._update(0, occ_fn, occ_thre=0.01, ema_decay=0.95, warmup_steps=256)
+    torch.manual_seed(5)
+    for lvl in range(levels):
+        cells = np.arange(res**3)
+        u = torch.rand((res**3, 3), device=device).cpu().numpy()
+        x = oracle.occ_cell_points(cells, u, [res] * 3, aab[lvl])
+        occ = occ_fn(torch.from_numpy(x).to(device)).squeeze(-1).cpu().numpy()
+        occs = oracle.occ_ema_update(occs, lvl * res**3 + cells, occ, 0.95)
+    bins, thre = oracle.occ_binarize(occs, 0.01)
+    assert np.allclose(est2.occs.cpu().numpy(), occs, rtol=0, atol=0)
+    assert (est2.binaries.cpu().numpy().reshape(-1) == bins).all()
+    assert est.binaries.any() and not est.binaries.all()
+
+
+def test_ema_update_with_duplicates_and_compaction(device):
+    from nerfacc_b200 import _occ_ops
+
+    rng = np.random.default_rng(0)
+    n_cells, n = 5000, 20000
+    occs = rng.random(n_cells).astype(np.float32)
+    occs[rng.random(n_cells) < 0.1] = -1.0
+    ids = rng.integers(0, n_cells, n)
+    occ = rng.random(n).astype(np.float32)
+    t_occs = torch.from_numpy(occs.copy()).to(device)
+    _occ_ops.ema_update(t_occs, torch.from_numpy(ids).to(device), torch.from_numpy(occ).to(device), 0, n, 0.9)
+    ref = oracle.occ_ema_update(occs, ids, occ, 0.9)
+    assert (t_occs.cpu().numpy() == ref).all()
+    b = _occ_ops.binarize(t_occs, 0.5).cpu().numpy()
+    rb, _ = oracle.occ_binarize(ref, 0.5)
+    assert (b == rb).all()
+    # compaction
+    m = 100003
+    mask = rng.random(m) < 0.3
+    ri = np.sort(rng.integers(0, 999, m)); ts = rng.random(m).astype(np.float32); te = ts + 1
+    a, b2, c = _occ_ops.compact_samples(*[torch.from_numpy(x).to(device) for x in (mask, ri, ts, te)], 999)
+    assert (a.cpu().numpy() == ri[mask]).all() and (b2.cpu().numpy() == ts[mask]).all() and (c.cpu().numpy() == te[mask]).all()
