@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py — the hot path's headline benchmark (BASELINE.json metric) on 1..8 B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rays R]
+
+Workload = BASELINE.json configs[1] extended to the metric's "marched + rendered fwd+bwd":
+a synthetic 128^3 occupancy grid (thin spherical shell, NeRF-Synthetic-like bounds
+[-1.5,1.5]^3), R = 2^20 rays per GPU from radius 4 toward the ball, render_step_size 5e-3.
+One step =
+    OccGridEstimator.sampling (two-pass DDA march: count -> scan -> fill)
+ -> rendering(): render_weight_from_density + accumulate_along_rays x3 (rgb, opacity, depth)
+ -> backward to d/d sigmas and d/d rgbs.
+The user's radiance field is excluded: sigmas [S] and rgbs [S,3] are supplied as resident
+tensors (S, the number of marched samples, is the same every step because the rays are).
+
+Numbers on the JSON line
+  value     Gsamples/s over all ranks, inputs resident in HBM, CUDA events, max over ranks
+  e2e       the same step through the public API with the rays in PINNED HOST memory:
+            host->device copy of rays_o/rays_d and device->host copy of colors/opacities/depths
+            inside the timed region
+  roofline  the dominant native kernel, timed live inside the timed region with CUDA events
+            recorded around its C-ABI call; algorithmic bytes per DESIGN.md
+  cpu_baseline  the CPU oracle port (oracle/, OpenMP) on a bounded sample of the same workload
+`--impl reference` times that CPU port alone (the reference has no CPU implementation of the
+packed path) and prints the same line with "impl": "reference".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Gsamples/s marched+rendered fwd+bwd"
+UNIT = "Gsamples/s"
+STEP_SIZE = 5e-3
+RES = 128
+SHELL = (0.8, 0.9)
+AABB = np.array([-1.5, -1.5, -1.5, 1.5, 1.5, 1.5], np.float32)
+
+
+# ------------------------------------------------------------------------------- workload
+def make_grid(res: int = RES) -> np.ndarray:
+    lin = (np.arange(res, dtype=np.float64) + 0.5) / res * 3.0 - 1.5
+    X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
+    rad = np.sqrt(X**2 + Y**2 + Z**2)
+    return ((rad >= SHELL[0]) & (rad <= SHELL[1]))[None]
+
+
+def make_rays(n_rays: int, seed: int):
+    rng = np.random.default_rng(seed)
+    o = rng.standard_normal((n_rays, 3))
+    o = 4.0 * o / np.linalg.norm(o, axis=-1, keepdims=True)
+    tgt = rng.standard_normal((n_rays, 3))
+    tgt = tgt / np.linalg.norm(tgt, axis=-1, keepdims=True) * 1.5 * rng.random((n_rays, 1)) ** (1 / 3)
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    return o.astype(np.float32), d.astype(np.float32)
+
+
+def workload_name(n_rays: int) -> str:
+    return (f"cfg2+render: OccGridEstimator.sampling on synthetic {RES}^3 shell grid, {n_rays} rays/GPU, "
+            f"render_step_size {STEP_SIZE}, then rendering() fwd+bwd (weights from density, rgb/opacity/depth)")
+
+
+# ------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int) -> None:
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------- CPU arm
+def cpu_problem(n_rays: int, seed: int):
+    import oracle
+
+    bins = make_grid()
+    o, d = make_rays(n_rays, seed)
+    ri, ts, te, pi = oracle.sampling(o, d, bins, AABB[None], render_step_size=STEP_SIZE)
+    S = ri.shape[0]
+    rng = np.random.default_rng(seed + 1)
+    sig = (rng.random(S) * 40.0).astype(np.float32)
+    rgb = rng.random((S, 3)).astype(np.float32)
+    g = [rng.random((n_rays, k)).astype(np.float32) for k in (3, 1, 1)]
+    return dict(bins=bins, o=o, d=d, sig=sig, rgb=rgb, g=g, n_rays=n_rays, S=S)
+
+
+def cpu_step(P) -> int:
+    """The same step on the host cores with the CPU oracle port (OpenMP)."""
+    import oracle
+
+    n_rays = P["n_rays"]
+    ri, ts, te, pi = oracle.sampling(P["o"], P["d"], P["bins"], AABB[None], render_step_size=STEP_SIZE)
+    sig, rgb = P["sig"], P["rgb"]
+    w, T, a = oracle.render_weight_from_density(ts, te, sig, pi)
+    tmid = ((ts + te) * 0.5)[:, None]
+    colors = oracle.accumulate_along_rays(w, rgb, ri, n_rays)
+    opac = oracle.accumulate_along_rays(w, None, ri, n_rays)
+    depth = oracle.accumulate_along_rays(w, tmid, ri, n_rays)
+    den = np.maximum(opac, np.finfo(np.float32).eps)
+    g_c, g_o, g_d = P["g"]
+    # depth_out = depth/den: d/d depth = g_d/den, d/d opac += -g_d*depth/den^2 where opac > eps
+    gd_eff = g_d / den
+    go_eff = g_o - np.where(opac > np.finfo(np.float32).eps, g_d * depth / (den * den), 0.0)
+    gw1, g_rgb = oracle.accumulate_along_rays_bwd(g_c, w, rgb, ri)
+    gw2, _ = oracle.accumulate_along_rays_bwd(go_eff.astype(np.float32), w, None, ri)
+    gw3, _ = oracle.accumulate_along_rays_bwd(gd_eff.astype(np.float32), w, tmid, ri)
+    g_sig = oracle.render_weight_from_density_bwd(gw1 + gw2 + gw3, None, None, ts, te, sig, pi)
+    assert g_sig.shape[0] == ri.shape[0] and g_rgb.shape[0] == ri.shape[0] and colors.shape[0] == n_rays
+    return int(ri.shape[0])
+
+
+def time_cpu(n_rays: int, steps: int, warmup: int, seed: int = 1234):
+    import oracle
+
+    P = cpu_problem(n_rays, seed)
+    for _ in range(warmup):
+        cpu_step(P)
+    t0 = time.perf_counter()
+    total = 0
+    for _ in range(steps):
+        total += cpu_step(P)
+    dt = time.perf_counter() - t0
+    return dict(value=total / dt / 1e9, seconds=dt, samples_per_step=P["S"], cores=oracle.num_threads(),
+                n_rays=n_rays, steps=steps)
+
+
+def run_reference(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_rays = args.cpu_rays
+    r = time_cpu(n_rays, args.steps, args.warmup)
+    sample = (f"{n_rays} rays/step of the same scene ({r['samples_per_step']} samples/step), "
+              f"{args.steps} steps after {args.warmup} warm-up, {r['cores']} OpenMP threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["seconds"] / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": workload_name(1 << 20), "cpu_sample_rays": n_rays},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------- GPU arm
+ALGO_BYTES = {
+    # algorithmic bytes per launch: S samples, R rays, B = bitfield bytes
+    "traverse_count": lambda S, R, B: 24 * R + 16 * R + B,
+    "traverse_fill_sampling": lambda S, R, B: 16 * S + 24 * R + 16 * R + B,
+    "render_weight_fwd": lambda S, R, B: 24 * S + 16 * R,
+    "render_weight_bwd": lambda S, R, B: 24 * S + 16 * R,
+    "render_composite_fwd": lambda S, R, B: 44 * S + 16 * R + 20 * R,
+    "render_composite_bwd": lambda S, R, B: 60 * S + 16 * R + 20 * R,
+    "pack_info": lambda S, R, B: 8 * S + 16 * R,
+}
+
+
+def run_ours(args) -> None:
+    import torch
+
+    import nerfacc_b200 as nf
+    from nerfacc_b200 import _C
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); "
+                         "use --impl reference for the CPU port")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+
+    n_rays = args.rays
+    bins = make_grid()
+    o_np, d_np = make_rays(n_rays, 1234 + rank)
+    est = nf.OccGridEstimator(AABB.tolist(), resolution=RES, levels=1).to(dev)
+    est.binaries = torch.from_numpy(bins).to(dev)
+    o_host = torch.from_numpy(o_np).pin_memory()
+    d_host = torch.from_numpy(d_np).pin_memory()
+    o_dev, d_dev = o_host.to(dev), d_host.to(dev)
+
+    ri, ts, te = est.sampling(o_dev, d_dev, render_step_size=STEP_SIZE)
+    S = int(ri.shape[0])
+    gen = torch.Generator(device=dev).manual_seed(4321 + rank)
+    sigmas = (torch.rand(S, device=dev, generator=gen) * 40.0).requires_grad_(True)
+    rgbs = torch.rand((S, 3), device=dev, generator=gen).requires_grad_(True)
+    g_c = torch.rand((n_rays, 3), device=dev, generator=gen)
+    g_o = torch.rand((n_rays, 1), device=dev, generator=gen)
+    g_d = torch.rand((n_rays, 1), device=dev, generator=gen)
+    out_host = torch.empty((n_rays, 5), dtype=torch.float32).pin_memory()
+    del ri, ts, te
+
+    def field(t_starts, t_ends, ray_indices):
+        assert t_starts.shape[0] == S
+        return rgbs, sigmas
+
+    def step(o, d):
+        sigmas.grad = None
+        rgbs.grad = None
+        ri, ts, te = est.sampling(o, d, render_step_size=STEP_SIZE)
+        colors, opac, depth, _ = nf.rendering(ts, te, ri, n_rays, rgb_sigma_fn=field)
+        torch.autograd.backward([colors, opac, depth], [g_c, g_o, g_d])
+        return colors, opac, depth
+
+    def step_e2e():
+        o = o_host.to(dev, non_blocking=True)
+        d = d_host.to(dev, non_blocking=True)
+        colors, opac, depth = step(o, d)
+        out_host[:, 0:3].copy_(colors.detach(), non_blocking=True)
+        out_host[:, 3:4].copy_(opac.detach(), non_blocking=True)
+        out_host[:, 4:5].copy_(depth.detach(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step(o_dev, d_dev)
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    _C.prof_enable(True)
+    launches0 = _C.launch_count()
+    ms = timed(lambda: step(o_dev, d_dev), args.steps)
+    launches = _C.launch_count() - launches0
+    prof = _C.prof_collect()
+    _C.prof_enable(False)
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    clk = clocks.stop() if rank == 0 else None
+
+    S_all = S
+    if dist is not None:
+        t = torch.tensor([S], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        S_all = int(t.item())
+    value = S_all * args.steps / (ms * 1e-3) / 1e9
+    e2e_value = S_all * args.steps / (ms_e2e * 1e-3) / 1e9
+
+    # per-entry-point live timings -> roofline of the dominant kernel
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    B = (bins.size + 7) // 8
+    kernels = {}
+    for name, (cnt, tot_ms) in prof.items():
+        avg = tot_ms / max(cnt, 1)
+        ent = {"launches_per_step": cnt / args.steps, "avg_ms": avg, "share_of_step": tot_ms / ms}
+        if name in ALGO_BYTES:
+            by = ALGO_BYTES[name](S, n_rays, B)
+            ent.update(bytes=by, gbs=by / (avg * 1e-3) / 1e9, frac=by / (avg * 1e-3) / 1e9 / peak)
+        kernels[name] = ent
+    candidates = [k for k in kernels if "bytes" in kernels[k]]
+    dom = max(candidates, key=lambda k: kernels[k]["avg_ms"] * kernels[k]["launches_per_step"]) if candidates else None
+    roofline = None
+    if dom is not None:
+        kd = kernels[dom]
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": kd["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": kd["frac"], "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": kd["bytes"], "avg_launch_ms": kd["avg_ms"]}
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                roofline["traffic"] = json.load(f).get(dom)
+        except Exception:
+            pass
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        r = time_cpu(args.cpu_rays, 3, 1)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+               "sample": f"{args.cpu_rays} rays/step of the same scene ({r['samples_per_step']} samples/step), "
+                         f"3 steps after 1 warm-up, {r['seconds']:.1f} s"}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(n_rays), "rays_per_gpu": n_rays, "samples_per_gpu": S,
+                   "samples_per_ray": S / n_rays, "l2": "inputs larger than L2 (sample stream "
+                   f"{S * 16 / 1e6:.0f} MB march output, {S * 44 / 1e6:.0f} MB render inputs/outputs)",
+                   "parallelism": f"rays sharded x{world}, grid replicated, no data-path collective"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": 2 * n_rays * 12 * world, "d2h_bytes_per_step": n_rays * 20 * world},
+        "gpu_launches": launches,
+        "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu, "clocks": clk,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU")
+    ap.add_argument("--cpu-rays", type=int, default=1 << 16, help="rays per step of the CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

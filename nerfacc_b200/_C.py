@@ -18,7 +18,7 @@ import torch
 
 from . import _build
 
-_LIB: Optional[C.CDLL] = None
+_LIB = None
 _LOCK = threading.Lock()
 
 c_f32p = C.c_void_p
@@ -97,7 +97,7 @@ def declared_symbols():
     return sorted(_PROTOS)
 
 
-def lib() -> C.CDLL:
+def lib():
     """Load (building first if the sources changed and nvcc is present) the CUDA library."""
     global _LIB
     if _LIB is not None:
@@ -122,12 +122,39 @@ def lib() -> C.CDLL:
                 "nerfacc_b200 has no CPU or PyTorch fallback."
             )
         l = C.CDLL(path)
+        proxy = _LibProxy(path)
         for name, argtypes in _PROTOS.items():
             fn = getattr(l, name)
             fn.argtypes = argtypes
             fn.restype = _RESTYPES.get(name, C.c_int)
-        _LIB = l
+            # entry points that launch kernels (they take the stream last) go through a
+            # timer shim so bench.py can measure them live; queries are bound directly
+            launches = name not in _RESTYPES and len(argtypes) > 0
+            setattr(proxy, name, _Timed(name[4:], fn) if launches else fn)
+        _LIB = proxy
     return _LIB
+
+
+class _LibProxy:
+    """Attribute bag holding the typed entry points of libnerfacc_b200.so."""
+
+    def __init__(self, path: str) -> None:
+        self._path = path
+
+
+class _Timed:
+    __slots__ = ("name", "fn")
+
+    def __init__(self, name: str, fn) -> None:
+        self.name, self.fn = name, fn
+
+    def __call__(self, *args):
+        if _PROF is None:
+            return self.fn(*args)
+        t0 = prof_start()
+        rc = self.fn(*args)
+        prof_stop(self.name, t0)
+        return rc
 
 
 def last_error() -> str:
@@ -160,6 +187,46 @@ def require_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
             raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
     assert dev is not None
     return dev
+
+
+# --------------------------------------------------------------------------- kernel timers
+# bench.py measures each native entry point live, inside its timed region, with CUDA events
+# recorded on the launching stream right around the C-ABI call (torch.cuda.Event only sees
+# torch's current stream, which is the stream the kernels are launched on).
+_PROF: Optional[Dict[str, list]] = None
+
+
+def prof_enable(on: bool = True) -> None:
+    global _PROF
+    _PROF = {} if on else None
+
+
+def prof_start():
+    if _PROF is None:
+        return None
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+def prof_stop(name: str, start) -> None:
+    if start is None or _PROF is None:
+        return
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    _PROF.setdefault(name, []).append((start, e))
+
+
+def prof_collect() -> Dict[str, Tuple[int, float]]:
+    """name -> (launches, total milliseconds); synchronises."""
+    out: Dict[str, Tuple[int, float]] = {}
+    if _PROF is None:
+        return out
+    torch.cuda.synchronize()
+    for name, evs in _PROF.items():
+        out[name] = (len(evs), float(sum(a.elapsed_time(b) for a, b in evs)))
+    _PROF.clear()
+    return out
 
 
 def ptr(t: Optional[torch.Tensor]) -> Optional[int]:

@@ -41,10 +41,6 @@ def cell_points(cells: Tensor, u: Tensor, resolution: Tensor, aabb: Tensor) -> T
     """World positions of jittered cell samples (occ_grid.py:385-392)."""
     n = cells.shape[0]
     res = [int(v) for v in resolution.tolist()]
-    if not cells.is_cuda:
-        coords = torch.stack([cells // (res[1] * res[2]), (cells // res[2]) % res[1], cells % res[2]], -1)
-        x = (coords + u) / resolution
-        return aabb[:3] + x * (aabb[3:] - aabb[:3])
     dev = _C.require_cuda(cells, u, aabb)
     x = torch.empty((n, 3), dtype=torch.float32, device=dev)
     if n:
@@ -63,10 +59,6 @@ def ema_update(occs: Tensor, cell_ids: Tensor, occ: Tensor, lo: int, hi: int, de
     n = cell_ids.shape[0]
     if n == 0:
         return
-    if not occs.is_cuda:
-        occs[cell_ids] = occs[cell_ids] * decay
-        occs.scatter_reduce_(0, cell_ids[lo:hi], occ.to(occs.dtype), "amax", include_self=True)
-        return
     dev = _C.require_cuda(occs, cell_ids, occ)
     assert occs.is_contiguous() and occs.dtype == torch.float32
     cell_ids = cell_ids.long().contiguous()
@@ -81,9 +73,6 @@ def ema_update(occs: Tensor, cell_ids: Tensor, occ: Tensor, lo: int, hi: int, de
 
 def binarize(occs: Tensor, occ_thre: float) -> Tensor:
     """bool tensor occs > min(mean(occs[occs >= 0]), occ_thre) (occ_grid.py:403-404)."""
-    if not occs.is_cuda:
-        thre = torch.clamp(occs[occs >= 0].mean(), max=occ_thre)
-        return occs > thre
     dev = _C.require_cuda(occs)
     o = occs.contiguous()
     out = torch.empty(o.shape, dtype=torch.bool, device=dev)
