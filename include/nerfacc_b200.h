@@ -165,6 +165,8 @@ typedef struct nfb_rays {
 
 typedef struct nfb_grid {
     const uint32_t* occ_bits;   /* bit field from nfb_pack_occupancy: [n_grids*rx*ry*rz] bits */
+    const uint32_t* occ_mip;    /* optional "any occupied" mip from nfb_pack_occupancy, or NULL */
+    int32_t mip_shift;          /* one mip bit per (2^mip_shift)^3 block of cells */
     const float* aabbs;         /* [n_grids, 6] */
     int32_t n_grids;            /* <= 8 (MAX_GRID_LEVELS, csrc/grid.cu:18) */
     int32_t res[3];
@@ -182,27 +184,44 @@ NFB_API int nfb_ray_aabb_intersect(const float* rays_o, const float* rays_d, con
                                    float far_plane, float miss_value, float* t_mins,
                                    float* t_maxs, uint8_t* hits, nfb_stream_t stream);
 
-/* binaries: 1 byte per cell (torch.bool) -> bits: ceil(n_cells/32) uint32 words. */
-NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int64_t n_cells, uint32_t* bits,
+/* binaries [n_grids, rx, ry, rz]: 1 byte per cell (torch.bool) -> bits: ceil(n_cells/32) uint32
+ * words, and optionally (mip_bits != NULL) the "any occupied" mip with one bit per
+ * (2^mip_shift)^3 block: ceil(n_grids * prod(ceil(res/2^mip_shift)) / 32) words.  Marching
+ * kernels keep the mip in shared memory (used when it is <= 160 KiB).  `res_host`: HOST int[3]. */
+NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int32_t n_grids, const int32_t* res_host,
+                               uint32_t* bits, uint32_t* mip_bits, int32_t mip_shift,
                                nfb_stream_t stream);
+
+/* Scratch needed by the traversal entry points (per-ray scan status words + ray counters). */
+NFB_API size_t nfb_traverse_scratch_bytes(int64_t n_rays);
 
 /* Pass 1 (csrc/grid.cu:413-438 + data_spec.hpp:90-93): per-ray counts -> complete, canonical
  * packed_info for samples and for interval edges (int64 [n_rays,2] each, interval_info may be
  * NULL), termination planes [n_rays] (may be NULL; defined for every ray), and the grand
- * totals {n_samples, n_edges} written to totals[0..1] (any device-visible memory, e.g. pinned
- * host memory: read it after synchronising the stream).  `scratch`: 16 bytes per 2048 rays. */
+ * totals {n_samples, n_edges, n_rays whose run list overflowed} written to totals[0..2] (any
+ * device-visible memory, e.g. pinned host memory: read it after synchronising the stream).
+ * `scratch`: nfb_traverse_scratch_bytes(n_rays) bytes. */
 NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                const nfb_march_t* march, int64_t* sample_info,
                                int64_t* interval_info, float* termination_planes,
                                int64_t* totals, void* scratch, size_t scratch_bytes,
-                               nfb_stream_t stream);
+                               void* run_buf, size_t run_buf_bytes, nfb_stream_t stream);
+
+/* Optional run buffer (nfb_traverse_run_bytes(n_rays) bytes, 16-byte aligned, contents need
+ * not be initialised).  When step_size > 0 and cone_angle == 0 the marched samples of a ray are
+ * a few arithmetic progressions ("runs": the reference's t += dt recurrence is exactly linear
+ * inside one float binade); pass 1 records them here and nfb_traverse_fill_sampling, given the
+ * same buffer, expands them warp-cooperatively instead of marching a second time. */
+NFB_API size_t nfb_traverse_run_bytes(int64_t n_rays);
 
 /* Pass 2, OccGridEstimator.sampling outputs (estimators/occ_grid.py:174-177): for every sample,
  * in packed order, ray_indices, t_starts (= left edge) and t_ends (= right edge). */
 NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                        const nfb_march_t* march, const int64_t* sample_info,
                                        int64_t* ray_indices, float* t_starts, float* t_ends,
-                                       nfb_stream_t stream);
+                                       const void* run_buf /* or NULL */,
+                                       int64_t n_overflowed /* totals[2] of pass 1; < 0: unknown */,
+                                       void* scratch, size_t scratch_bytes, nfb_stream_t stream);
 
 /* Pass 2, traverse_grids outputs (csrc/grid.cu:445-470): interval edges {vals, ray_indices,
  * is_left, is_right} and samples {vals, ray_indices, is_valid}.

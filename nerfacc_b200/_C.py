@@ -40,7 +40,8 @@ class Rays(C.Structure):
 
 class Grid(C.Structure):
     """nfb_grid_t"""
-    _fields_ = [("occ_bits", c_ptr), ("aabbs", c_ptr), ("n_grids", C.c_int32), ("res", C.c_int32 * 3)]
+    _fields_ = [("occ_bits", c_ptr), ("occ_mip", c_ptr), ("mip_shift", C.c_int32), ("aabbs", c_ptr),
+                ("n_grids", C.c_int32), ("res", C.c_int32 * 3)]
 
 
 class March(C.Structure):
@@ -70,10 +71,13 @@ _PROTOS = {
     "nfb_pack_info": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_ray_aabb_intersect": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_f32, c_f32, c_ptr, c_ptr,
                                c_ptr, c_ptr],
-    "nfb_pack_occupancy": [c_ptr, c_i64, c_ptr, c_ptr],
+    "nfb_pack_occupancy": [c_ptr, C.c_int32, c_ptr, c_ptr, c_ptr, C.c_int32, c_ptr],
+    "nfb_traverse_run_bytes": [c_i64],
     "nfb_traverse_count": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
-                           c_size, c_ptr],
-    "nfb_traverse_fill_sampling": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+                           c_size, c_ptr, c_size, c_ptr],
+    "nfb_traverse_scratch_bytes": [c_i64],
+    "nfb_traverse_fill_sampling": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                   c_i64, c_ptr, c_size, c_ptr],
     "nfb_occ_cell_points": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "nfb_occ_ema_update": [c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_i64, c_f32, c_ptr, c_ptr],
     "nfb_occ_binarize_workspace_bytes": [],
@@ -90,6 +94,8 @@ _RESTYPES = {
     "nfb_workspace_bytes": C.c_size_t,
     "nfb_occ_binarize_workspace_bytes": C.c_size_t,
     "nfb_compact_workspace_bytes": C.c_size_t,
+    "nfb_traverse_run_bytes": C.c_size_t,
+    "nfb_traverse_scratch_bytes": C.c_size_t,
 }
 
 

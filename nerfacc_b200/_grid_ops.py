@@ -3,6 +3,7 @@ nfb_pack_occupancy, nfb_ray_aabb_intersect in include/nerfacc_b200.h)."""
 from __future__ import annotations
 
 import ctypes as C
+import math
 import weakref
 from typing import Dict, Optional, Tuple
 
@@ -11,32 +12,46 @@ from torch import Tensor
 
 from . import _C
 
-_BITS: Dict[int, Tuple[weakref.ref, int, Tensor]] = {}
+_BITS: Dict[int, Tuple[weakref.ref, int, Tensor, Optional[Tensor], int]] = {}
+_MIP_BYTES_MAX = 128 * 1024  # mip kept in shared memory by the marching kernels
 
 
-def occupancy_bits(binaries: Tensor) -> Tensor:
-    """Bit-packed copy of a bool grid [m, rx, ry, rz] (int32 words, 32 cells each), cached per
-    tensor object and in-place version so repeated marches through the same grid pack once."""
+def occupancy_bits(binaries: Tensor) -> Tuple[Tensor, Optional[Tensor], int]:
+    """Bit-packed copy of a bool grid [m, rx, ry, rz] (int32 words, 32 cells each) and its
+    "any occupied" mip (one bit per (2^shift)^3 block, sized to fit shared memory), cached per
+    tensor object and in-place version so repeated marches through the same grid pack once.
+    Returns (bits, mip or None, shift)."""
     key = id(binaries)
     ent = _BITS.get(key)
     if ent is not None and ent[0]() is binaries and ent[1] == binaries._version:
-        return ent[2]
+        return ent[2], ent[3], ent[4]
     dev = _C.require_cuda(binaries)
     b = binaries.contiguous()
     if b.dtype != torch.bool:
         b = b != 0
+    m, res = b.shape[0], [int(v) for v in b.shape[1:]]
     n = b.numel()
     bits = torch.empty(((n + 31) // 32,), dtype=torch.int32, device=dev)
+    mip, shift = None, 0
     if n:
+        for sh in range(1, 9):
+            words = (m * math.prod((r + (1 << sh) - 1) >> sh for r in res) + 31) // 32
+            if words * 4 <= _MIP_BYTES_MAX:
+                shift = sh
+                mip = torch.empty((words,), dtype=torch.int32, device=dev)
+                break
+        res_host = (C.c_int32 * 3)(*res)
         with torch.cuda.device(dev):
-            rc = _C.lib().nfb_pack_occupancy(b.data_ptr(), n, bits.data_ptr(), _C.stream_ptr(dev))
+            rc = _C.lib().nfb_pack_occupancy(b.data_ptr(), m, res_host, bits.data_ptr(),
+                                             None if mip is None else mip.data_ptr(), shift,
+                                             _C.stream_ptr(dev))
         _C.check(rc, "pack_occupancy")
 
     def _drop(_r, key=key):
         _BITS.pop(key, None)
 
-    _BITS[key] = (weakref.ref(binaries, _drop), binaries._version, bits)
-    return bits
+    _BITS[key] = (weakref.ref(binaries, _drop), binaries._version, bits, mip, shift)
+    return bits, mip, shift
 
 
 _PINNED: Dict[int, Tensor] = {}
@@ -46,7 +61,7 @@ def _pinned_totals(dev: torch.device) -> Tensor:
     idx = dev.index if dev.index is not None else torch.cuda.current_device()
     t = _PINNED.get(idx)
     if t is None:
-        t = _PINNED[idx] = torch.zeros(2, dtype=torch.long).pin_memory()
+        t = _PINNED[idx] = torch.zeros(4, dtype=torch.long).pin_memory()
     return t
 
 
@@ -62,8 +77,8 @@ class Marcher:
         self.rays_o, self.rays_d, self.aabbs = f32(rays_o), f32(rays_d), f32(aabbs)
         self.n_rays = self.rays_o.shape[0]
         assert binaries.dim() == 4 and binaries.shape[0] == self.aabbs.shape[0]
-        self.bits = occupancy_bits(binaries)
-        keep = [self.rays_o, self.rays_d, self.aabbs, self.bits]
+        self.bits, self.mip, mip_shift = occupancy_bits(binaries)
+        keep = [self.rays_o, self.rays_d, self.aabbs, self.bits, self.mip]
         r = _C.Rays()
         r.rays_o, r.rays_d = self.rays_o.data_ptr(), self.rays_d.data_ptr()
         r.n_rays = self.n_rays
@@ -86,16 +101,22 @@ class Marcher:
             r.t_sorted, r.t_indices, r.hits = ts.data_ptr(), ti.data_ptr(), hh.data_ptr()
         g = _C.Grid()
         g.occ_bits, g.aabbs, g.n_grids = self.bits.data_ptr(), self.aabbs.data_ptr(), binaries.shape[0]
+        if self.mip is not None:
+            g.occ_mip, g.mip_shift = self.mip.data_ptr(), mip_shift
         g.res[0], g.res[1], g.res[2] = binaries.shape[1], binaries.shape[2], binaries.shape[3]
         self._keep, self.rays, self.grid = keep, r, g
         self.march = _C.March(float(step_size), float(cone_angle), int(limit))
+        self.run_buf: Optional[Tensor] = None
+        self.n_overflowed = -1
 
     def _scratch(self) -> Tensor:
-        return _C.scratch(self.dev, 16 * (self.n_rays // 2048 + 2), "ray")
+        return _C.scratch(self.dev, int(_C.lib().nfb_traverse_scratch_bytes(self.n_rays)), "ray")
 
-    def count(self, want_intervals: bool, want_term: bool):
+    def count(self, want_intervals: bool, want_term: bool, want_runs: bool = False):
         """Pass 1.  Returns (sample_info, interval_info|None, termination|None, n_samples, n_edges);
-        synchronises the stream once to learn the totals (the only host sync of a traversal)."""
+        synchronises the stream once to learn the totals (the only host sync of a traversal).
+        With `want_runs` (constant-dt marching only) the pass also records each ray's sample runs
+        so that fill_sampling() can expand them instead of marching again."""
         dev, n = self.dev, self.n_rays
         sample_info = torch.empty((n, 2), dtype=torch.long, device=dev)
         interval_info = torch.empty((n, 2), dtype=torch.long, device=dev) if want_intervals else None
@@ -103,15 +124,20 @@ class Marcher:
         if n == 0:
             return sample_info, interval_info, term, 0, 0
         totals = _pinned_totals(dev)
+        self.run_buf = None
         with torch.cuda.device(dev):
             sc = self._scratch()
+            if want_runs and self.march.step_size > 0.0 and self.march.cone_angle == 0.0:
+                self.run_buf = _C.scratch(dev, int(_C.lib().nfb_traverse_run_bytes(n)), "runs")
             rc = _C.lib().nfb_traverse_count(
                 C.byref(self.rays), C.byref(self.grid), C.byref(self.march), sample_info.data_ptr(),
                 None if interval_info is None else interval_info.data_ptr(),
                 None if term is None else term.data_ptr(), totals.data_ptr(), sc.data_ptr(),
-                sc.numel(), _C.stream_ptr(dev))
+                sc.numel(), None if self.run_buf is None else self.run_buf.data_ptr(),
+                0 if self.run_buf is None else self.run_buf.numel(), _C.stream_ptr(dev))
             _C.check(rc, "traverse_count")
             torch.cuda.current_stream(dev).synchronize()
+        self.n_overflowed = int(totals[2])
         return sample_info, interval_info, term, int(totals[0]), int(totals[1])
 
     def fill_sampling(self, sample_info: Tensor, n_samples: int):
@@ -121,10 +147,12 @@ class Marcher:
         t_ends = torch.empty((n_samples,), dtype=torch.float32, device=dev)
         if n_samples > 0:
             with torch.cuda.device(dev):
+                sc = self._scratch()
                 rc = _C.lib().nfb_traverse_fill_sampling(
                     C.byref(self.rays), C.byref(self.grid), C.byref(self.march),
                     sample_info.data_ptr(), ray_indices.data_ptr(), t_starts.data_ptr(),
-                    t_ends.data_ptr(), _C.stream_ptr(dev))
+                    t_ends.data_ptr(), None if self.run_buf is None else self.run_buf.data_ptr(),
+                    self.n_overflowed, sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
             _C.check(rc, "traverse_fill_sampling")
         return ray_indices, t_starts, t_ends
 

@@ -5,11 +5,18 @@
 //  * ray/box intersection + event sort are fused into the traversal when the caller does
 //    not pass precomputed t_sorted/t_indices/hits (the reference runs ray_aabb_intersect,
 //    torch.cat and torch.sort with int64 indices first, grid.py:158-162);
-//  * occupancy is a 1-bit/cell field (256 KiB per 128^3 level) instead of 1-byte bools;
+//  * occupancy is a 1-bit/cell field (256 KiB per 128^3 level) plus an "any occupied" mip
+//    that the marching kernels keep in shared memory, instead of 1-byte bools in HBM;
+//  * marching runs on the warp-convergent producer/consumer engine of grid.cuh (persistent
+//    threads, event queue, exact closed-form t += dt recurrence);
 //  * per-ray counts go straight into the int64 packed_info layout and one look-back scan
 //    produces starts and the grand totals (the reference: 2x torch.cumsum + 2x .item());
-//  * OccGridEstimator.sampling gets exactly its API outputs (ray_indices, t_starts, t_ends)
-//    from the fill pass; the wider traverse_grids outputs are a second emission mode.
+//  * with a constant dt pass 1 also records each ray's samples as a few arithmetic
+//    progressions ("runs"), and pass 2 of OccGridEstimator.sampling is a pure,
+//    warp-cooperative expansion of those runs — the grid is marched once, not twice.
+#include <algorithm>
+#include <type_traits>
+
 #include "grid.cuh"
 
 namespace nfb {
@@ -31,77 +38,68 @@ struct RayArgs {
     long long n_rays;
 };
 
-__device__ __forceinline__ void load_ray(const RayArgs& A, const GridSpec& G, long long r,
-                                         float (&o)[3], float (&d)[3], float& near, float& far,
-                                         RayEvents& ev) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) { o[k] = __ldg(A.rays_o + 3 * r + k); d[k] = __ldg(A.rays_d + 3 * r + k); }
-    near = A.near_arr ? __ldg(A.near_arr + r) : A.near_s;
-    far = A.far_arr ? __ldg(A.far_arr + r) : A.far_s;
-    const int m = G.n_grids;
-    if (A.t_sorted != nullptr) {
-        ev.hit_mask = 0;
-        for (int l = 0; l < m; ++l)
-            if (A.hits[r * m + l]) ev.hit_mask |= (1u << l);
-        for (int i = 0; i < 2 * m; ++i) {
-            ev.t[i] = __ldg(A.t_sorted + r * 2 * m + i);
-            ev.idx[i] = (int8_t)__ldg(A.t_indices + r * 2 * m + i);
-        }
-    } else {
-        float inv[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) inv[k] = __fdiv_rn(1.0f, d[k]);
-        compute_events(o, inv, G, ev);
-    }
-}
-
-struct CountEmit {
-    __device__ __forceinline__ void operator()(float, float, bool, int, int) const {}
+// ---------------------------------------------------------------------------------- sinks
+struct CountSink {
+    __device__ __forceinline__ void run(float, float, int, bool, int, int) const {}
+    __device__ __forceinline__ void one(float, float, bool, int, int) const {}
 };
 
-// Pass 1: counts (into packed_info[2r+1]) and termination planes.
-__global__ void __launch_bounds__(256)
-traverse_count_kernel(const RayArgs A, const GridSpec G, const MarchOpts opt,
-                      int64_t* __restrict__ sample_info, int64_t* __restrict__ interval_info,
-                      float* __restrict__ term) {
-    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < A.n_rays;
-         r += (long long)gridDim.x * blockDim.x) {
-        float o[3], d[3], near, far;
-        RayEvents ev;
-        int nS = 0, nI = 0;
-        float tt;
-        if (A.rays_mask != nullptr && !A.rays_mask[r]) {
-            tt = A.near_arr ? A.near_arr[r] : A.near_s;
-        } else {
-            load_ray(A, G, r, o, d, near, far, ev);
-            CountEmit e;
-            march_ray(o, d, near, far, G, ev, opt, e, nS, nI, tt);
-        }
-        if (sample_info) sample_info[2 * r + 1] = nS;
-        if (interval_info) interval_info[2 * r + 1] = nI;
-        if (term) term[r] = tt;
-    }
-}
+// Run buffer written by the count pass when marching with a constant dt (cone_angle == 0,
+// step_size > 0): per ray up to kRunSlots runs (t0, q, n, s0) — n samples whose edges are
+// t0 + j*q, the first of them sample s0 of the ray — followed by one int32 run count per ray
+// (> kRunSlots: the ray overflowed and is re-marched by the fill pass).  Only the slots in use
+// are ever touched, so the traffic is ~2 sectors per ray, not the reserved 128 bytes.
+constexpr int kRunSlots = 8;
+struct __align__(16) Run { float t0, q; int n, s0; };
 
-struct SamplingEmit {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177)
+struct RunSink {
+    Run* __restrict__ slots;
+    Run cur;
+    int idx;
+    bool have;
+    __device__ __forceinline__ void flush() {
+        if (have) {
+            if (idx < kRunSlots) *reinterpret_cast<int4*>(slots + idx) = *reinterpret_cast<const int4*>(&cur);
+            ++idx;
+            have = false;
+        }
+    }
+    __device__ __forceinline__ void run(float t0, float q, int k, bool, int nS, int) {
+        // consecutive pieces of one arithmetic progression merge
+        if (have && q == cur.q && nS == cur.s0 + cur.n && t0 == __fmaf_rn((float)cur.n, cur.q, cur.t0)) {
+            cur.n += k;
+            return;
+        }
+        flush();
+        cur.t0 = t0; cur.q = q; cur.n = k; cur.s0 = nS;
+        have = true;
+    }
+    __device__ __forceinline__ void one(float, float, bool, int, int) { idx = kRunSlots + 1; }
+};
+
+struct SamplingSink {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177), one lane per ray
     int64_t* __restrict__ ray_indices;
     float* __restrict__ t_starts;
     float* __restrict__ t_ends;
     long long base, r;
-    __device__ __forceinline__ void operator()(float t_last, float t_next, bool, int nS, int) const {
+    __device__ __forceinline__ void one(float t_last, float t_next, bool, int nS, int) const {
         const long long i = base + nS;
         ray_indices[i] = r;
         t_starts[i] = t_last;
         t_ends[i] = t_next;
     }
+    __device__ __forceinline__ void run(float t0, float q, int k, bool, int nS, int) const {
+        for (int j = 0; j < k; ++j)
+            one(__fmaf_rn((float)j, q, t0), __fmaf_rn((float)(j + 1), q, t0), true, nS + j, 0);
+    }
 };
 
-struct FullEmit {  // traverse_grids outputs (grid.cu:218-255)
+struct FullSink {  // traverse_grids outputs (grid.cu:218-255)
     float* __restrict__ iv_vals; int64_t* __restrict__ iv_ray;
     uint8_t* __restrict__ iv_left; uint8_t* __restrict__ iv_right;
     float* __restrict__ sm_vals; int64_t* __restrict__ sm_ray; uint8_t* __restrict__ sm_valid;
     long long iv_base, sm_base, r;
-    __device__ __forceinline__ void operator()(float t_last, float t_next, bool continuous, int nS, int nI) const {
+    __device__ __forceinline__ void one(float t_last, float t_next, bool continuous, int nS, int nI) const {
         long long e = iv_base + nI;
         if (!continuous) {
             iv_vals[e] = t_last; iv_ray[e] = r; iv_left[e] = 1; iv_right[e] = 0;
@@ -115,50 +113,150 @@ struct FullEmit {  // traverse_grids outputs (grid.cu:218-255)
         sm_ray[s] = r;
         sm_valid[s] = 1;
     }
+    __device__ __forceinline__ void run(float t0, float q, int k, bool continuous, int nS, int nI) const {
+        for (int j = 0; j < k; ++j) {
+            one(__fmaf_rn((float)j, q, t0), __fmaf_rn((float)(j + 1), q, t0), continuous, nS + j, nI);
+            nI += continuous ? 1 : 2;
+            continuous = true;
+        }
+    }
 };
 
-struct FillArgs {
+// ---------------------------------------------------------------------------------- policies
+// Pass 1: counts (into packed_info[2r+1]), termination planes and, optionally, the run buffer.
+template <bool RUNS>
+struct CountPolicy {
+    using Sink = typename std::conditional<RUNS, RunSink, CountSink>::type;
+    int64_t* __restrict__ sample_info;
+    int64_t* __restrict__ interval_info;
+    float* __restrict__ term;
+    Run* __restrict__ runs;
+    int* __restrict__ n_runs;
+    unsigned long long* __restrict__ n_overflow;
+    __device__ __forceinline__ bool accept(long long) const { return true; }
+    __device__ __forceinline__ void skipped(long long) const {}
+    __device__ __forceinline__ Sink begin(long long r) const {
+        Sink s;
+        if constexpr (RUNS) { s.slots = runs + r * kRunSlots; s.idx = 0; s.have = false; }
+        return s;
+    }
+    __device__ __forceinline__ void end(long long r, Sink& s, int nS, int nI, float t_last) const {
+        if (sample_info) sample_info[2 * r + 1] = nS;
+        if (interval_info) interval_info[2 * r + 1] = nI;
+        if (term) term[r] = t_last;
+        if constexpr (RUNS) {
+            s.flush();
+            n_runs[r] = s.idx;
+            if (s.idx > kRunSlots) atomicAdd(n_overflow, 1ull);
+        }
+    }
+};
+
+template <bool FULL>
+struct FillPolicy {
+    using Sink = typename std::conditional<FULL, FullSink, SamplingSink>::type;
+    const uint8_t* __restrict__ rays_mask;  // honoured in single-pass mode only (grid.cu:380)
+    const float* __restrict__ near_arr; float near_s;
     // where each ray's data starts: info[r * stride]; packed_info (stride 2) or a plain array
     const int64_t* sm_starts; int sm_stride;
     const int64_t* iv_starts; int iv_stride;
     // two-pass: skip rays whose count (info[2r+1]) is zero; single pass: write the counts
     int64_t* sample_info; int64_t* interval_info; bool single_pass;
     float* term;
-    SamplingEmit se; FullEmit fe; bool full;
+    const int* __restrict__ only_overflowed;  // n_runs of the count pass: march overflowed rays only
+    Sink proto;
+    __device__ __forceinline__ bool masked(long long r) const { return rays_mask != nullptr && !rays_mask[r]; }
+    __device__ __forceinline__ bool accept(long long r) const {
+        if (masked(r)) return false;
+        if (!single_pass && sample_info[2 * r + 1] == 0) return false;  // grid.cu:103-106
+        if (only_overflowed != nullptr && only_overflowed[r] <= kRunSlots) return false;
+        return true;
+    }
+    __device__ __forceinline__ void skipped(long long r) const {
+        if (single_pass && masked(r)) {
+            if (sample_info) sample_info[2 * r + 1] = 0;
+            if (interval_info) interval_info[2 * r + 1] = 0;
+            if (term) term[r] = near_arr ? near_arr[r] : near_s;
+        }
+    }
+    __device__ __forceinline__ Sink begin(long long r) const {
+        Sink s = proto;
+        s.r = r;
+        if constexpr (FULL) { s.sm_base = sm_starts[r * sm_stride]; s.iv_base = iv_starts[r * iv_stride]; }
+        else s.base = sm_starts[r * sm_stride];
+        return s;
+    }
+    __device__ __forceinline__ void end(long long r, Sink&, int nS, int nI, float t_last) const {
+        if (single_pass) {
+            if (sample_info) sample_info[2 * r + 1] = nS;
+            if (interval_info) interval_info[2 * r + 1] = nI;
+        }
+        if (term) term[r] = t_last;
+    }
 };
 
-__global__ void __launch_bounds__(256)
-traverse_fill_kernel(const RayArgs A, const GridSpec G, const MarchOpts opt, const FillArgs F) {
-    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < A.n_rays;
-         r += (long long)gridDim.x * blockDim.x) {
-        if (A.rays_mask != nullptr && !A.rays_mask[r]) {
-            if (F.single_pass) {
-                if (F.sample_info) F.sample_info[2 * r + 1] = 0;
-                if (F.interval_info) F.interval_info[2 * r + 1] = 0;
-                if (F.term) F.term[r] = A.near_arr ? A.near_arr[r] : A.near_s;
+// ---------------------------------------------------------------------------------- kernels
+// Persistent CTAs: dynamic shared memory = [mip words][event queue kQ x blockDim floats].
+constexpr int kMarchThreads = 512;
+
+template <class Policy>
+__global__ void __launch_bounds__(kMarchThreads, 1)
+march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
+             unsigned long long* ray_counter) {
+    extern __shared__ uint32_t s_dyn[];
+    const GridSpec G = stage_mip(Gp, s_dyn);
+    float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
+    march_engine(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
+                 A.hits, A.n_rays, G, opt, P, s_evt, ray_counter);
+}
+
+// Pass 2 of OccGridEstimator.sampling when pass 1 left a run buffer: no marching at all.
+// One warp owns 32 consecutive rays, whose samples are one contiguous stretch of the packed
+// output.  Each lane stages its ray's runs in shared memory; then the whole warp expands run
+// after run — lane j of the warp writes sample j, j+32, ... of the run — so ray_indices /
+// t_starts / t_ends are written as contiguous warp stores instead of 32 scattered scalars.
+// Rays whose run list overflowed are left to a march_kernel launch restricted to them.
+constexpr int kExpandWarps = 8;
+__global__ void __launch_bounds__(kExpandWarps * 32)
+traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info,
+                       const Run* __restrict__ runs, const int* __restrict__ n_runs,
+                       int64_t* __restrict__ ray_indices, float* __restrict__ t_starts,
+                       float* __restrict__ t_ends) {
+    __shared__ Run s_runs[kExpandWarps][32][kRunSlots];
+    const int lane = lane_id(), w = warp_id();
+    const long long n_groups = (n_rays + 31) >> 5;
+    for (long long g = (long long)blockIdx.x * kExpandWarps + w; g < n_groups;
+         g += (long long)gridDim.x * kExpandWarps) {
+        const long long r = g * 32 + lane;
+        long long base = 0;
+        int nr = 0;
+        if (r < n_rays) {
+            base = load_chunk(sample_info, r).start;
+            nr = __ldg(n_runs + r);
+        }
+        const int mine = nr <= kRunSlots ? nr : 0;
+        for (int s = 0; s < mine; ++s)
+            *reinterpret_cast<int4*>(&s_runs[w][lane][s]) =
+                __ldg(reinterpret_cast<const int4*>(runs + r * kRunSlots + s));
+        __syncwarp();
+        unsigned todo = __ballot_sync(kFull, mine > 0);
+        while (todo) {
+            const int b = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int nb = __shfl_sync(kFull, mine, b);
+            const long long base_b = __shfl_sync(kFull, base, b);
+            const long long rb = g * 32 + b;
+            for (int s = 0; s < nb; ++s) {
+                const Run run = s_runs[w][b][s];
+                long long i = base_b + run.s0 + lane;
+                for (int j = lane; j < run.n; j += 32, i += 32) {
+                    ray_indices[i] = rb;
+                    t_starts[i] = __fmaf_rn((float)j, run.q, run.t0);
+                    t_ends[i] = __fmaf_rn((float)(j + 1), run.q, run.t0);
+                }
             }
-            continue;
         }
-        if (!F.single_pass && F.sample_info[2 * r + 1] == 0) continue;  // grid.cu:103-106
-        float o[3], d[3], near, far;
-        RayEvents ev;
-        load_ray(A, G, r, o, d, near, far, ev);
-        int nS = 0, nI = 0;
-        float tt;
-        if (F.full) {
-            FullEmit e = F.fe;
-            e.r = r; e.sm_base = F.sm_starts[r * F.sm_stride]; e.iv_base = F.iv_starts[r * F.iv_stride];
-            march_ray(o, d, near, far, G, ev, opt, e, nS, nI, tt);
-        } else {
-            SamplingEmit e = F.se;
-            e.r = r; e.base = F.sm_starts[r * F.sm_stride];
-            march_ray(o, d, near, far, G, ev, opt, e, nS, nI, tt);
-        }
-        if (F.single_pass) {
-            if (F.sample_info) F.sample_info[2 * r + 1] = nS;
-            if (F.interval_info) F.interval_info[2 * r + 1] = nI;
-        }
-        if (F.term) F.term[r] = tt;
+        __syncwarp();
     }
 }
 
@@ -197,6 +295,30 @@ __global__ void pack_bits_kernel(const uint8_t* __restrict__ binaries, long long
     }
 }
 
+// "any occupied" mip: one thread per coarse cell ORs its (2^shift)^3 fine cells
+__global__ void pack_mip_kernel(const uint8_t* __restrict__ binaries, int n_grids, int rx, int ry, int rz,
+                                int shift, int mx, int my, int mz, uint32_t* __restrict__ mip) {
+    const long long n_coarse = (long long)n_grids * mx * my * mz;
+    const long long n_words = (n_coarse + 31) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int B = 1 << shift;
+    for (long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_words;
+         w += ((long long)gridDim.x * blockDim.x) >> 5) {
+        const long long c = w * 32 + lane;
+        bool on = false;
+        if (c < n_coarse) {
+            const int cz = (int)(c % mz), cy = (int)((c / mz) % my), cx = (int)((c / ((long long)mz * my)) % mx);
+            const int l = (int)(c / ((long long)mz * my * mx));
+            for (int i = cx * B; i < min(cx * B + B, rx) && !on; ++i)
+                for (int j = cy * B; j < min(cy * B + B, ry) && !on; ++j)
+                    for (int k = cz * B; k < min(cz * B + B, rz); ++k)
+                        if (binaries[(((long long)l * rx + i) * ry + j) * rz + k]) { on = true; break; }
+        }
+        const unsigned m = __ballot_sync(kFull, on);
+        if (lane == 0) mip[w] = m;
+    }
+}
+
 static inline unsigned grid_for(long long n, int block, int per_sm = 16) {
     long long b = ceil_div<long long>(n, block);
     const long long cap = (long long)sm_count() * per_sm;
@@ -208,6 +330,34 @@ static inline unsigned grid_for(long long n, int block, int per_sm = 16) {
 }  // namespace nfb
 
 namespace nfb {
+constexpr long long kMaxMipBytes = 128 * 1024;
+constexpr size_t kCounterBytes = 64;  // ray counter + overflow counter, at the end of `scratch`
+
+// Persistent launch: one CTA per SM (the engine is register-heavy), dynamic shared memory
+// for the mip and the event queue; zeroes the ray counter first.
+template <class Policy>
+static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& opt, const Policy& P,
+                        unsigned long long* counter, cudaStream_t s) {
+    const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float);
+    auto kernel = march_kernel<Policy>;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+        set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
+        return NFB_ERR_CUDA;
+    }
+    if (cudaMemsetAsync(counter, 0, sizeof(unsigned long long), s) != cudaSuccess) {
+        set_error("ray counter memset failed");
+        return NFB_ERR_CUDA;
+    }
+    long long b = ceil_div<long long>(A.n_rays, kMarchThreads);
+    const long long cap = (long long)sm_count();
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    kernel<<<(unsigned)b, kMarchThreads, smem, s>>>(A, G, opt, P, counter);
+    count_launch();
+    NFB_CHECK_LAUNCH("march_kernel");
+    return NFB_OK;
+}
+
 static int check_common(const nfb_rays_t* rays, const nfb_grid_t* grid, const nfb_march_t* march) {
     NFB_CHECK_ARG(rays && grid && march, "null descriptor");
     NFB_CHECK_ARG(rays->n_rays >= 0, "negative n_rays");
@@ -232,14 +382,30 @@ static GridSpec to_grid(const nfb_grid_t* g) {
     G.occ_bits = g->occ_bits; G.aabbs = g->aabbs; G.n_grids = g->n_grids;
     G.res[0] = g->res[0]; G.res[1] = g->res[1]; G.res[2] = g->res[2];
     G.cells_per_level = (long long)g->res[0] * g->res[1] * g->res[2];
+    G.mip = nullptr; G.mip_shift = 0; G.mres[0] = G.mres[1] = G.mres[2] = 0;
+    G.mip_cells_per_level = 0; G.mip_words = 0;
+    if (g->occ_mip != nullptr && g->mip_shift > 0) {
+        const int sh = g->mip_shift;
+        long long mc = 1;
+        for (int k = 0; k < 3; ++k) { G.mres[k] = (g->res[k] + (1 << sh) - 1) >> sh; mc *= G.mres[k]; }
+        const long long words = (mc * g->n_grids + 31) / 32;
+        if (words * 4 <= kMaxMipBytes) {
+            G.mip = g->occ_mip; G.mip_shift = sh; G.mip_cells_per_level = (int)mc; G.mip_words = (int)words;
+        }
+    }
     return G;
 }
 static MarchOpts to_opts(const nfb_march_t* m) { return MarchOpts{m->step_size, m->cone_angle, m->traverse_steps_limit}; }
 
+static unsigned long long* counters_of(void* scratch, size_t scratch_bytes, long long n_rays) {
+    const size_t need = nfb_traverse_scratch_bytes(n_rays);
+    if (scratch == nullptr || scratch_bytes < need) return nullptr;
+    return reinterpret_cast<unsigned long long*>(static_cast<char*>(scratch) + need - kCounterBytes);
+}
+
 static int scan_both(int64_t* sample_info, int64_t* interval_info, long long n_rays, int64_t* totals,
-                     void* scratch, size_t scratch_bytes, cudaStream_t s) {
-    const size_t one = ray_scan_status_bytes(n_rays);
-    NFB_CHECK_ARG(scratch != nullptr && scratch_bytes >= 2 * one, "scratch too small");
+                     void* scratch, cudaStream_t s) {
+    const size_t one = (ray_scan_status_bytes(n_rays) + 63) & ~(size_t)63;
     int rc = launch_ray_scan(sample_info, n_rays, reinterpret_cast<long long*>(totals), scratch, s);
     if (rc != NFB_OK) return rc;
     if (interval_info != nullptr)
@@ -250,6 +416,11 @@ static int scan_both(int64_t* sample_info, int64_t* interval_info, long long n_r
 }  // namespace nfb
 
 extern "C" {
+
+NFB_API size_t nfb_traverse_scratch_bytes(int64_t n_rays) {
+    const size_t one = (nfb::ray_scan_status_bytes(n_rays) + 63) & ~(size_t)63;
+    return 2 * one + nfb::kCounterBytes;
+}
 
 NFB_API int nfb_ray_aabb_intersect(const float* rays_o, const float* rays_d, const float* aabbs,
                                    int64_t n_rays, int64_t n_aabbs, float near_plane,
@@ -266,61 +437,114 @@ NFB_API int nfb_ray_aabb_intersect(const float* rays_o, const float* rays_d, con
     return NFB_OK;
 }
 
-NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int64_t n_cells, uint32_t* bits,
+NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int32_t n_grids, const int32_t* res_host,
+                               uint32_t* bits, uint32_t* mip_bits, int32_t mip_shift,
                                nfb_stream_t stream) {
     using namespace nfb;
-    NFB_CHECK_ARG(n_cells >= 0, "negative size");
+    NFB_CHECK_ARG(n_grids >= 0 && res_host != nullptr, "bad grid shape");
+    const long long n_cells = (long long)n_grids * res_host[0] * res_host[1] * res_host[2];
     if (n_cells == 0) return NFB_OK;
     NFB_CHECK_ARG(binaries && bits, "null pointer");
-    pack_bits_kernel<<<grid_for(n_cells, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(binaries, n_cells, bits);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    pack_bits_kernel<<<grid_for(n_cells, 256), 256, 0, s>>>(binaries, n_cells, bits);
     count_launch();
+    if (mip_bits != nullptr) {
+        NFB_CHECK_ARG(mip_shift >= 1 && mip_shift <= 8, "mip_shift must be in [1, 8]");
+        const int B = 1 << mip_shift;
+        const int mx = (res_host[0] + B - 1) / B, my = (res_host[1] + B - 1) / B, mz = (res_host[2] + B - 1) / B;
+        pack_mip_kernel<<<grid_for((long long)n_grids * mx * my * mz, 256), 256, 0, s>>>(
+            binaries, n_grids, res_host[0], res_host[1], res_host[2], mip_shift, mx, my, mz, mip_bits);
+        count_launch();
+    }
     NFB_CHECK_LAUNCH("pack_occupancy");
     return NFB_OK;
+}
+
+NFB_API size_t nfb_traverse_run_bytes(int64_t n_rays) {
+    const size_t n = (size_t)(n_rays > 0 ? n_rays : 0);
+    return n * nfb::kRunSlots * sizeof(nfb::Run) + n * sizeof(int) + 16;
 }
 
 NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                const nfb_march_t* march, int64_t* sample_info,
                                int64_t* interval_info, float* termination_planes,
                                int64_t* totals, void* scratch, size_t scratch_bytes,
-                               nfb_stream_t stream) {
+                               void* run_buf, size_t run_buf_bytes, nfb_stream_t stream) {
     using namespace nfb;
     int rc = check_common(rays, grid, march);
     if (rc != NFB_OK) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (rays->n_rays == 0) {
-        if (totals) cudaMemsetAsync(totals, 0, 2 * sizeof(int64_t), s);
+        if (totals) cudaMemsetAsync(totals, 0, 3 * sizeof(int64_t), s);
         return NFB_OK;
     }
     NFB_CHECK_ARG(sample_info != nullptr, "null sample_info");
+    unsigned long long* counters = counters_of(scratch, scratch_bytes, rays->n_rays);
+    NFB_CHECK_ARG(counters != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
     RayArgs A = to_args(rays);
     A.rays_mask = nullptr;  // the two-pass path ignores rays_mask (grid.cu:418,450)
-    traverse_count_kernel<<<grid_for(rays->n_rays, 256, 64), 256, 0, s>>>(
-        A, to_grid(grid), to_opts(march), sample_info, interval_info, termination_planes);
-    count_launch();
-    NFB_CHECK_LAUNCH("traverse_count");
-    return scan_both(sample_info, interval_info, rays->n_rays, totals, scratch, scratch_bytes, s);
+    const GridSpec G = to_grid(grid);
+    const bool want_runs = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle == 0.0f;
+    if (want_runs) {
+        NFB_CHECK_ARG(run_buf_bytes >= nfb_traverse_run_bytes(rays->n_rays), "run buffer too small");
+        NFB_CHECK_ARG(aligned16(run_buf), "run buffer must be 16-byte aligned");
+        CountPolicy<true> P;
+        P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
+        P.runs = static_cast<Run*>(run_buf);
+        P.n_runs = reinterpret_cast<int*>(P.runs + rays->n_rays * kRunSlots);
+        P.n_overflow = counters + 1;
+        cudaMemsetAsync(counters + 1, 0, sizeof(unsigned long long), s);
+        rc = launch_march(A, G, to_opts(march), P, counters, s);
+    } else {
+        CountPolicy<false> P;
+        P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
+        P.runs = nullptr; P.n_runs = nullptr; P.n_overflow = nullptr;
+        cudaMemsetAsync(counters + 1, 0, sizeof(unsigned long long), s);
+        rc = launch_march(A, G, to_opts(march), P, counters, s);
+    }
+    if (rc != NFB_OK) return rc;
+    rc = scan_both(sample_info, interval_info, rays->n_rays, totals, scratch, s);
+    if (rc != NFB_OK) return rc;
+    if (totals != nullptr)
+        cudaMemcpyAsync(totals + 2, counters + 1, sizeof(int64_t), cudaMemcpyDefault, s);
+    return NFB_OK;
 }
 
 NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                        const nfb_march_t* march, const int64_t* sample_info,
                                        int64_t* ray_indices, float* t_starts, float* t_ends,
-                                       nfb_stream_t stream) {
+                                       const void* run_buf, int64_t n_overflowed, void* scratch,
+                                       size_t scratch_bytes, nfb_stream_t stream) {
     using namespace nfb;
     int rc = check_common(rays, grid, march);
     if (rc != NFB_OK) return rc;
     if (rays->n_rays == 0) return NFB_OK;
     NFB_CHECK_ARG(sample_info != nullptr, "null sample_info");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
     RayArgs A = to_args(rays);
     A.rays_mask = nullptr;
-    FillArgs F{};
-    F.sm_starts = sample_info; F.sm_stride = 2;
-    F.sample_info = const_cast<int64_t*>(sample_info); F.single_pass = false; F.full = false;
-    F.se.ray_indices = ray_indices; F.se.t_starts = t_starts; F.se.t_ends = t_ends;
-    traverse_fill_kernel<<<grid_for(rays->n_rays, 256, 64), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        A, to_grid(grid), to_opts(march), F);
-    count_launch();
-    NFB_CHECK_LAUNCH("traverse_fill_sampling");
-    return NFB_OK;
+    const bool expand = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle == 0.0f;
+    const int* n_runs = nullptr;
+    if (expand) {
+        NFB_CHECK_ARG(aligned16(run_buf) && aligned16(sample_info), "run buffer / sample_info must be 16-byte aligned");
+        const Run* runs = static_cast<const Run*>(run_buf);
+        n_runs = reinterpret_cast<const int*>(runs + rays->n_rays * kRunSlots);
+        const long long groups = (rays->n_rays + 31) / 32;
+        traverse_expand_kernel<<<grid_for(groups, kExpandWarps, 8), kExpandWarps * 32, 0, s>>>(
+            rays->n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends);
+        count_launch();
+        NFB_CHECK_LAUNCH("traverse_expand");
+        if (n_overflowed == 0) return NFB_OK;
+    }
+    unsigned long long* counters = counters_of(scratch, scratch_bytes, rays->n_rays);
+    NFB_CHECK_ARG(counters != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
+    FillPolicy<false> P{};
+    P.rays_mask = nullptr; P.near_arr = A.near_arr; P.near_s = A.near_s;
+    P.sm_starts = sample_info; P.sm_stride = 2;
+    P.sample_info = const_cast<int64_t*>(sample_info); P.interval_info = nullptr; P.single_pass = false;
+    P.term = nullptr; P.only_overflowed = n_runs;
+    P.proto.ray_indices = ray_indices; P.proto.t_starts = t_starts; P.proto.t_ends = t_ends;
+    return launch_march(A, to_grid(grid), to_opts(march), P, counters, s);
 }
 
 NFB_API int nfb_traverse_fill(const nfb_rays_t* rays, const nfb_grid_t* grid,
@@ -337,30 +561,37 @@ NFB_API int nfb_traverse_fill(const nfb_rays_t* rays, const nfb_grid_t* grid,
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (rays->n_rays == 0) return NFB_OK;
     NFB_CHECK_ARG(sample_info && interval_info, "null packed_info");
+    unsigned long long* counters = counters_of(scratch, scratch_bytes, rays->n_rays);
+    NFB_CHECK_ARG(counters != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
     RayArgs A = to_args(rays);
-    FillArgs F{};
-    F.full = true;
-    F.sample_info = sample_info; F.interval_info = interval_info; F.term = termination_planes;
-    F.fe.iv_vals = iv_vals; F.fe.iv_ray = iv_ray_indices; F.fe.iv_left = iv_is_left; F.fe.iv_right = iv_is_right;
-    F.fe.sm_vals = sm_vals; F.fe.sm_ray = sm_ray_indices; F.fe.sm_valid = sm_is_valid;
+    FillPolicy<true> P{};
+    P.near_arr = A.near_arr; P.near_s = A.near_s;
+    P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
+    P.only_overflowed = nullptr;
+    P.proto.iv_vals = iv_vals; P.proto.iv_ray = iv_ray_indices; P.proto.iv_left = iv_is_left; P.proto.iv_right = iv_is_right;
+    P.proto.sm_vals = sm_vals; P.proto.sm_ray = sm_ray_indices; P.proto.sm_valid = sm_is_valid;
     if (over_allocate) {
         NFB_CHECK_ARG(march->traverse_steps_limit > 0, "traverse_steps_limit must be > 0 when over_allocate is true");
         NFB_CHECK_ARG(sample_starts && interval_starts, "over_allocate needs the allocated starts");
-        F.single_pass = true;
-        F.sm_starts = sample_starts; F.sm_stride = 1;
-        F.iv_starts = interval_starts; F.iv_stride = 1;
+        P.rays_mask = A.rays_mask;
+        P.single_pass = true;
+        P.sm_starts = sample_starts; P.sm_stride = 1;
+        P.iv_starts = interval_starts; P.iv_stride = 1;
     } else {
-        A.rays_mask = nullptr;
-        F.single_pass = false;
-        F.term = nullptr;  // already written by nfb_traverse_count for every ray
-        F.sm_starts = sample_info; F.sm_stride = 2;
-        F.iv_starts = interval_info; F.iv_stride = 2;
+        P.rays_mask = nullptr;
+        P.single_pass = false;
+        P.term = nullptr;  // already written by nfb_traverse_count for every ray
+        P.sm_starts = sample_info; P.sm_stride = 2;
+        P.iv_starts = interval_info; P.iv_stride = 2;
     }
-    traverse_fill_kernel<<<grid_for(rays->n_rays, 256, 64), 256, 0, s>>>(A, to_grid(grid), to_opts(march), F);
-    count_launch();
-    NFB_CHECK_LAUNCH("traverse_fill");
-    if (over_allocate) return scan_both(sample_info, interval_info, rays->n_rays, totals, scratch, scratch_bytes, s);
-    return NFB_OK;
+    A.rays_mask = nullptr;
+    rc = launch_march(A, to_grid(grid), to_opts(march), P, counters, s);
+    if (rc != NFB_OK) return rc;
+    if (over_allocate) {
+        rc = scan_both(sample_info, interval_info, rays->n_rays, totals, scratch, s);
+        if (rc == NFB_OK && totals != nullptr) cudaMemsetAsync(totals + 2, 0, sizeof(int64_t), s);
+    }
+    return rc;
 }
 
 }  // extern "C"

@@ -1,4 +1,4 @@
-// grid.cuh — per-ray multi-level DDA march shared by the count and fill kernels.
+// grid.cuh — per-ray multi-level DDA march shared by the count / fill kernels.
 //
 // Semantics follow the reference kernel line by line (csrc/grid.cu:98-281 with
 // include/utils_grid.cuh:10-142, data_spec_packed.cuh:43-72, utils_contraction.cuh:19-24):
@@ -7,11 +7,26 @@
 // expressions into FFMA are explicit __fmaf_rn here; nothing else may
 // fuse (the library is also built with -fmad=false).
 //
+// What is NOT like the reference: how the marching recurrence is evaluated.  The reference
+// advances t by repeated addition, one dependent FADD per step, both to skip empty space
+//     while (t + dt*0.5f < target) t += dt;                          (grid.cu:157-161, 199-203)
+// and to emit samples (grid.cu:208-262).  A closed form t0 + k*dt is not allowed (it rounds
+// differently), but the recurrence itself has an exact closed form per binade: while t stays
+// in [2^e, 2^(e+1)] it is a multiple of u = ulp(2^e), so RN(t + dt) = t + q with the constant
+// q = RN_u(dt) (ties excepted), and t_k = t + k*q holds EXACTLY.  advance() below finds the
+// number of steps with integer mantissa arithmetic plus an exact predicate check, takes the
+// binade crossings (and the rare tie case) as single real steps, and hands the marcher
+// "runs" (t0, q, n) of samples whose edges are t0 + j*q — bit-identical to the serial loop,
+// O(1) per grid cell instead of O(cell length / dt), and expandable by a whole warp.
+//
 // Differences from the reference, all outside its defined behaviour:
 //  * occupancy is read from a bit-packed copy of `binaries` (1 bit/cell, L1/L2 resident);
 //  * the DDA stops if an index leaves the grid (the reference would read out of bounds);
-//  * a march that can no longer advance (t + dt == t) stops (the reference spins forever).
+//  * a march that can no longer advance (t + dt == t, or NaN) stops (the reference spins).
 #pragma once
+
+#include <cmath>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -25,7 +40,28 @@ struct GridSpec {
     int n_grids;
     int res[3];
     long long cells_per_level;
+    // "any occupied" mip: one bit per (2^shift)^3 block of cells, [n_grids, mres0, mres1, mres2]
+    // in C order.  `mip` points to global memory in the kernel parameters; marching kernels copy
+    // it to shared memory and march with `mip` redirected there (nullptr: no mip).  97 % of the
+    // cells of a trained scene are empty: their lookups then never leave the SM.
+    const uint32_t* mip;
+    int mip_shift;
+    int mres[3];
+    int mip_cells_per_level;
+    int mip_words;
 };
+
+// Copy the mip into shared memory (all threads of the CTA; ends with a barrier) and return a
+// GridSpec whose `mip` points at the copy.
+__device__ __forceinline__ GridSpec stage_mip(const GridSpec& G, uint32_t* smem) {
+    GridSpec L = G;
+    if (G.mip != nullptr) {
+        for (int i = threadIdx.x; i < G.mip_words; i += blockDim.x) smem[i] = __ldg(G.mip + i);
+        L.mip = smem;
+    }
+    __syncthreads();
+    return L;
+}
 
 struct MarchOpts {
     float step_size;
@@ -99,116 +135,355 @@ __device__ __forceinline__ void compute_events(const float (&o)[3], const float 
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return max(lo, min(v, hi)); }
 
-// The march of one ray.  `emit(t_last, t_next, continuous)` is called for every sample, in
-// order; the caller's functor counts or stores.  Returns through n_samples / n_intervals /
-// t_last exactly what the reference kernel leaves in chunk_cnts and terminate_planes.
-template <class Emit>
-__device__ __forceinline__ void march_ray(const float (&o)[3], const float (&d)[3], float near,
-                                          float far, const GridSpec& G, const RayEvents& ev,
-                                          const MarchOpts& opt, Emit& emit, int& n_samples,
-                                          int& n_intervals, float& t_term) {
+// ---------------------------------------------------------------------------------------------
+// advance(): exact evaluation of
+//     n = 0; while (n < cap && !(fmaf(dt, .5f, t) >= target)) { t1 = t + dt; if (!(t1 > t)) break;
+//                                                              piece(t, t1 - t, 1); t = t1; ++n; }
+// in O(#binades crossed) instead of O(n).  `piece(t0, q, k)` is called for every maximal stretch
+// of k steps with constant increment q (t0 + j*q are exactly the serial values); `steps` is
+// incremented by the total.  dt must be > 0.
+// Round-to-nearest primitives that also compile for the host, so tests/host/advance_check.cu
+// can run advance() against the serial loop on the CPU (x86-64 SSE arithmetic is IEEE; the
+// host build uses -ffp-contract=off).
+#ifdef __CUDA_ARCH__
+#define NFB_HD __host__ __device__ __forceinline__
+NFB_HD float rn_add(float a, float b) { return __fadd_rn(a, b); }
+NFB_HD float rn_sub(float a, float b) { return __fsub_rn(a, b); }
+NFB_HD float rn_mul(float a, float b) { return __fmul_rn(a, b); }
+NFB_HD float rn_div(float a, float b) { return __fdiv_rn(a, b); }
+NFB_HD float rn_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+NFB_HD int f2i_rn(float a) { return __float2int_rn(a); }
+NFB_HD float i2f_rn(int a) { return __int2float_rn(a); }
+NFB_HD uint32_t f_bits(float a) { return __float_as_uint(a); }
+NFB_HD float bits_f(uint32_t a) { return __uint_as_float(a); }
+#else
+#define NFB_HD __host__ __device__ inline
+NFB_HD float rn_add(float a, float b) { volatile float r = a + b; return r; }
+NFB_HD float rn_sub(float a, float b) { volatile float r = a - b; return r; }
+NFB_HD float rn_mul(float a, float b) { volatile float r = a * b; return r; }
+NFB_HD float rn_div(float a, float b) { volatile float r = a / b; return r; }
+NFB_HD float rn_fma(float a, float b, float c) { return ::fmaf(a, b, c); }
+NFB_HD int f2i_rn(float a) { return (int)::lrintf(a); }
+NFB_HD float i2f_rn(int a) { return (float)a; }
+NFB_HD uint32_t f_bits(float a) { uint32_t r; memcpy(&r, &a, 4); return r; }
+NFB_HD float bits_f(uint32_t a) { float r; memcpy(&r, &a, 4); return r; }
+#endif
+
+template <class Piece>
+NFB_HD float advance(float t, const float dt, const float target, const int cap, int& steps,
+                     Piece&& piece) {
+    if (!(dt > 0.0f) || target != target) return t;
+    while (steps < cap) {
+        if (rn_fma(dt, 0.5f, t) >= target) break;
+        const float t1 = rn_add(t, dt);
+        if (!(t1 > t)) break;  // stuck at this magnitude (or NaN / inf)
+        const float q = rn_sub(t1, t);  // exact: t1 is a grid point reached from t
+        const uint32_t tb = f_bits(t);
+        const int E = (int)(tb >> 23);  // sign bit set (t < 0) makes E >= 256: excluded below
+        if (E >= 24 && E < 254) {
+            const float u = bits_f((uint32_t)(E - 23) << 23);   // ulp of t's binade
+            const float top = bits_f((uint32_t)(E + 1) << 23);  // 2^(e+1)
+            const float r = rn_sub(dt, q);                      // exact, |r| <= u/2
+            if (t1 <= top && rn_mul(fabsf(r), 2.0f) != u) {
+                // linear regime: t_k = t + k*q for every k with t + k*q <= top
+                const int ti = (int)((tb & 0x7fffffu) | 0x800000u);
+                const int qi = f2i_rn(rn_mul(q, bits_f((uint32_t)(277 - E) << 23)));
+                int kmax = (0x1000000 - ti) / qi;  // >= 1 because t1 <= top
+                if (kmax > cap - steps) kmax = cap - steps;
+                auto t_at = [&](int k) { return rn_mul(i2f_rn(ti + k * qi), u); };
+                auto done = [&](int k) { return rn_fma(dt, 0.5f, t_at(k)) >= target; };
+                int k = kmax;
+                if (kmax > 1 && done(kmax)) {
+                    // smallest k in [1, kmax] with done(k): estimate, then fix up (monotone)
+                    const float gap = rn_sub(target, rn_fma(dt, 0.5f, t));
+                    const float kf = ceilf(rn_div(gap, q));
+                    k = (kf >= (float)kmax) ? kmax : ((kf <= 1.0f) ? 1 : (int)kf);
+                    while (k > 1 && done(k - 1)) --k;
+                    while (!done(k)) ++k;
+                }
+                piece(t, q, k);
+                steps += k;
+                t = t_at(k);
+                continue;
+            }
+        }
+        piece(t, q, 1);  // binade crossing, tie case, tiny / negative t: one real step
+        steps += 1;
+        t = t1;
+    }
+    return t;
+}
+
+struct NoPiece {
+    NFB_HD void operator()(float, float, int) const {}
+};
+
+// ---------------------------------------------------------------------------------------------
+// The marching engine.
+//
+// The reference walks every ray with one thread: DDA step, occupancy test, and — inside the
+// same loop — the skip / emit recurrences.  On a GPU that interleaving is what hurts: lanes of
+// a warp reach occupied cells at different times, so the expensive emit code runs with two or
+// three lanes active.  Here the work of a ray is split into two phases that a warp executes
+// in lock step, round after round:
+//   produce   a tight DDA loop (<= kRoundSteps cells per round) that touches only the grid and
+//             appends EVENTS (t, kind) to a small per-lane queue in shared memory.  With a
+//             constant dt consecutive cells of the same kind fold into one event, because both
+//             recurrences are idempotent in their target (a ray through a trained scene yields
+//             a handful of events, not hundreds);
+//   consume   all lanes replay their queued events together through ONE advance() call site.
+// Lanes whose ray is finished fetch the next ray from a global counter (persistent threads), so
+// short rays do not idle while a long one finishes.  Results are addressed by ray id; nothing
+// depends on which lane marched which ray.
+//
+// Event kinds (t = exit of the cell / start of the segment):
+//   EV_EMPTY  empty cell(s):     skip to t, continuous = false        (grid.cu:189-206)
+//   EV_OCC    occupied cell(s):  emit samples up to t                 (grid.cu:208-262)
+//   EV_SEG    segment start:     if (!continuous) skip to t           (grid.cu:150-163)
+constexpr int kQ = 16;           // events queued per lane and round
+constexpr int kRoundSteps = 48;  // DDA cells per lane and round
+enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2 };
+
+// Policy interface (see grid.cu):
+//   typename Sink;  bool accept(r);  void skipped(r);  Sink begin(r);
+//   void end(r, Sink&, nS, nI, t_last);
+// Sink: run(t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
+// and one(t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
+template <class Policy>
+__device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
+                                             const float* __restrict__ rays_d,
+                                             const float* __restrict__ near_arr, float near_s,
+                                             const float* __restrict__ far_arr, float far_s,
+                                             const float* __restrict__ t_sorted,
+                                             const int64_t* __restrict__ t_indices,
+                                             const uint8_t* __restrict__ hits, long long n_rays,
+                                             const GridSpec& G, const MarchOpts& opt, Policy& P,
+                                             float* __restrict__ s_evt /* [kQ][blockDim.x] */,
+                                             unsigned long long* __restrict__ ray_counter) {
     const float eps = 1e-6f;
     const int m = G.n_grids;
     const float step = opt.step_size, cone = opt.cone_angle;
-    const int limit = opt.limit;
-    float inv[3];
+    const int cap = opt.limit > 0 ? opt.limit : 0x7fffffff;
+    const bool const_dt = (step > 0.0f) && (cone == 0.0f);
+    const int lane = lane_id();
+    const int tid = threadIdx.x, nthr = blockDim.x;
+
+    // ---- lane state: the ray, the producer (DDA) and the consumer (t_last recurrence)
+    bool have_ray = false, prod_done = true, exhausted = false;
+    long long r = -1;
+    float o[3], d[3], inv[3], near = 0.0f, far = 0.0f;
+    RayEvents ev;
+    int seg_i = 0, seg_steps = 0;
+    const int max_seg_steps = G.res[0] + G.res[1] + G.res[2] + 8;  // a DDA cannot take more
+    bool in_seg = false;
+    float tdist[3], delta[3], tmax_seg = 0.0f;
+    int cur[3], stepi[3], ovf[3];
+    long long level_base = 0;
+    int mip_base = 0;
+    int pend_kind = -1;
+    float pend_t = 0.0f;
+    int nq = 0;
+    uint32_t kinds = 0;
+    float t_last = 0.0f;
+    bool continuous = false, capped = false;
+    int nS = 0, nI = 0, dummy = 0;
+    typename Policy::Sink sink;
+
+    auto push = [&](int kind, float t) {
+        s_evt[nq * nthr + tid] = t;
+        kinds |= (uint32_t)kind << (2 * nq);
+        ++nq;
+    };
+    auto push_pending = [&]() {
+        if (pend_kind >= 0) { push(pend_kind, pend_t); pend_kind = -1; }
+    };
+
+    while (true) {
+        // ------------------------------------------------------------------ refill
+#pragma unroll 1
+        for (int attempt = 0; attempt < 4; ++attempt) {
+            const bool need = !have_ray && !exhausted;
+            const unsigned mask = __ballot_sync(kFull, need);
+            if (mask == 0u) break;
+            unsigned long long base = 0;
+            if (lane == __ffs(mask) - 1) base = atomicAdd(ray_counter, (unsigned long long)__popc(mask));
+            base = __shfl_sync(kFull, base, __ffs(mask) - 1);
+            if (need) {
+                const long long cand = (long long)base + __popc(mask & ((1u << lane) - 1u));
+                if (cand >= n_rays) {
+                    exhausted = true;
+                } else if (!P.accept(cand)) {
+                    P.skipped(cand);
+                } else {
+                    r = cand;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) inv[k] = __fdiv_rn(1.0f, d[k]);
-    int nS = 0, nI = 0;
-    float t_last = near;
-    bool continuous = false;
-    for (int i = 0; i < 2 * m - 1; ++i) {
-        const bool entering = ev.idx[i] < m;
-        int level = ev.idx[i] % m;
-        if (!((ev.hit_mask >> level) & 1u)) continue;
-        if (!entering) {
-            if (ev.idx[i + 1] < m) continue;  // next event enters a box: we are in a gap
-            level = ev.idx[i + 1] % m;
-            if (!((ev.hit_mask >> level) & 1u)) continue;
-        }
-        const float tmin = fmaxf(ev.t[i], near);
-        const float tmax = fminf(ev.t[i + 1], far);
-        if (tmin >= tmax) continue;
-        if (!continuous) {
-            if (step <= 0.0f) t_last = tmin;
-            else {
-                const float dt = calc_dt(t_last, cone, step);  // once, even when cone > 0
-                while (!(__fmaf_rn(dt, 0.5f, t_last) >= tmin)) {
-                    const float nt = __fadd_rn(t_last, dt);
-                    if (nt == t_last) break;
-                    t_last = nt;
+                    for (int k = 0; k < 3; ++k) {
+                        o[k] = __ldg(rays_o + 3 * r + k);
+                        d[k] = __ldg(rays_d + 3 * r + k);
+                        inv[k] = __fdiv_rn(1.0f, d[k]);
+                    }
+                    near = near_arr ? __ldg(near_arr + r) : near_s;
+                    far = far_arr ? __ldg(far_arr + r) : far_s;
+                    if (t_sorted != nullptr) {
+                        ev.hit_mask = 0;
+                        for (int l = 0; l < m; ++l)
+                            if (hits[r * m + l]) ev.hit_mask |= (1u << l);
+                        for (int i = 0; i < 2 * m; ++i) {
+                            ev.t[i] = __ldg(t_sorted + r * 2 * m + i);
+                            ev.idx[i] = (int8_t)__ldg(t_indices + r * 2 * m + i);
+                        }
+                    } else {
+                        compute_events(o, inv, G, ev);
+                    }
+                    have_ray = true; prod_done = false; in_seg = false; seg_i = 0; pend_kind = -1;
+                    t_last = near; continuous = false; capped = false; nS = 0; nI = 0;
+                    sink = P.begin(r);
                 }
             }
         }
-        // setup_traversal, utils_grid.cuh:58-114
-        const float* __restrict__ bb = G.aabbs + 6 * level;
-        float tdist[3], delta[3];
-        int stepi[3], cur[3], ovf[3];
-        const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax, eps);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const float bmin = bb[k], bmax = bb[3 + k];
-            const float resf = (float)G.res[k];
-            const float ext = __fsub_rn(bmax, bmin);
-            const float vox = __fdiv_rn(ext, resf);
-            const float rs = __fmaf_rn(d[k], ts, o[k]);  // FFMA site 1
-            const float re = __fmaf_rn(d[k], te, o[k]);
-            cur[k] = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(rs, bmin), ext), resf)), 0, G.res[k] - 1);
-            const int fin = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(re, bmin), ext), resf)), 0, G.res[k] - 1);
-            const int start_index = cur[k] + (d[k] > 0.0f ? 1 : 0);
-            // FFMA site 2: fma(bmin + fma(float(idx), vox, -rs), inv, tmin)
-            const float tm = __fmaf_rn(__fadd_rn(bmin, __fmaf_rn((float)start_index, vox, -rs)), inv[k], tmin);
-            const float sf = (d[k] == 0.0f) ? 0.0f : (d[k] > 0.0f ? 1.0f : -1.0f);
-            tdist[k] = (d[k] == 0.0f) ? tmax : tm;
-            stepi[k] = (int)sf;
-            delta[k] = (d[k] == 0.0f) ? tmax : __fmul_rn(__fmul_rn(vox, inv[k]), sf);
-            ovf[k] = fin + stepi[k];
+        if (!__any_sync(kFull, have_ray)) {
+            if (__all_sync(kFull, exhausted)) break;
+            continue;
         }
-        const long long level_base = (long long)level * G.cells_per_level;
-        while (limit <= 0 || nS < limit) {
-            const float t_trav = fminf(fminf(tdist[0], fminf(tdist[1], tdist[2])), tmax);
-            const long long cell = level_base + ((long long)cur[0] * G.res[1] + cur[1]) * G.res[2] + cur[2];
-            const bool occupied = (__ldg(G.occ_bits + (cell >> 5)) >> (cell & 31)) & 1u;
-            if (!occupied) {
-                if (step <= 0.0f) t_last = t_trav;
-                else {
-                    const float dt = calc_dt(t_last, cone, step);
-                    while (!(__fmaf_rn(dt, 0.5f, t_last) >= t_trav)) {
-                        const float nt = __fadd_rn(t_last, dt);
-                        if (nt == t_last) break;
-                        t_last = nt;
+        // ------------------------------------------------------------------ produce
+        int steps = 0;
+        while (have_ray && !prod_done && steps < kRoundSteps && nq <= kQ - 2) {
+            if (!in_seg) {
+                // next ray/box segment (grid.cu:128-149)
+                bool found = false;
+                float tmin = 0.0f;
+                int level = 0;
+                while (seg_i < 2 * m - 1) {
+                    const int i = seg_i++;
+                    const bool entering = ev.idx[i] < m;
+                    level = ev.idx[i] % m;
+                    if (!((ev.hit_mask >> level) & 1u)) continue;
+                    if (!entering) {
+                        if (ev.idx[i + 1] < m) continue;  // next event enters a box: we are in a gap
+                        level = ev.idx[i + 1] % m;
+                        if (!((ev.hit_mask >> level) & 1u)) continue;
                     }
+                    tmin = fmaxf(ev.t[i], near);
+                    tmax_seg = fminf(ev.t[i + 1], far);
+                    if (tmin >= tmax_seg) continue;
+                    found = true;
+                    break;
                 }
-                continuous = false;
-            } else {
-                while (limit <= 0 || nS < limit) {
-                    float t_next;
-                    if (step <= 0.0f) t_next = t_trav;
-                    else {
-                        const float dt = calc_dt(t_last, cone, step);
-                        if (__fmaf_rn(dt, 0.5f, t_last) >= t_trav) break;
-                        t_next = __fadd_rn(t_last, dt);
-                        if (!(t_next > t_last)) break;  // stuck
-                    }
-                    emit(t_last, t_next, continuous, nS, nI);
-                    nI += continuous ? 1 : 2;
-                    nS += 1;
-                    continuous = true;
-                    t_last = t_next;
-                    if (t_next >= t_trav) break;
+                if (!found) { push_pending(); prod_done = true; break; }
+                push_pending();
+                push(EV_SEG, tmin);
+                // setup_traversal, utils_grid.cuh:58-114
+                const float* __restrict__ bb = G.aabbs + 6 * level;
+                const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax_seg, eps);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float bmin = bb[k], bmax = bb[3 + k];
+                    const float resf = (float)G.res[k];
+                    const float ext = __fsub_rn(bmax, bmin);
+                    const float vox = __fdiv_rn(ext, resf);
+                    const float rs = __fmaf_rn(d[k], ts, o[k]);  // FFMA site 1
+                    const float re = __fmaf_rn(d[k], te, o[k]);
+                    cur[k] = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(rs, bmin), ext), resf)), 0, G.res[k] - 1);
+                    const int fin = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(re, bmin), ext), resf)), 0, G.res[k] - 1);
+                    const int start_index = cur[k] + (d[k] > 0.0f ? 1 : 0);
+                    // FFMA site 2: fma(bmin + fma(float(idx), vox, -rs), inv, tmin)
+                    const float tm = __fmaf_rn(__fadd_rn(bmin, __fmaf_rn((float)start_index, vox, -rs)), inv[k], tmin);
+                    const float sf = (d[k] == 0.0f) ? 0.0f : (d[k] > 0.0f ? 1.0f : -1.0f);
+                    tdist[k] = (d[k] == 0.0f) ? tmax_seg : tm;
+                    stepi[k] = (int)sf;
+                    delta[k] = (d[k] == 0.0f) ? tmax_seg : __fmul_rn(__fmul_rn(vox, inv[k]), sf);
+                    ovf[k] = fin + stepi[k];
                 }
+                level_base = (long long)level * G.cells_per_level;
+                mip_base = level * G.mip_cells_per_level;
+                in_seg = true;
+                seg_steps = 0;
+                continue;
             }
+            // one DDA cell (grid.cu:183-281)
+            const float t_trav = fminf(fminf(tdist[0], fminf(tdist[1], tdist[2])), tmax_seg);
+            bool occupied = true;
+            if (G.mip != nullptr) {
+                const int ci = mip_base + ((cur[0] >> G.mip_shift) * G.mres[1] + (cur[1] >> G.mip_shift)) * G.mres[2] +
+                               (cur[2] >> G.mip_shift);
+                occupied = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
+            }
+            if (occupied) {
+                const long long cell = level_base + ((long long)cur[0] * G.res[1] + cur[1]) * G.res[2] + cur[2];
+                occupied = (__ldg(G.occ_bits + (cell >> 5)) >> (cell & 31)) & 1u;
+            }
+            const int kind = occupied ? EV_OCC : EV_EMPTY;
+            // folding: constant dt — same kind; per-voxel mode — empties only; cone — never
+            const bool fold = (kind == pend_kind) && (const_dt || (step <= 0.0f && kind == EV_EMPTY));
+            if (!fold) { push_pending(); pend_kind = kind; }
+            pend_t = t_trav;
             // single_traversal, utils_grid.cuh:116-142: x if strictly smallest, else y if < z, else z
             const int ax = (tdist[0] < tdist[1] && tdist[0] < tdist[2]) ? 0 : (tdist[1] < tdist[2] ? 1 : 2);
-            // (written without dynamic register indexing)
-            if (ax == 0) { cur[0] += stepi[0]; tdist[0] = __fadd_rn(tdist[0], delta[0]); if (cur[0] == ovf[0] || cur[0] < 0 || cur[0] >= G.res[0]) break; }
-            else if (ax == 1) { cur[1] += stepi[1]; tdist[1] = __fadd_rn(tdist[1], delta[1]); if (cur[1] == ovf[1] || cur[1] < 0 || cur[1] >= G.res[1]) break; }
-            else { cur[2] += stepi[2]; tdist[2] = __fadd_rn(tdist[2], delta[2]); if (cur[2] == ovf[2] || cur[2] < 0 || cur[2] >= G.res[2]) break; }
+            bool leave;
+            if (ax == 0) { cur[0] += stepi[0]; tdist[0] = __fadd_rn(tdist[0], delta[0]); leave = (cur[0] == ovf[0] || cur[0] < 0 || cur[0] >= G.res[0]); }
+            else if (ax == 1) { cur[1] += stepi[1]; tdist[1] = __fadd_rn(tdist[1], delta[1]); leave = (cur[1] == ovf[1] || cur[1] < 0 || cur[1] >= G.res[1]); }
+            else { cur[2] += stepi[2]; tdist[2] = __fadd_rn(tdist[2], delta[2]); leave = (cur[2] == ovf[2] || cur[2] < 0 || cur[2] >= G.res[2]); }
+            if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
+            ++steps;
+        }
+        // ------------------------------------------------------------------ consume
+        const int maxq = __reduce_max_sync(kFull, nq);
+#pragma unroll 1
+        for (int j = 0; j < maxq; ++j) {
+            if (j < nq && !capped) {
+                const int kind = (int)((kinds >> (2 * j)) & 3u);
+                const float t = s_evt[j * nthr + tid];
+                const bool emit = (kind == EV_OCC);
+                const bool doit = !(kind == EV_SEG && continuous);
+                if (step <= 0.0f) {  // one interval per occupied voxel crossing
+                    if (!emit) {
+                        if (doit) t_last = t;
+                    } else {
+                        sink.one(t_last, t, continuous, nS, nI);
+                        nI += continuous ? 1 : 2;
+                        nS += 1;
+                        continuous = true;
+                        t_last = t;
+                    }
+                } else if (const_dt || !emit) {
+                    if (doit) {
+                        const float dt = const_dt ? step : calc_dt(t_last, cone, step);
+                        if (emit) {
+                            t_last = advance(t_last, dt, t, cap, nS, [&](float t0, float q, int k) {
+                                sink.run(t0, q, k, continuous, nS, nI);
+                                nI += continuous ? k : k + 1;
+                                continuous = true;
+                            });
+                        } else {
+                            t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
+                        }
+                    }
+                } else {  // cone_angle > 0: dt follows t, a true serial recurrence
+                    while (nS < cap) {
+                        const float dt = calc_dt(t_last, cone, step);
+                        if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
+                        const float t_next = __fadd_rn(t_last, dt);
+                        if (!(t_next > t_last)) break;  // stuck
+                        sink.one(t_last, t_next, continuous, nS, nI);
+                        nI += continuous ? 1 : 2;
+                        nS += 1;
+                        continuous = true;
+                        t_last = t_next;
+                        if (t_next >= t) break;
+                    }
+                }
+                if (kind == EV_EMPTY) continuous = false;
+                if (nS >= cap) { capped = true; prod_done = true; pend_kind = -1; }
+            }
+        }
+        nq = 0;
+        kinds = 0;
+        // ------------------------------------------------------------------ retire
+        if (have_ray && prod_done && pend_kind < 0) {
+            P.end(r, sink, nS, nI, t_last);
+            have_ray = false;
         }
     }
-    n_samples = nS;
-    n_intervals = nI;
-    t_term = t_last;
 }
 
 }  // namespace nfb
