@@ -363,6 +363,8 @@ static int check_common(const nfb_rays_t* rays, const nfb_grid_t* grid, const nf
     NFB_CHECK_ARG(rays->n_rays >= 0, "negative n_rays");
     NFB_CHECK_ARG(grid->n_grids >= 1 && grid->n_grids <= kMaxLevels, "n_grids must be in [1, %d]", kMaxLevels);
     NFB_CHECK_ARG(grid->res[0] > 0 && grid->res[1] > 0 && grid->res[2] > 0, "bad resolution");
+    NFB_CHECK_ARG((long long)grid->n_grids * grid->res[0] * grid->res[1] * grid->res[2] < (1ll << 31),
+                  "grids with 2^31 or more cells are not supported");
     if (rays->n_rays > 0) {
         NFB_CHECK_ARG(rays->rays_o && rays->rays_d && grid->occ_bits && grid->aabbs, "null pointer");
         const int pre = (rays->t_sorted != nullptr) + (rays->t_indices != nullptr) + (rays->hits != nullptr);

@@ -274,11 +274,12 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     float o[3], d[3], inv[3], near = 0.0f, far = 0.0f;
     RayEvents ev;
     int seg_i = 0, seg_steps = 0;
+    bool first_seg = true;
     const int max_seg_steps = G.res[0] + G.res[1] + G.res[2] + 8;  // a DDA cannot take more
     bool in_seg = false;
     float tdist[3], delta[3], tmax_seg = 0.0f;
-    int cur[3], stepi[3], ovf[3];
-    long long level_base = 0;
+    int cur[3], stepi[3], stop[3], cstride[3];
+    int cell = 0;  // linear index of the current cell (host side guarantees it fits 31 bits)
     int mip_base = 0;
     int pend_kind = -1;
     float pend_t = 0.0f;
@@ -335,7 +336,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     } else {
                         compute_events(o, inv, G, ev);
                     }
-                    have_ray = true; prod_done = false; in_seg = false; seg_i = 0; pend_kind = -1;
+                    have_ray = true; prod_done = false; in_seg = false; seg_i = 0; pend_kind = -1; first_seg = true;
                     t_last = near; continuous = false; capped = false; nS = 0; nI = 0;
                     sink = P.begin(r);
                 }
@@ -370,8 +371,16 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     break;
                 }
                 if (!found) { push_pending(); prod_done = true; break; }
-                push_pending();
-                push(EV_SEG, tmin);
+                // "if (!continuous) skip to tmin": right after the ray starts or after empty
+                // cells `continuous` is known to be false and the event is a plain skip
+                if (first_seg) {
+                    pend_kind = EV_EMPTY; pend_t = tmin; first_seg = false;
+                } else if (pend_kind == EV_EMPTY && (const_dt || step <= 0.0f)) {
+                    pend_t = tmin;
+                } else {
+                    push_pending();
+                    push(EV_SEG, tmin);
+                }
                 // setup_traversal, utils_grid.cuh:58-114
                 const float* __restrict__ bb = G.aabbs + 6 * level;
                 const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax_seg, eps);
@@ -392,37 +401,51 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     tdist[k] = (d[k] == 0.0f) ? tmax_seg : tm;
                     stepi[k] = (int)sf;
                     delta[k] = (d[k] == 0.0f) ? tmax_seg : __fmul_rn(__fmul_rn(vox, inv[k]), sf);
-                    ovf[k] = fin + stepi[k];
+                    // The walk leaves when the index reaches fin + step (utils_grid.cuh:123) or the
+                    // grid edge, whichever lies ahead: one stop value per axis.
+                    const int ovf = fin + stepi[k];
+                    const bool ahead = stepi[k] > 0 ? ovf > cur[k] : (stepi[k] < 0 ? ovf < cur[k] : true);
+                    stop[k] = ahead ? ovf : (stepi[k] > 0 ? G.res[k] : -1);
                 }
-                level_base = (long long)level * G.cells_per_level;
+                cstride[0] = stepi[0] * G.res[1] * G.res[2];
+                cstride[1] = stepi[1] * G.res[2];
+                cstride[2] = stepi[2];
+                cell = level * (int)G.cells_per_level + (cur[0] * G.res[1] + cur[1]) * G.res[2] + cur[2];
                 mip_base = level * G.mip_cells_per_level;
                 in_seg = true;
                 seg_steps = 0;
                 continue;
             }
-            // one DDA cell (grid.cu:183-281)
+            // one DDA cell (grid.cu:183-281), branch-free
             const float t_trav = fminf(fminf(tdist[0], fminf(tdist[1], tdist[2])), tmax_seg);
-            bool occupied = true;
+            uint32_t cbit = 1u;
             if (G.mip != nullptr) {
                 const int ci = mip_base + ((cur[0] >> G.mip_shift) * G.mres[1] + (cur[1] >> G.mip_shift)) * G.mres[2] +
                                (cur[2] >> G.mip_shift);
-                occupied = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
+                cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
             }
-            if (occupied) {
-                const long long cell = level_base + ((long long)cur[0] * G.res[1] + cur[1]) * G.res[2] + cur[2];
-                occupied = (__ldg(G.occ_bits + (cell >> 5)) >> (cell & 31)) & 1u;
-            }
-            const int kind = occupied ? EV_OCC : EV_EMPTY;
+            // fine bit, fetched only under a set mip bit (predicated load: no divergent section)
+            uint32_t word;
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\tmov.u32 %0, 0;\n\t"
+                         "@p ld.global.nc.u32 %0, [%2];\n\t}"
+                         : "=r"(word) : "r"(cbit), "l"(G.occ_bits + (cell >> 5)));
+            const int kind = (int)((word >> (cell & 31)) & 1u);  // EV_OCC == 1, EV_EMPTY == 0
             // folding: constant dt — same kind; per-voxel mode — empties only; cone — never
             const bool fold = (kind == pend_kind) && (const_dt || (step <= 0.0f && kind == EV_EMPTY));
             if (!fold) { push_pending(); pend_kind = kind; }
             pend_t = t_trav;
             // single_traversal, utils_grid.cuh:116-142: x if strictly smallest, else y if < z, else z
-            const int ax = (tdist[0] < tdist[1] && tdist[0] < tdist[2]) ? 0 : (tdist[1] < tdist[2] ? 1 : 2);
-            bool leave;
-            if (ax == 0) { cur[0] += stepi[0]; tdist[0] = __fadd_rn(tdist[0], delta[0]); leave = (cur[0] == ovf[0] || cur[0] < 0 || cur[0] >= G.res[0]); }
-            else if (ax == 1) { cur[1] += stepi[1]; tdist[1] = __fadd_rn(tdist[1], delta[1]); leave = (cur[1] == ovf[1] || cur[1] < 0 || cur[1] >= G.res[1]); }
-            else { cur[2] += stepi[2]; tdist[2] = __fadd_rn(tdist[2], delta[2]); leave = (cur[2] == ovf[2] || cur[2] < 0 || cur[2] >= G.res[2]); }
+            const bool px = tdist[0] < tdist[1] && tdist[0] < tdist[2];
+            const bool py = !px && tdist[1] < tdist[2];
+            const bool pz = !px && !py;
+            cur[0] += px ? stepi[0] : 0;
+            cur[1] += py ? stepi[1] : 0;
+            cur[2] += pz ? stepi[2] : 0;
+            tdist[0] = px ? __fadd_rn(tdist[0], delta[0]) : tdist[0];
+            tdist[1] = py ? __fadd_rn(tdist[1], delta[1]) : tdist[1];
+            tdist[2] = pz ? __fadd_rn(tdist[2], delta[2]) : tdist[2];
+            cell += px ? cstride[0] : (py ? cstride[1] : cstride[2]);
+            const bool leave = (px && cur[0] == stop[0]) || (py && cur[1] == stop[1]) || (pz && cur[2] == stop[2]);
             if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
             ++steps;
         }
