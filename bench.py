@@ -209,8 +209,8 @@ ALGO_BYTES = {
     "traverse_fill_sampling": lambda S, R, B: 16 * S + 24 * R + 16 * R + B,
     "render_weight_fwd": lambda S, R, B: 24 * S + 16 * R,
     "render_weight_bwd": lambda S, R, B: 24 * S + 16 * R,
-    "render_composite_fwd": lambda S, R, B: 44 * S + 16 * R + 20 * R,
-    "render_composite_bwd": lambda S, R, B: 60 * S + 16 * R + 20 * R,
+    "composite_fwd": lambda S, R, B: 24 * S + 16 * R + 20 * R,   # read w, rgb, ts, te; write 5 floats/ray
+    "composite_bwd": lambda S, R, B: 52 * S + 16 * R + 20 * R,   # read ts,te,sigma,rgb,T,ray_idx; write g_sigma,g_rgb
     "pack_info": lambda S, R, B: 8 * S + 16 * R,
 }
 

@@ -137,6 +137,30 @@ NFB_API int nfb_accumulate_bwd(const float* g_out, const float* weights, const f
                                float* g_weights, float* g_values, nfb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * Compositing of nerfacc.rendering() (nerfacc/volrend.py:140-156), fused.
+ * Forward: colors[n_rays,3] = sum w*rgb, opacity[n_rays] = sum w, depth[n_rays] = sum
+ * w*(t_starts+t_ends)/2 per ray in one pass (replaces three accumulate_along_rays calls);
+ * canonical packed_info required; deterministic, every row written (zeros for empty rays). */
+NFB_API int nfb_composite_fwd(const float* weights, const float* rgbs, const float* t_starts,
+                              const float* t_ends, const int64_t* packed_info, int64_t n_rays,
+                              int64_t n, float* colors, float* opacity, float* depth,
+                              void* workspace, size_t workspace_bytes, uint32_t epoch,
+                              nfb_stream_t stream);
+/* Backward of rendering() down to the radiance field outputs, one reverse pass: what autograd
+ * derives from volrend.py:140-151 (three accumulate_along_rays) chained with the weight backward
+ * (nfb_render_weight_bwd).  g_colors [n_rays,3], g_opacity [n_rays], g_depth [n_rays] (wrt the
+ * un-normalised depth sum) and the optional per-sample g_weights / g_trans / g_alphas may each
+ * be NULL.  Writes g_in (d/d sigmas or d/d alphas) and g_rgbs [n,3] (optional). */
+NFB_API int nfb_composite_bwd(int from_density, const float* g_colors, const float* g_opacity,
+                              const float* g_depth, const float* g_weights, const float* g_trans,
+                              const float* g_alphas, const float* alphas, const float* t_starts,
+                              const float* t_ends, const float* sigmas, const float* rgbs,
+                              const float* trans, const int64_t* ray_indices,
+                              const int64_t* packed_info, int64_t n_rays, int64_t n, float* g_in,
+                              float* g_rgbs, void* workspace, size_t workspace_bytes,
+                              uint32_t epoch, nfb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * pack_info: ray_indices [n] -> packed_info [n_rays, 2] (nerfacc/pack.py:43-46: histogram of
  * the indices, starts = exclusive cumsum).  `workspace` needs 8 bytes per 2048 rays.
  */

@@ -186,3 +186,69 @@ class Accumulate(torch.autograd.Function):
         g_w, g_v = accumulate_bwd(g_out.contiguous(), weights, values, ray_indices,
                                   ctx.needs_input_grad[0], ctx.has_values and ctx.needs_input_grad[1])
         return g_w, g_v, None, None, None
+
+
+# ----------------------------------------------------------------------------- rendering()
+class RenderComposite(torch.autograd.Function):
+    """rendering() of volrend.py:14-158 for flattened CUDA inputs, in three kernels:
+    weights forward (nfb_render_weight_fwd), composite forward (nfb_composite_fwd) and ONE
+    backward (nfb_composite_bwd) down to d/d field and d/d rgbs.
+
+    Returns (colors_sum [R,3], opacity [R,1], depth_sum [R,1], weights, trans, alphas); the
+    depth normalisation and the background blend stay torch ops on [R, .] tensors in volrend.py.
+    """
+
+    @staticmethod
+    def forward(ctx, field, rgbs, t_starts, t_ends, packed_info, ray_indices, n_rays: int,
+                from_density: bool):
+        field, rgbs = field.contiguous(), rgbs.contiguous()
+        t_starts, t_ends = t_starts.contiguous(), t_ends.contiguous()
+        dev = _C.require_cuda(field, rgbs, t_starts, t_ends, packed_info, ray_indices)
+        if from_density:
+            weights, trans, alphas, _ = weight_fwd(True, None, t_starts, t_ends, field, None,
+                                                   packed_info, 0, True, True, True)
+        else:
+            weights, trans, _, _ = weight_fwd(False, field, None, None, None, None, packed_info, 0,
+                                              True, True, False)
+            alphas = None
+        n = field.numel()
+        colors = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)
+        opacity = torch.empty((n_rays, 1), dtype=torch.float32, device=dev)
+        depth = torch.empty((n_rays, 1), dtype=torch.float32, device=dev)
+        if n_rays > 0:
+            with torch.cuda.device(dev):
+                ws, ws_bytes, epoch = _C.workspace(dev, max(n, 1))
+                rc = _C.lib().nfb_composite_fwd(
+                    _p(weights), _p(rgbs), _p(t_starts), _p(t_ends), _p(packed_info), n_rays, n,
+                    colors.data_ptr(), opacity.data_ptr(), depth.data_ptr(), ws.data_ptr(), ws_bytes,
+                    epoch, _C.stream_ptr(dev))
+            _C.check(rc, "composite_fwd")
+        ctx.set_materialize_grads(False)
+        ctx.from_density = from_density
+        ctx.n_rays = n_rays
+        ctx.save_for_backward(field, rgbs, t_starts, t_ends, trans, packed_info, ray_indices)
+        if alphas is None:
+            alphas = field.new_empty(0)
+            ctx.mark_non_differentiable(alphas)
+        return colors, opacity, depth, weights, trans, alphas
+
+    @staticmethod
+    def backward(ctx, g_colors, g_opacity, g_depth, g_weights, g_trans, g_alphas):
+        field, rgbs, t_starts, t_ends, trans, packed_info, ray_indices = ctx.saved_tensors
+        dev = field.device
+        n = field.numel()
+        need_field, need_rgb = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        g_field = torch.empty_like(field)
+        g_rgbs = torch.empty_like(rgbs) if need_rgb else None
+        if n > 0:
+            fd = ctx.from_density
+            with torch.cuda.device(dev):
+                ws, ws_bytes, epoch = _C.workspace(dev, n)
+                rc = _C.lib().nfb_composite_bwd(
+                    int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),
+                    _p(_cg(g_trans)), _p(_cg(g_alphas)) if fd else None,
+                    None if fd else _p(field), _p(t_starts), _p(t_ends), _p(field) if fd else None,
+                    _p(rgbs), _p(trans), _p(ray_indices), _p(packed_info), ctx.n_rays, n,
+                    g_field.data_ptr(), _p(g_rgbs), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            _C.check(rc, "composite_bwd")
+        return (g_field if need_field else None), g_rgbs, None, None, None, None, None, None

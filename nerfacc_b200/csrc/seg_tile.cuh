@@ -27,7 +27,7 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kVec = 4;                   // float4 per thread
 constexpr int kTile = kThreads * kVec * 4;  // 4096 items
 constexpr int kWarpItems = kTile / kWarps;  // 512
-constexpr int kStatusPerTile = 4;          // look-back words reserved per tile
+constexpr int kStatusPerTile = 8;          // look-back words reserved per tile
 constexpr uint32_t kEpochMemset = 0x3fffffffu;
 
 struct SumOp {

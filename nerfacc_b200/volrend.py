@@ -88,6 +88,21 @@ def rendering(
         what, field.shape
     )
 
+    if flat and _composite_fused_ok(t_starts, t_ends, ray_indices, n_rays, rgbs, field):
+        # one weights kernel + one composite kernel forward, one kernel backward
+        pi = pack_info(ray_indices, n_rays)
+        colors, opacities, depths, weights, trans, alphas = _ops.RenderComposite.apply(
+            field, rgbs, t_starts.detach(), t_ends.detach(), pi, ray_indices.contiguous(), int(n_rays),
+            use_density)
+        if use_density:
+            extras = {"weights": weights, "alphas": alphas, "trans": trans, "sigmas": field, "rgbs": rgbs}
+        else:
+            extras = {"weights": weights, "trans": trans, "rgbs": rgbs, "alphas": field}
+        depths = depths / opacities.clamp_min(torch.finfo(rgbs.dtype).eps)
+        if render_bkgd is not None:
+            colors = colors + render_bkgd * (1.0 - opacities)
+        return colors, opacities, depths, extras
+
     seg = dict(ray_indices=ray_indices, n_rays=n_rays)
     if use_density:
         weights, trans, alphas = render_weight_from_density(t_starts, t_ends, field, **seg)
@@ -348,6 +363,18 @@ def accumulate_along_rays_(
         return
     src = weights[..., None] if values is None else weights[..., None] * values
     outputs.index_add_(0, ray_indices, src)
+
+
+def _composite_fused_ok(t_starts, t_ends, ray_indices, n_rays, rgbs, field) -> bool:
+    f32 = torch.float32
+    return (
+        n_rays is not None
+        and field.is_cuda and field.dim() == 1 and field.numel() > 0
+        and field.dtype == f32 and rgbs.dtype == f32 and t_starts.dtype == f32 and t_ends.dtype == f32
+        and rgbs.dim() == 2 and rgbs.shape[0] == field.shape[0]
+        and ray_indices.dtype == torch.long and ray_indices.is_cuda
+        and _no_grad_needed(t_starts, t_ends)
+    )
 
 
 def _accumulate_fused_ok(weights, values, ray_indices) -> bool:

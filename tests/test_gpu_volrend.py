@@ -254,3 +254,63 @@ def test_rendering_end_to_end(device):
     assert set(extras) == {"weights", "alphas", "trans", "sigmas", "rgbs"}
     (colors.sum() + opac.sum()).backward()
     assert torch.isfinite(s.grad).all() and torch.isfinite(c.grad).all()
+
+
+@pytest.mark.parametrize("mode", ["density", "alpha"])
+def test_rendering_fused_composite_vs_oracle(device, mode):
+    """rendering() on flattened inputs (fused weights + composite forward, one fused backward)
+    against the oracle's composition of volrend.py:140-156, incl. empty rays, a long ray that
+    spans several tiles, a background colour, and an extra loss on extras['weights']."""
+    import nerfacc_b200 as nf
+
+    counts = ragged_counts(3000, mean=14, seed=5, long_rays=((17, 9000), (1500, 1)))
+    pi = packed_info_from_counts(counts)
+    ri = ray_indices_from_counts(counts)
+    n, R = int(counts.sum()), len(counts)
+    rng = np.random.default_rng(9)
+    ts = np.sort(rng.random(n).astype(np.float32) * 4)
+    te = (ts + rng.random(n).astype(np.float32) * 0.02 + 1e-3).astype(np.float32)
+    field = (rng.random(n) * (8.0 if mode == "density" else 0.3)).astype(np.float32)
+    rgb = rng.random((n, 3)).astype(np.float32)
+    gc, go, gd = (rng.random((R, k)).astype(np.float32) for k in (3, 1, 1))
+    gwx = rng.random(n).astype(np.float32)
+    bk = np.array([0.1, 0.5, 0.9], np.float32)
+
+    t = lambda a: torch.from_numpy(a).to(device)
+    f_t, rgb_t = t(field).requires_grad_(True), t(rgb).requires_grad_(True)
+    fn = (lambda a, b, r: (rgb_t, f_t))
+    kw = dict(rgb_sigma_fn=fn) if mode == "density" else dict(rgb_alpha_fn=fn)
+    colors, opac, depth, extras = nf.rendering(t(ts), t(te), t(ri), R, render_bkgd=t(bk), **kw)
+    loss = (colors * t(gc)).sum() + (opac * t(go)).sum() + (depth * t(gd)).sum() + (extras["weights"] * t(gwx)).sum()
+    loss.backward()
+
+    if mode == "density":
+        w, T, a = oracle.render_weight_from_density(ts, te, field, pi)
+    else:
+        w, T = oracle.render_weight_from_alpha(field, pi)
+    tmid = ((ts + te) / 2)[:, None].astype(np.float32)
+    c0 = oracle.accumulate_along_rays(w, rgb, ri, R)
+    o0 = oracle.accumulate_along_rays(w, None, ri, R)
+    d0 = oracle.accumulate_along_rays(w, tmid, ri, R)
+    eps = np.finfo(np.float32).eps
+    den = np.maximum(o0, eps)
+    assert_close(extras["weights"].detach().cpu().numpy(), w, 1e-5, 1e-7, "weights")
+    assert_close(colors.detach().cpu().numpy(), c0 + bk * (1 - o0), 2e-5, 1e-5, "colors")
+    assert_close(opac.detach().cpu().numpy(), o0, 2e-5, 1e-5, "opacity")
+    assert_close(depth.detach().cpu().numpy(), d0 / den, 1e-4, 1e-5, "depth")
+    assert (opac.detach().cpu().numpy()[counts == 0] == 0).all()
+    # backward: colors = c0 + bk*(1-o0), depth = d0/den
+    g_c0 = gc
+    g_o0 = go - (gc * bk).sum(-1, keepdims=True) - np.where(o0 > eps, gd * d0 / (den * den), 0.0)
+    g_d0 = gd / den
+    gw1, g_rgb = oracle.accumulate_along_rays_bwd(g_c0, w, rgb, ri)
+    gw2, _ = oracle.accumulate_along_rays_bwd(g_o0.astype(np.float32), w, None, ri)
+    gw3, _ = oracle.accumulate_along_rays_bwd(g_d0.astype(np.float32), w, tmid, ri)
+    gw = (gw1 + gw2 + gw3 + gwx).astype(np.float32)
+    if mode == "density":
+        g_f = oracle.render_weight_from_density_bwd(gw, None, None, ts, te, field, pi)
+    else:
+        g_f = oracle.render_weight_from_alpha_bwd(gw, None, field, pi)
+    assert_close(rgb_t.grad.cpu().numpy(), g_rgb, 1e-5, 1e-7, "g_rgb")
+    scale = float(np.abs(g_f).max())
+    assert_close(f_t.grad.cpu().numpy(), g_f, 1e-4, 2e-6 * scale, "g_field")
