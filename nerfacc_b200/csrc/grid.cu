@@ -199,14 +199,14 @@ struct FillPolicy {
 // Persistent CTAs: dynamic shared memory = [mip words][event queue kQ x blockDim floats].
 constexpr int kMarchThreads = 512;
 
-template <class Policy>
-__global__ void __launch_bounds__(kMarchThreads, 1)
+template <bool MIP, class Policy>
+__global__ void __launch_bounds__(kMarchThreads, 2)
 march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
              unsigned long long* ray_counter) {
     extern __shared__ uint32_t s_dyn[];
     const GridSpec G = stage_mip(Gp, s_dyn);
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
-    march_engine(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
+    march_engine<MIP>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
                  A.hits, A.n_rays, G, opt, P, s_evt, ray_counter);
 }
 
@@ -339,7 +339,7 @@ template <class Policy>
 static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& opt, const Policy& P,
                         unsigned long long* counter, cudaStream_t s) {
     const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float);
-    auto kernel = march_kernel<Policy>;
+    auto kernel = G.mip != nullptr ? march_kernel<true, Policy> : march_kernel<false, Policy>;
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
         set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
         return NFB_ERR_CUDA;
@@ -349,7 +349,7 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
         return NFB_ERR_CUDA;
     }
     long long b = ceil_div<long long>(A.n_rays, kMarchThreads);
-    const long long cap = (long long)sm_count();
+    const long long cap = (long long)sm_count() * (smem <= 100 * 1024 ? 2 : 1);
     if (b > cap) b = cap;
     if (b < 1) b = 1;
     kernel<<<(unsigned)b, kMarchThreads, smem, s>>>(A, G, opt, P, counter);

@@ -224,32 +224,35 @@ struct NoPiece {
 // The reference walks every ray with one thread: DDA step, occupancy test, and — inside the
 // same loop — the skip / emit recurrences.  On a GPU that interleaving is what hurts: lanes of
 // a warp reach occupied cells at different times, so the expensive emit code runs with two or
-// three lanes active.  Here the work of a ray is split into two phases that a warp executes
-// in lock step, round after round:
-//   produce   a tight DDA loop (<= kRoundSteps cells per round) that touches only the grid and
-//             appends EVENTS (t, kind) to a small per-lane queue in shared memory.  With a
-//             constant dt consecutive cells of the same kind fold into one event, because both
-//             recurrences are idempotent in their target (a ray through a trained scene yields
-//             a handful of events, not hundreds);
-//   consume   all lanes replay their queued events together through ONE advance() call site.
-// Lanes whose ray is finished fetch the next ray from a global counter (persistent threads), so
-// short rays do not idle while a long one finishes.  Results are addressed by ray id; nothing
-// depends on which lane marched which ray.
+// three lanes active.  Here the work of a ray is split into a PRODUCER and a CONSUMER that a
+// warp executes in lock step:
+//   produce   a tight, branch-free DDA loop (<= kRoundSteps cells per round) that touches only
+//             the grid and appends EVENTS (kind, t) to a per-lane queue in shared memory.  With
+//             a constant dt consecutive cells of the same kind fold into one event, because both
+//             recurrences are idempotent in their target: a ray through a trained scene yields
+//             a handful of events, not hundreds;
+//   consume   when a queue fills up, all lanes replay their queued events together through
+//             ONE advance() call site.  The queue also carries the ray boundaries (EV_RAY), so
+//             the producer of a lane may be several rays ahead of its consumer and the replay
+//             finds every lane with work.
+// Lanes whose DDA has finished a ray fetch the next one from a global counter (persistent
+// threads).  Results are addressed by ray id; nothing depends on which lane marched which ray.
 //
 // Event kinds (t = exit of the cell / start of the segment):
 //   EV_EMPTY  empty cell(s):     skip to t, continuous = false        (grid.cu:189-206)
 //   EV_OCC    occupied cell(s):  emit samples up to t                 (grid.cu:208-262)
 //   EV_SEG    segment start:     if (!continuous) skip to t           (grid.cu:150-163)
-constexpr int kQ = 16;           // events queued per lane and round
-constexpr int kRoundSteps = 48;  // DDA cells per lane and round
-enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2 };
+//   EV_RAY    a new ray starts:  payload = ray id; retires the previous ray of the lane
+constexpr int kQ = 16;           // events queued per lane
+constexpr int kRoundSteps = 64;  // DDA cells per lane and round
+enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2, EV_RAY = 3 };
 
 // Policy interface (see grid.cu):
 //   typename Sink;  bool accept(r);  void skipped(r);  Sink begin(r);
 //   void end(r, Sink&, nS, nI, t_last);
 // Sink: run(t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
 // and one(t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
-template <class Policy>
+template <bool MIP, class Policy>
 __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const float* __restrict__ rays_d,
                                              const float* __restrict__ near_arr, float near_s,
@@ -265,28 +268,33 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     const float step = opt.step_size, cone = opt.cone_angle;
     const int cap = opt.limit > 0 ? opt.limit : 0x7fffffff;
     const bool const_dt = (step > 0.0f) && (cone == 0.0f);
+    const bool fold_empty = const_dt || step <= 0.0f;  // consecutive empty cells fold
+    const bool fold_occ = const_dt;                    // consecutive occupied cells fold
+    const bool eager = opt.limit > 0;  // with a sample cap, replay every round (bounds wasted DDA work)
     const int lane = lane_id();
     const int tid = threadIdx.x, nthr = blockDim.x;
 
-    // ---- lane state: the ray, the producer (DDA) and the consumer (t_last recurrence)
-    bool have_ray = false, prod_done = true, exhausted = false;
+    // ---- producer state (the DDA of the ray being walked)
+    bool have_ray = false, exhausted = false;
+    float far = 0.0f, near = 0.0f;
     long long r = -1;
-    float o[3], d[3], inv[3], near = 0.0f, far = 0.0f;
     RayEvents ev;
     int seg_i = 0, seg_steps = 0;
-    bool first_seg = true;
     const int max_seg_steps = G.res[0] + G.res[1] + G.res[2] + 8;  // a DDA cannot take more
-    bool in_seg = false;
+    bool in_seg = false, first_seg = true;
     float tdist[3], delta[3], tmax_seg = 0.0f;
     int cur[3], stepi[3], stop[3], cstride[3];
     int cell = 0;  // linear index of the current cell (host side guarantees it fits 31 bits)
     int mip_base = 0;
     int pend_kind = -1;
     float pend_t = 0.0f;
+    // ---- queue
     int nq = 0;
     uint32_t kinds = 0;
+    // ---- consumer state (the t_last recurrence of the ray being replayed)
+    bool c_have = false, continuous = false, capped = false;
+    long long c_r = -1;
     float t_last = 0.0f;
-    bool continuous = false, capped = false;
     int nS = 0, nI = 0, dummy = 0;
     typename Policy::Sink sink;
 
@@ -299,11 +307,78 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         if (pend_kind >= 0) { push(pend_kind, pend_t); pend_kind = -1; }
     };
 
+    auto consume = [&]() {
+        const int maxq = __reduce_max_sync(kFull, nq);
+#pragma unroll 1
+        for (int j = 0; j < maxq; ++j) {
+            if (j >= nq) continue;
+            const int kind = (int)((kinds >> (2 * j)) & 3u);
+            const float t = s_evt[j * nthr + tid];
+            if (kind == EV_RAY) {
+                if (c_have) P.end(c_r, sink, nS, nI, t_last);
+                c_r = (long long)__float_as_int(t);
+                t_last = near_arr ? __ldg(near_arr + c_r) : near_s;
+                continuous = false; capped = false; nS = 0; nI = 0;
+                sink = P.begin(c_r);
+                c_have = true;
+                continue;
+            }
+            if (capped) continue;
+            const bool emit = (kind == EV_OCC);
+            const bool doit = !(kind == EV_SEG && continuous);
+            if (step <= 0.0f) {  // one interval per occupied voxel crossing
+                if (!emit) {
+                    if (doit) t_last = t;
+                } else {
+                    sink.one(t_last, t, continuous, nS, nI);
+                    nI += continuous ? 1 : 2;
+                    nS += 1;
+                    continuous = true;
+                    t_last = t;
+                }
+            } else if (const_dt || !emit) {
+                if (doit) {
+                    const float dt = const_dt ? step : calc_dt(t_last, cone, step);
+                    if (emit) {
+                        t_last = advance(t_last, dt, t, cap, nS, [&](float t0, float q, int k) {
+                            sink.run(t0, q, k, continuous, nS, nI);
+                            nI += continuous ? k : k + 1;
+                            continuous = true;
+                        });
+                    } else {
+                        t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
+                    }
+                }
+            } else {  // cone_angle > 0: dt follows t, a true serial recurrence
+                while (nS < cap) {
+                    const float dt = calc_dt(t_last, cone, step);
+                    if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
+                    const float t_next = __fadd_rn(t_last, dt);
+                    if (!(t_next > t_last)) break;  // stuck
+                    sink.one(t_last, t_next, continuous, nS, nI);
+                    nI += continuous ? 1 : 2;
+                    nS += 1;
+                    continuous = true;
+                    t_last = t_next;
+                    if (t_next >= t) break;
+                }
+            }
+            if (kind == EV_EMPTY) continuous = false;
+            if (nS >= cap) {
+                capped = true;
+                if (have_ray && r == c_r) { have_ray = false; pend_kind = -1; }  // stop walking it
+            }
+        }
+        nq = 0;
+        kinds = 0;
+    };
+
     while (true) {
         // ------------------------------------------------------------------ refill
+        // (needs room for the EV_RAY marker and the first events of the ray)
 #pragma unroll 1
         for (int attempt = 0; attempt < 4; ++attempt) {
-            const bool need = !have_ray && !exhausted;
+            const bool need = !have_ray && !exhausted && nq <= kQ - 4;
             const unsigned mask = __ballot_sync(kFull, need);
             if (mask == 0u) break;
             unsigned long long base = 0;
@@ -317,6 +392,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     P.skipped(cand);
                 } else {
                     r = cand;
+                    float o[3], d[3], inv[3];
 #pragma unroll
                     for (int k = 0; k < 3; ++k) {
                         o[k] = __ldg(rays_o + 3 * r + k);
@@ -336,19 +412,21 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     } else {
                         compute_events(o, inv, G, ev);
                     }
-                    have_ray = true; prod_done = false; in_seg = false; seg_i = 0; pend_kind = -1; first_seg = true;
-                    t_last = near; continuous = false; capped = false; nS = 0; nI = 0;
-                    sink = P.begin(r);
+                    have_ray = true; in_seg = false; seg_i = 0; pend_kind = -1; first_seg = true;
+                    push(EV_RAY, __int_as_float((int)r));
                 }
             }
         }
         if (!__any_sync(kFull, have_ray)) {
-            if (__all_sync(kFull, exhausted)) break;
+            if (__all_sync(kFull, exhausted || nq > kQ - 4)) {
+                consume();
+                if (__all_sync(kFull, exhausted)) break;
+            }
             continue;
         }
         // ------------------------------------------------------------------ produce
         int steps = 0;
-        while (have_ray && !prod_done && steps < kRoundSteps && nq <= kQ - 2) {
+        while (have_ray && steps < kRoundSteps && nq <= kQ - 3) {
             if (!in_seg) {
                 // next ray/box segment (grid.cu:128-149)
                 bool found = false;
@@ -370,37 +448,40 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     found = true;
                     break;
                 }
-                if (!found) { push_pending(); prod_done = true; break; }
+                if (!found) { push_pending(); have_ray = false; break; }
                 // "if (!continuous) skip to tmin": right after the ray starts or after empty
                 // cells `continuous` is known to be false and the event is a plain skip
                 if (first_seg) {
                     pend_kind = EV_EMPTY; pend_t = tmin; first_seg = false;
-                } else if (pend_kind == EV_EMPTY && (const_dt || step <= 0.0f)) {
+                } else if (pend_kind == EV_EMPTY && fold_empty) {
                     pend_t = tmin;
                 } else {
                     push_pending();
                     push(EV_SEG, tmin);
                 }
-                // setup_traversal, utils_grid.cuh:58-114
+                // setup_traversal, utils_grid.cuh:58-114 (the ray is re-read: it is not kept in
+                // registers across the DDA loop)
                 const float* __restrict__ bb = G.aabbs + 6 * level;
                 const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax_seg, eps);
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
+                    const float ok = __ldg(rays_o + 3 * r + k), dk = __ldg(rays_d + 3 * r + k);
+                    const float invk = __fdiv_rn(1.0f, dk);
                     const float bmin = bb[k], bmax = bb[3 + k];
                     const float resf = (float)G.res[k];
                     const float ext = __fsub_rn(bmax, bmin);
                     const float vox = __fdiv_rn(ext, resf);
-                    const float rs = __fmaf_rn(d[k], ts, o[k]);  // FFMA site 1
-                    const float re = __fmaf_rn(d[k], te, o[k]);
+                    const float rs = __fmaf_rn(dk, ts, ok);  // FFMA site 1
+                    const float re = __fmaf_rn(dk, te, ok);
                     cur[k] = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(rs, bmin), ext), resf)), 0, G.res[k] - 1);
                     const int fin = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(re, bmin), ext), resf)), 0, G.res[k] - 1);
-                    const int start_index = cur[k] + (d[k] > 0.0f ? 1 : 0);
+                    const int start_index = cur[k] + (dk > 0.0f ? 1 : 0);
                     // FFMA site 2: fma(bmin + fma(float(idx), vox, -rs), inv, tmin)
-                    const float tm = __fmaf_rn(__fadd_rn(bmin, __fmaf_rn((float)start_index, vox, -rs)), inv[k], tmin);
-                    const float sf = (d[k] == 0.0f) ? 0.0f : (d[k] > 0.0f ? 1.0f : -1.0f);
-                    tdist[k] = (d[k] == 0.0f) ? tmax_seg : tm;
+                    const float tm = __fmaf_rn(__fadd_rn(bmin, __fmaf_rn((float)start_index, vox, -rs)), invk, tmin);
+                    const float sf = (dk == 0.0f) ? 0.0f : (dk > 0.0f ? 1.0f : -1.0f);
+                    tdist[k] = (dk == 0.0f) ? tmax_seg : tm;
                     stepi[k] = (int)sf;
-                    delta[k] = (d[k] == 0.0f) ? tmax_seg : __fmul_rn(__fmul_rn(vox, inv[k]), sf);
+                    delta[k] = (dk == 0.0f) ? tmax_seg : __fmul_rn(__fmul_rn(vox, invk), sf);
                     // The walk leaves when the index reaches fin + step (utils_grid.cuh:123) or the
                     // grid edge, whichever lies ahead: one stop value per axis.
                     const int ovf = fin + stepi[k];
@@ -416,97 +497,42 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 seg_steps = 0;
                 continue;
             }
-            // one DDA cell (grid.cu:183-281), branch-free
-            const float t_trav = fminf(fminf(tdist[0], fminf(tdist[1], tdist[2])), tmax_seg);
-            uint32_t cbit = 1u;
-            if (G.mip != nullptr) {
-                const int ci = mip_base + ((cur[0] >> G.mip_shift) * G.mres[1] + (cur[1] >> G.mip_shift)) * G.mres[2] +
-                               (cur[2] >> G.mip_shift);
-                cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
-            }
-            // fine bit, fetched only under a set mip bit (predicated load: no divergent section)
-            uint32_t word;
-            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\tmov.u32 %0, 0;\n\t"
-                         "@p ld.global.nc.u32 %0, [%2];\n\t}"
-                         : "=r"(word) : "r"(cbit), "l"(G.occ_bits + (cell >> 5)));
-            const int kind = (int)((word >> (cell & 31)) & 1u);  // EV_OCC == 1, EV_EMPTY == 0
-            // folding: constant dt — same kind; per-voxel mode — empties only; cone — never
-            const bool fold = (kind == pend_kind) && (const_dt || (step <= 0.0f && kind == EV_EMPTY));
-            if (!fold) { push_pending(); pend_kind = kind; }
-            pend_t = t_trav;
-            // single_traversal, utils_grid.cuh:116-142: x if strictly smallest, else y if < z, else z
-            const bool px = tdist[0] < tdist[1] && tdist[0] < tdist[2];
-            const bool py = !px && tdist[1] < tdist[2];
-            const bool pz = !px && !py;
-            cur[0] += px ? stepi[0] : 0;
-            cur[1] += py ? stepi[1] : 0;
-            cur[2] += pz ? stepi[2] : 0;
-            tdist[0] = px ? __fadd_rn(tdist[0], delta[0]) : tdist[0];
-            tdist[1] = py ? __fadd_rn(tdist[1], delta[1]) : tdist[1];
-            tdist[2] = pz ? __fadd_rn(tdist[2], delta[2]) : tdist[2];
-            cell += px ? cstride[0] : (py ? cstride[1] : cstride[2]);
-            const bool leave = (px && cur[0] == stop[0]) || (py && cur[1] == stop[1]) || (pz && cur[2] == stop[2]);
-            if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
-            ++steps;
+            // the DDA proper (grid.cu:183-281), branch-free; leaves the loop when the segment
+            // ends, the round is over or the queue is (nearly) full
+            do {
+                const float t_trav = fminf(fminf(tdist[0], fminf(tdist[1], tdist[2])), tmax_seg);
+                uint32_t cbit = 1u;
+                if (MIP) {
+                    const int ci = mip_base + ((cur[0] >> G.mip_shift) * G.mres[1] + (cur[1] >> G.mip_shift)) * G.mres[2] +
+                                   (cur[2] >> G.mip_shift);
+                    cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
+                }
+                // fine bit, fetched only under a set mip bit
+                uint32_t word = 0u;
+                if (cbit) word = __ldg(G.occ_bits + (cell >> 5));
+                const int kind = (int)((word >> (cell & 31)) & 1u);  // EV_OCC == 1, EV_EMPTY == 0
+                if (kind != pend_kind || !(kind == EV_OCC ? fold_occ : fold_empty)) { push_pending(); pend_kind = kind; }
+                pend_t = t_trav;
+                // single_traversal, utils_grid.cuh:116-142: x if strictly smallest, else y if < z, else z
+                const bool px = tdist[0] < tdist[1] && tdist[0] < tdist[2];
+                const bool py = !px && tdist[1] < tdist[2];
+                const bool pz = !px && !py;
+                cur[0] += px ? stepi[0] : 0;
+                cur[1] += py ? stepi[1] : 0;
+                cur[2] += pz ? stepi[2] : 0;
+                tdist[0] = px ? __fadd_rn(tdist[0], delta[0]) : tdist[0];
+                tdist[1] = py ? __fadd_rn(tdist[1], delta[1]) : tdist[1];
+                tdist[2] = pz ? __fadd_rn(tdist[2], delta[2]) : tdist[2];
+                cell += px ? cstride[0] : (py ? cstride[1] : cstride[2]);
+                const bool leave = (px && cur[0] == stop[0]) || (py && cur[1] == stop[1]) || (pz && cur[2] == stop[2]);
+                if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
+                ++steps;
+            } while (in_seg && steps < kRoundSteps && nq <= kQ - 3);
         }
         // ------------------------------------------------------------------ consume
-        const int maxq = __reduce_max_sync(kFull, nq);
-#pragma unroll 1
-        for (int j = 0; j < maxq; ++j) {
-            if (j < nq && !capped) {
-                const int kind = (int)((kinds >> (2 * j)) & 3u);
-                const float t = s_evt[j * nthr + tid];
-                const bool emit = (kind == EV_OCC);
-                const bool doit = !(kind == EV_SEG && continuous);
-                if (step <= 0.0f) {  // one interval per occupied voxel crossing
-                    if (!emit) {
-                        if (doit) t_last = t;
-                    } else {
-                        sink.one(t_last, t, continuous, nS, nI);
-                        nI += continuous ? 1 : 2;
-                        nS += 1;
-                        continuous = true;
-                        t_last = t;
-                    }
-                } else if (const_dt || !emit) {
-                    if (doit) {
-                        const float dt = const_dt ? step : calc_dt(t_last, cone, step);
-                        if (emit) {
-                            t_last = advance(t_last, dt, t, cap, nS, [&](float t0, float q, int k) {
-                                sink.run(t0, q, k, continuous, nS, nI);
-                                nI += continuous ? k : k + 1;
-                                continuous = true;
-                            });
-                        } else {
-                            t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
-                        }
-                    }
-                } else {  // cone_angle > 0: dt follows t, a true serial recurrence
-                    while (nS < cap) {
-                        const float dt = calc_dt(t_last, cone, step);
-                        if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
-                        const float t_next = __fadd_rn(t_last, dt);
-                        if (!(t_next > t_last)) break;  // stuck
-                        sink.one(t_last, t_next, continuous, nS, nI);
-                        nI += continuous ? 1 : 2;
-                        nS += 1;
-                        continuous = true;
-                        t_last = t_next;
-                        if (t_next >= t) break;
-                    }
-                }
-                if (kind == EV_EMPTY) continuous = false;
-                if (nS >= cap) { capped = true; prod_done = true; pend_kind = -1; }
-            }
-        }
-        nq = 0;
-        kinds = 0;
-        // ------------------------------------------------------------------ retire
-        if (have_ray && prod_done && pend_kind < 0) {
-            P.end(r, sink, nS, nI, t_last);
-            have_ray = false;
-        }
+        if (eager || __any_sync(kFull, nq > kQ - 6)) consume();
     }
+    if (c_have) P.end(c_r, sink, nS, nI, t_last);
 }
 
 }  // namespace nfb
