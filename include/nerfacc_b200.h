@@ -293,6 +293,36 @@ NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
                                 int64_t* total, void* workspace, size_t workspace_bytes,
                                 nfb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * Inverse-CDF resampling and per-ray search (nerfacc/cuda/csrc/pdf.cu).
+ */
+/* importance_sampling: replaces csrc/pdf.cu:294-456 (the three host overloads) and their kernels
+ * importance_sampling_kernel (pdf.cu:98-167) + compute_intervels_kernel (pdf.cu:169-241).
+ * For each ray draws n_out sample centres u_k = cdf_first + (k + bias) * (cdf_last-cdf_first)/n_out
+ * through the piecewise-linear inverse of (vals, cdfs) and, when out_edges != NULL, the n_out+1
+ * interval edges (midpoints of neighbouring centres, clamped to the ray's first / last edge).
+ *   input rows : in_info == NULL -> [n_rays, n_in] batched;  else packed chunks (start,count) int64
+ *   output rows: n_out_per_ray == NULL -> [n_rays, n_out] centres, [n_rays, n_out+1] edges;
+ *                else per-ray counts with packed chunks edge_info / sample_info ([n_rays,2] int64)
+ *   bias       : per-ray offset in (0,1] (the reference's `1 - curand_uniform`, drawn by the
+ *                caller), or NULL for the unstratified 0.5
+ *   max_in / max_out: upper bounds of the per-ray counts (size shared-memory staging; 0 = unknown,
+ *                search in global memory). */
+NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const int64_t* in_info,
+                                    int64_t n_rays, int64_t n_in, int64_t max_in,
+                                    const int64_t* n_out_per_ray, int64_t n_out, int64_t max_out,
+                                    const int64_t* edge_info, const int64_t* sample_info,
+                                    const float* bias, float* out_edges, float* out_centres,
+                                    nfb_stream_t stream);
+/* searchsorted: replaces csrc/pdf.cu:245-286 + 458-503.  For every query value the pair of
+ * neighbouring key positions (ids_left, ids_right) with key[left] <= v < key[right], clamped to
+ * the row.  Batched query (q_info == NULL): ids are relative to the key row; packed query:
+ * absolute positions in key.  q_info / k_info: packed chunks, or NULL for rows of n_q / n_k. */
+NFB_API int nfb_searchsorted(const float* query, const int64_t* q_info, int64_t n_q,
+                             const float* key, const int64_t* k_info, int64_t n_k, int64_t max_k,
+                             int64_t n_rays, int64_t* ids_left, int64_t* ids_right,
+                             nfb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -90,6 +90,9 @@ _PROTOS = {
     "nfb_compact_workspace_bytes": [c_i64],
     "nfb_compact_samples": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                             c_size, c_ptr],
+    "nfb_importance_sampling": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr,
+                                c_ptr, c_ptr, c_ptr, c_ptr],
+    "nfb_searchsorted": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "nfb_traverse_fill": [_sp(Rays), _sp(Grid), _sp(March), c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                           c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
 }

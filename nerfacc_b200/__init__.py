@@ -2,8 +2,10 @@
 nerfacc's own Python API (reference nerfacc/__init__.py:23-46).  No CPU fallback for packed ops."""
 from .data_specs import RayIntervals, RaySamples
 from .estimators.occ_grid import OccGridEstimator
+from .estimators.prop_net import PropNetEstimator
 from .grid import ray_aabb_intersect, traverse_grids
 from .pack import pack_info
+from .pdf import importance_sampling, searchsorted
 from .scan import exclusive_prod, exclusive_sum, inclusive_prod, inclusive_sum
 from .version import __version__
 from .volrend import (

@@ -1,0 +1,235 @@
+// pdf.cu — inverse-CDF importance sampling and per-ray searchsorted behind the C ABI.
+//
+// Replaces csrc/pdf.cu of the reference: importance_sampling_kernel + compute_intervels_kernel
+// (pdf.cu:98-241, one thread per output sample, a global-memory binary search each, and a second
+// kernel that re-reads the samples to make the edges) and searchsorted_kernel (pdf.cu:245-286).
+// Here one WARP owns a ray:
+//   * the ray's CDF and edge rows are staged once in shared memory (coalesced), every search
+//     runs there;
+//   * the sample centres go to shared memory as well, so the interval edges (midpoints of
+//     neighbouring centres, clamped to the ray's first / last edge) come out of the same kernel;
+//   * outputs are written as coalesced rows.
+// Arithmetic is spelled with round-to-nearest intrinsics exactly as nvcc compiles the reference
+// (u = fma(sid + bias, u_step, u_floor), t = fma(u - u_lower, scaling, t_lower), IEEE divisions,
+// the 1e-10 degenerate-bin rule of pdf.cu:159-160), so positions agree to the last bit where the
+// reference is well defined.
+#include "common.cuh"
+
+namespace nfb {
+
+constexpr int kPdfWarps = 8;
+
+// first index in [lo, hi) whose value is > val (pdf.cu:44-63), on any pointer
+__device__ __forceinline__ int upper_bound(const float* data, int lo, int hi, float val) {
+    while (lo < hi) {
+        const int mid = lo + ((hi - lo) >> 1);
+        if (!(data[mid] > val)) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+struct PdfArgs {
+    const float* vals;            // input edges: [n_rays, n_in] or packed
+    const float* cdfs;            // same layout
+    const int64_t* in_info;       // packed input chunks or nullptr (batched, n_in per ray)
+    long long n_in;               // batched row length
+    const int64_t* n_out_per_ray; // optional per-ray sample counts (packed output), else n_out
+    long long n_out;
+    const int64_t* edge_info;     // packed output chunks (with n_out_per_ray), else rows of n_out+1
+    const int64_t* sample_info;   //                                            else rows of n_out
+    const float* bias;            // per-ray stratification offset in (0,1], or nullptr = 0.5
+    float* out_edges;             // may be nullptr
+    float* out_centres;
+    long long n_rays;
+    int smem_floats_per_warp;     // staging capacity; longer rows are searched in global memory
+};
+
+__global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_kernel(const PdfArgs p) {
+    extern __shared__ float s_pdf[];
+    const int lane = lane_id(), w = warp_id();
+    float* s_row = s_pdf + (size_t)w * p.smem_floats_per_warp;
+    for (long long r = (long long)blockIdx.x * kPdfWarps + w; r < p.n_rays;
+         r += (long long)gridDim.x * kPdfWarps) {
+        long long in0, cnt;
+        if (p.in_info) { const RayChunk c = load_chunk(p.in_info, r); in0 = c.start; cnt = c.cnt; }
+        else { in0 = r * p.n_in; cnt = p.n_in; }
+        long long e0, s0;
+        int n_out;
+        if (p.n_out_per_ray) {
+            n_out = (int)p.n_out_per_ray[r];
+            e0 = p.edge_info[2 * r];
+            s0 = p.sample_info[2 * r];
+        } else {
+            n_out = (int)p.n_out;
+            e0 = r * (p.n_out + 1);
+            s0 = r * p.n_out;
+        }
+        if (cnt <= 0 || n_out <= 0) continue;
+        const int n_in = (int)cnt, last = n_in - 1;
+        // stage the rows: [cdfs n_in][vals n_in][centres n_out]
+        const bool staged = 2 * n_in + n_out <= p.smem_floats_per_warp;
+        const float* cdf = p.cdfs + in0;
+        const float* val = p.vals + in0;
+        float* cen = nullptr;
+        if (staged) {
+            for (int i = lane; i < n_in; i += 32) { s_row[i] = __ldg(cdf + i); s_row[n_in + i] = __ldg(val + i); }
+            __syncwarp();
+            cdf = s_row; val = s_row + n_in; cen = s_row + 2 * n_in;
+        }
+        const float u_floor = cdf[0], u_ceil = cdf[last];
+        const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
+        const float b = p.bias ? __ldg(p.bias + r) : 0.5f;
+        const float t_min = val[0], t_max = val[last];
+        for (int sid = lane; sid < n_out; sid += 32) {
+            const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
+            const int q = upper_bound(cdf, 0, last, u);
+            const int p0 = max(min(q - 1, last), 0), p1 = max(min(q, last), 0);
+            const float u_lower = cdf[p0], u_upper = cdf[p1], t_lower = val[p0], t_upper = val[p1];
+            float t;
+            if (__fsub_rn(u_upper, u_lower) < 1e-10f) {
+                t = __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f);
+            } else {
+                const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), __fsub_rn(u_upper, u_lower));
+                t = __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
+            }
+            p.out_centres[s0 + sid] = t;
+            if (cen) cen[sid] = t;
+        }
+        if (p.out_edges == nullptr) { __syncwarp(); continue; }
+        __syncwarp();  // centres visible (shared memory, or this warp's own global writes)
+        const float* c = cen ? cen : p.out_centres + s0;
+        // compute_intervels_kernel, pdf.cu:169-241
+        for (int sid = lane; sid < n_out; sid += 32) {
+            if (sid == 0) {
+                const float t = c[0], t_next = n_out > 1 ? c[1] : c[0];
+                const float half = __fmul_rn(__fsub_rn(t_next, t), 0.5f);
+                p.out_edges[e0] = fmaxf(__fsub_rn(t, half), t_min);
+                if (n_out == 1) p.out_edges[e0 + 1] = fminf(__fadd_rn(t, half), t_max);
+            } else {
+                const float t = c[sid], t_prev = c[sid - 1];
+                p.out_edges[e0 + sid] = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                if (sid == n_out - 1) {
+                    const float half = __fmul_rn(__fsub_rn(t, t_prev), 0.5f);
+                    p.out_edges[e0 + sid + 1] = fminf(__fadd_rn(t, half), t_max);
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+struct SearchArgs {
+    const float* query; const int64_t* q_info; long long n_q;   // packed (q_info) or batched
+    const float* key; const int64_t* k_info; long long n_k;
+    int64_t* ids_left; int64_t* ids_right;
+    long long n_rays;
+    int smem_floats_per_warp;
+};
+
+__global__ void __launch_bounds__(kPdfWarps * 32) searchsorted_kernel(const SearchArgs p) {
+    extern __shared__ float s_pdf[];
+    const int lane = lane_id(), w = warp_id();
+    float* s_row = s_pdf + (size_t)w * p.smem_floats_per_warp;
+    for (long long r = (long long)blockIdx.x * kPdfWarps + w; r < p.n_rays;
+         r += (long long)gridDim.x * kPdfWarps) {
+        long long k0, kc, q0, qc;
+        if (p.k_info) { const RayChunk c = load_chunk(p.k_info, r); k0 = c.start; kc = c.cnt; }
+        else { k0 = r * p.n_k; kc = p.n_k; }
+        if (p.q_info) { const RayChunk c = load_chunk(p.q_info, r); q0 = c.start; qc = c.cnt; }
+        else { q0 = r * p.n_q; qc = p.n_q; }
+        if (qc <= 0) continue;
+        const int n_k = (int)kc, last = n_k - 1;
+        const float* key = p.key + k0;
+        if (n_k > 0 && n_k <= p.smem_floats_per_warp) {
+            for (int i = lane; i < n_k; i += 32) s_row[i] = __ldg(key + i);
+            __syncwarp();
+            key = s_row;
+        }
+        // batched query: ids relative to the key row; packed query: absolute positions (pdf.cu:278-284)
+        const long long off = p.q_info ? k0 : 0;
+        for (long long i = lane; i < qc; i += 32) {
+            const float v = __ldg(p.query + q0 + i);
+            const int q = (n_k > 0) ? upper_bound(key, 0, last, v) : 0;
+            const int l = max(min(q - 1, last), 0), h = max(min(q, last), 0);
+            p.ids_left[q0 + i] = off + l;
+            p.ids_right[q0 + i] = off + h;
+        }
+        __syncwarp();
+    }
+}
+
+static inline unsigned pdf_blocks(long long n_rays) {
+    long long b = ceil_div<long long>(n_rays, kPdfWarps);
+    const long long cap = (long long)sm_count() * 8;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (unsigned)b;
+}
+
+// shared-memory floats per warp: what the longest row needs when the caller knows it, a 6 KiB
+// default otherwise, capped so that 8 warps stay under 96 KiB (2 CTAs/SM).  Rows that do not fit
+// are searched in global memory (the kernels decide per ray).
+static inline int pdf_smem_floats(long long want) {
+    const long long cap = (96 * 1024) / (kPdfWarps * 4);
+    if (want <= 0) return 1536;
+    return (int)(want <= cap ? want : cap);
+}
+
+}  // namespace nfb
+
+extern "C" {
+
+NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const int64_t* in_info,
+                                    int64_t n_rays, int64_t n_in, int64_t max_in,
+                                    const int64_t* n_out_per_ray, int64_t n_out, int64_t max_out,
+                                    const int64_t* edge_info, const int64_t* sample_info,
+                                    const float* bias, float* out_edges, float* out_centres,
+                                    nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_rays >= 0, "negative size");
+    if (n_rays == 0) return NFB_OK;
+    NFB_CHECK_ARG(vals && cdfs && out_centres, "null pointer");
+    NFB_CHECK_ARG(in_info != nullptr || n_in > 0, "need in_info or n_in");
+    NFB_CHECK_ARG(in_info == nullptr || aligned16(in_info), "packed_info must be 16-byte aligned");
+    if (n_out_per_ray) NFB_CHECK_ARG(edge_info && sample_info, "per-ray counts need edge_info and sample_info");
+    else NFB_CHECK_ARG(n_out > 0, "n_out must be positive");
+    PdfArgs a{};
+    a.vals = vals; a.cdfs = cdfs; a.in_info = in_info; a.n_in = n_in;
+    a.n_out_per_ray = n_out_per_ray; a.n_out = n_out; a.edge_info = edge_info; a.sample_info = sample_info;
+    a.bias = bias; a.out_edges = out_edges; a.out_centres = out_centres; a.n_rays = n_rays;
+    const long long mi = in_info ? max_in : n_in, mo = n_out_per_ray ? max_out : n_out;
+    a.smem_floats_per_warp = pdf_smem_floats((mi > 0 && mo > 0) ? 2 * mi + mo : 0);
+    const size_t smem = (size_t)a.smem_floats_per_warp * 4 * kPdfWarps;
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(importance_sampling_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    importance_sampling_kernel<<<pdf_blocks(n_rays), kPdfWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("importance_sampling");
+    return NFB_OK;
+}
+
+NFB_API int nfb_searchsorted(const float* query, const int64_t* q_info, int64_t n_q,
+                             const float* key, const int64_t* k_info, int64_t n_k, int64_t max_k,
+                             int64_t n_rays, int64_t* ids_left, int64_t* ids_right,
+                             nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_rays >= 0, "negative size");
+    if (n_rays == 0) return NFB_OK;
+    NFB_CHECK_ARG(query && key && ids_left && ids_right, "null pointer");
+    NFB_CHECK_ARG((q_info == nullptr || aligned16(q_info)) && (k_info == nullptr || aligned16(k_info)),
+                  "packed_info must be 16-byte aligned");
+    SearchArgs a{};
+    a.query = query; a.q_info = q_info; a.n_q = n_q; a.key = key; a.k_info = k_info; a.n_k = n_k;
+    a.ids_left = ids_left; a.ids_right = ids_right; a.n_rays = n_rays;
+    const long long mk = k_info ? max_k : n_k;
+    a.smem_floats_per_warp = pdf_smem_floats(mk);
+    const size_t smem = (size_t)a.smem_floats_per_warp * 4 * kPdfWarps;
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(searchsorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    searchsorted_kernel<<<pdf_blocks(n_rays), kPdfWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("searchsorted");
+    return NFB_OK;
+}
+
+}  // extern "C"

@@ -1,4 +1,5 @@
 from .base import AbstractEstimator
 from .occ_grid import OccGridEstimator
+from .prop_net import PropNetEstimator
 
-__all__ = ["AbstractEstimator", "OccGridEstimator"]
+__all__ = ["AbstractEstimator", "OccGridEstimator", "PropNetEstimator"]

@@ -122,3 +122,36 @@ def test_ray_aabb_vs_reference_cuda(ref, device):
         b = ref.ray_aabb_intersect(o, d, bb, *args)
         for x, y in zip(a, b):
             assert torch.equal(x, y)
+
+
+def test_pdf_vs_reference_cuda(ref, device):
+    """importance_sampling (batched + packed input) and searchsorted at 2^15 rays."""
+    import nerfacc_b200 as nf
+
+    g0 = torch.Generator(device=device).manual_seed(17)
+    n_rays, n_in, n_out = 1 << 15, 65, 48
+    vals = torch.sort(torch.rand((n_rays, n_in), device=device, generator=g0) * 8 + 0.1, dim=-1).values
+    w = torch.rand((n_rays, n_in - 1), device=device, generator=g0)
+    w = w * (torch.rand((n_rays, n_in - 1), device=device, generator=g0) > 0.2) + 1e-4
+    cdf = torch.cat([torch.zeros((n_rays, 1), device=device), torch.cumsum(w, -1)], -1)
+    cdf = cdf / cdf[:, -1:]
+    iv, sm = nf.importance_sampling(nf.RayIntervals(vals=vals), cdf, n_out)
+    e_ref, c_ref = ref.importance_sampling(vals, cdf, n_out)
+    assert torch.equal(sm.vals, c_ref)
+    assert torch.equal(iv.vals, e_ref)
+    q = torch.rand((n_rays, 37), device=device, generator=g0) * 9
+    l, r = nf.searchsorted(nf.RayIntervals(vals=vals), nf.RayIntervals(vals=q))
+    l_ref, r_ref = ref.searchsorted(vals, q)
+    assert torch.equal(l, l_ref) and torch.equal(r, r_ref)
+    # packed key + packed query
+    kc = torch.randint(1, 80, (n_rays,), device=device, generator=g0)
+    qc = torch.randint(0, 40, (n_rays,), device=device, generator=g0)
+    ki = torch.stack([torch.cumsum(kc, 0) - kc, kc], -1)
+    qi = torch.stack([torch.cumsum(qc, 0) - qc, qc], -1)
+    kv = torch.rand(int(kc.sum()), device=device, generator=g0)
+    rid = torch.repeat_interleave(torch.arange(n_rays, device=device), kc)
+    kv = torch.sort(kv + rid.float() * 2)[0] - rid.float() * 2  # sorted within each ray
+    qv = torch.rand(int(qc.sum()), device=device, generator=g0) * 1.2 - 0.1
+    l, r = nf.searchsorted(nf.RaySamples(vals=kv, packed_info=ki), nf.RaySamples(vals=qv, packed_info=qi))
+    l_ref, r_ref = ref.searchsorted(kv, qv, ki, qi)
+    assert torch.equal(l, l_ref) and torch.equal(r, r_ref)
