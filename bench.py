@@ -215,6 +215,20 @@ ALGO_BYTES = {
 }
 
 
+def aggregate_over_ranks(ms_local: float, units_local: int, dist, device):
+    """(MAX over ranks of a timed region in ms, SUM over ranks of the units processed in it) —
+    the whole-job figures of the bench contract.  `dist` = torch.distributed or None (one rank)."""
+    if dist is None:
+        return float(ms_local), int(units_local)
+    import torch
+
+    t = torch.tensor([ms_local], device=device, dtype=torch.float64)
+    u = torch.tensor([units_local], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(u, op=dist.ReduceOp.SUM)
+    return float(t.item()), int(u.item())
+
+
 def run_ours(args) -> None:
     import torch
 
@@ -289,12 +303,7 @@ def run_ours(args) -> None:
             fn()
         e1.record()
         barrier()
-        ms = e0.elapsed_time(e1)
-        if dist is not None:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+        return aggregate_over_ranks(e0.elapsed_time(e1), 0, dist, dev)[0]
 
     for _ in range(max(args.warmup, 3)):
         step(o_dev, d_dev)
@@ -312,11 +321,7 @@ def run_ours(args) -> None:
     ms_e2e = timed(step_e2e, args.steps)
     clk = clocks.stop() if rank == 0 else None
 
-    S_all = S
-    if dist is not None:
-        t = torch.tensor([S], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        S_all = int(t.item())
+    S_all = aggregate_over_ranks(0.0, S, dist, dev)[1]
     value = S_all * args.steps / (ms * 1e-3) / 1e9
     e2e_value = S_all * args.steps / (ms_e2e * 1e-3) / 1e9
 
