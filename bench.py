@@ -212,6 +212,10 @@ ALGO_BYTES = {
     "composite_fwd": lambda S, R, B: 24 * S + 16 * R + 20 * R,   # read w, rgb, ts, te; write 5 floats/ray
     "composite_bwd": lambda S, R, B: 52 * S + 16 * R + 20 * R,   # read ts,te,sigma,rgb,T,ray_idx; write g_sigma,g_rgb
     "pack_info": lambda S, R, B: 8 * S + 16 * R,
+    # per-ray fused rendering: read ts,te,sigma,rgb (24) write w,T,alpha (12) + 5 floats/ray
+    "render_rays_fwd": lambda S, R, B: 36 * S + 16 * R + 20 * R,
+    # read ts,te,sigma,rgb,T (28) write g_sigma,g_rgb (16) + 5 floats/ray
+    "render_rays_bwd": lambda S, R, B: 44 * S + 16 * R + 20 * R,
 }
 
 
@@ -266,7 +270,6 @@ def run_ours(args) -> None:
     g_c = torch.rand((n_rays, 3), device=dev, generator=gen)
     g_o = torch.rand((n_rays, 1), device=dev, generator=gen)
     g_d = torch.rand((n_rays, 1), device=dev, generator=gen)
-    out_host = torch.empty((n_rays, 5), dtype=torch.float32).pin_memory()
     del ri, ts, te
 
     def field(t_starts, t_ends, ray_indices):
@@ -281,14 +284,62 @@ def run_ours(args) -> None:
         torch.autograd.backward([colors, opac, depth], [g_c, g_o, g_d])
         return colors, opac, depth
 
+    # ---- e2e: the same work through the public API from PINNED HOST rays, pipelined the way a
+    # caller streams ray batches: `e2e_chunks` blocks of rays; H2D copies, compute and the D2H
+    # copies of colours/opacity/depth run on three streams and overlap across blocks.
+    n_chunks = max(1, min(args.e2e_chunks, n_rays))
+    cuts = [n_rays * i // n_chunks for i in range(n_chunks + 1)]
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    o_buf = [torch.empty((cuts[i + 1] - cuts[i], 3), device=dev) for i in range(n_chunks)]
+    d_buf = [torch.empty((cuts[i + 1] - cuts[i], 3), device=dev) for i in range(n_chunks)]
+    host_c = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
+    host_o = torch.empty((n_rays, 1), dtype=torch.float32).pin_memory()
+    host_d = torch.empty((n_rays, 1), dtype=torch.float32).pin_memory()
+    sig_c, rgb_c, s_cuts = [], [], [0]
+    with torch.no_grad():
+        for i in range(n_chunks):
+            a, b = cuts[i], cuts[i + 1]
+            ri_i, _, _ = est.sampling(o_dev[a:b], d_dev[a:b], render_step_size=STEP_SIZE)
+            s_cuts.append(s_cuts[-1] + int(ri_i.shape[0]))
+            del ri_i
+    assert s_cuts[-1] == S, "chunked marching must give the same samples"
+    for i in range(n_chunks):
+        sig_c.append(sigmas.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
+        rgb_c.append(rgbs.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
+
     def step_e2e():
-        o = o_host.to(dev, non_blocking=True)
-        d = d_host.to(dev, non_blocking=True)
-        colors, opac, depth = step(o, d)
-        out_host[:, 0:3].copy_(colors.detach(), non_blocking=True)
-        out_host[:, 3:4].copy_(opac.detach(), non_blocking=True)
-        out_host[:, 4:5].copy_(depth.detach(), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        main = torch.cuda.current_stream(dev)
+        s_in.wait_stream(main)
+        ready = []
+        with torch.cuda.stream(s_in):
+            for i in range(n_chunks):
+                a, b = cuts[i], cuts[i + 1]
+                o_buf[i].copy_(o_host[a:b], non_blocking=True)
+                d_buf[i].copy_(d_host[a:b], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(s_in)
+                ready.append(ev)
+        keep = []
+        for i in range(n_chunks):
+            a, b = cuts[i], cuts[i + 1]
+            main.wait_event(ready[i])
+            sig_c[i].grad = None
+            rgb_c[i].grad = None
+            ri, ts, te = est.sampling(o_buf[i], d_buf[i], render_step_size=STEP_SIZE)
+            colors, opac, depth, _ = nf.rendering(
+                ts, te, ri, b - a, rgb_sigma_fn=lambda t0, t1, r, i=i: (rgb_c[i], sig_c[i]))
+            torch.autograd.backward([colors, opac, depth], [g_c[a:b], g_o[a:b], g_d[a:b]])
+            done = torch.cuda.Event()
+            done.record(main)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done)
+                host_c[a:b].copy_(colors.detach(), non_blocking=True)
+                host_o[a:b].copy_(opac.detach(), non_blocking=True)
+                host_d[a:b].copy_(depth.detach(), non_blocking=True)
+            keep.append((colors, opac, depth))
+        s_out.synchronize()
+        main.synchronize()
+        del keep
 
     def barrier():
         if dist is not None:
@@ -376,7 +427,10 @@ def run_ours(args) -> None:
                    f"{S * 16 / 1e6:.0f} MB march output, {S * 44 / 1e6:.0f} MB render inputs/outputs)",
                    "parallelism": f"rays sharded x{world}, grid replicated, no data-path collective"},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": 2 * n_rays * 12 * world, "d2h_bytes_per_step": n_rays * 20 * world},
+                "h2d_bytes_per_step": 2 * n_rays * 12 * world, "d2h_bytes_per_step": n_rays * 20 * world,
+                "pipeline": f"{n_chunks} ray blocks/step through OccGridEstimator.sampling + rendering + backward; "
+                            "pinned-host rays in, colours/opacity/depth out to pinned host, every step; "
+                            "H2D / compute / D2H on three streams"},
         "gpu_launches": launches,
         "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu, "clocks": clk,
     }
@@ -392,8 +446,10 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU")
-    ap.add_argument("--cpu-rays", type=int, default=1 << 16, help="rays per step of the CPU sample")
+    ap.add_argument("--cpu-rays", type=int, default=1 << 17, help="rays per step of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=2,
+                    help="ray blocks per step of the end-to-end leg (copies overlap compute across blocks)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -294,6 +294,30 @@ NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
                                 nfb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * nerfacc.rendering() for packed rays in one forward and one backward kernel (a group of
+ * `lanes_per_ray` lanes walks one ray; 0 = choose from the mean count; else 4, 8, 16 or 32).
+ * Forward replaces render_weight_from_density/alpha + 3x accumulate_along_rays
+ * (nerfacc/volrend.py:116-150): writes weights, trans (+ alphas_out in density mode) per sample
+ * and colors [n_rays,3] = sum w*rgb, opacity [n_rays] = sum w, depth [n_rays] = sum w*(ts+te)/2
+ * per ray (rows of empty rays are zero).  `packed_info` may be any non-overlapping chunks.
+ * Backward is what autograd derives from that composition (see nfb_composite_bwd); it needs no
+ * ray_indices.  Same results as nfb_render_weight_fwd + nfb_composite_fwd / nfb_composite_bwd
+ * up to fp32 summation order. */
+NFB_API int nfb_render_rays_fwd(int from_density, const float* alphas, const float* t_starts,
+                                const float* t_ends, const float* sigmas, const float* rgbs,
+                                const int64_t* packed_info, int64_t n_rays, int64_t n,
+                                float* weights, float* trans, float* alphas_out, float* colors,
+                                float* opacity, float* depth, int lanes_per_ray,
+                                nfb_stream_t stream);
+NFB_API int nfb_render_rays_bwd(int from_density, const float* g_colors, const float* g_opacity,
+                                const float* g_depth, const float* g_weights, const float* g_trans,
+                                const float* g_alphas, const float* alphas, const float* t_starts,
+                                const float* t_ends, const float* sigmas, const float* rgbs,
+                                const float* trans, const int64_t* packed_info, int64_t n_rays,
+                                int64_t n, float* g_in, float* g_rgbs, int lanes_per_ray,
+                                nfb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * Inverse-CDF resampling and per-ray search (nerfacc/cuda/csrc/pdf.cu).
  */
 /* importance_sampling: replaces csrc/pdf.cu:294-456 (the three host overloads) and their kernels

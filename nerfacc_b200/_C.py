@@ -73,6 +73,10 @@ _PROTOS = {
     "nfb_composite_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                           c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_size, c_u32,
                           c_ptr],
+    "nfb_render_rays_fwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr,
+                            c_ptr, c_ptr, c_ptr, c_int, c_ptr],
+    "nfb_render_rays_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                            c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_int, c_ptr],
     "nfb_pack_info": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_ray_aabb_intersect": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_f32, c_f32, c_ptr, c_ptr,
                                c_ptr, c_ptr],

@@ -7,6 +7,7 @@ or `uniform_len` (batched [..., n] tensors flattened, every row one segment).
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -189,10 +190,22 @@ class Accumulate(torch.autograd.Function):
 
 
 # ----------------------------------------------------------------------------- rendering()
+# Mean samples per ray up to which rendering() uses the per-ray kernels (a group of lanes walks
+# one ray); above it the flat tile kernels, whose cost does not depend on how the samples are
+# distributed over the rays.  NFB_RAYS_L forces the lanes per ray (4/8/16/32) for experiments.
+_PER_RAY_MAX_MEAN = 512
+_RAYS_L = int(os.environ.get("NFB_RAYS_L", "0"))
+
+
+def _per_ray_kernels(n: int, n_rays: int) -> bool:
+    return n_rays > 0 and n <= _PER_RAY_MAX_MEAN * n_rays
+
+
 class RenderComposite(torch.autograd.Function):
-    """rendering() of volrend.py:14-158 for flattened CUDA inputs, in three kernels:
-    weights forward (nfb_render_weight_fwd), composite forward (nfb_composite_fwd) and ONE
-    backward (nfb_composite_bwd) down to d/d field and d/d rgbs.
+    """rendering() of volrend.py:14-158 for flattened CUDA inputs: one forward and one backward
+    kernel (nfb_render_rays_fwd / nfb_render_rays_bwd, a group of lanes per ray) or, when rays
+    are very long on average, the flat tile kernels — weights forward (nfb_render_weight_fwd),
+    composite forward (nfb_composite_fwd), one backward (nfb_composite_bwd).
 
     Returns (colors_sum [R,3], opacity [R,1], depth_sum [R,1], weights, trans, alphas); the
     depth normalisation and the background blend stay torch ops on [R, .] tensors in volrend.py.
@@ -204,25 +217,40 @@ class RenderComposite(torch.autograd.Function):
         field, rgbs = field.contiguous(), rgbs.contiguous()
         t_starts, t_ends = t_starts.contiguous(), t_ends.contiguous()
         dev = _C.require_cuda(field, rgbs, t_starts, t_ends, packed_info, ray_indices)
-        if from_density:
-            weights, trans, alphas, _ = weight_fwd(True, None, t_starts, t_ends, field, None,
-                                                   packed_info, 0, True, True, True)
-        else:
-            weights, trans, _, _ = weight_fwd(False, field, None, None, None, None, packed_info, 0,
-                                              True, True, False)
-            alphas = None
         n = field.numel()
         colors = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)
         opacity = torch.empty((n_rays, 1), dtype=torch.float32, device=dev)
         depth = torch.empty((n_rays, 1), dtype=torch.float32, device=dev)
-        if n_rays > 0:
-            with torch.cuda.device(dev):
-                ws, ws_bytes, epoch = _C.workspace(dev, max(n, 1))
-                rc = _C.lib().nfb_composite_fwd(
-                    _p(weights), _p(rgbs), _p(t_starts), _p(t_ends), _p(packed_info), n_rays, n,
-                    colors.data_ptr(), opacity.data_ptr(), depth.data_ptr(), ws.data_ptr(), ws_bytes,
-                    epoch, _C.stream_ptr(dev))
-            _C.check(rc, "composite_fwd")
+        per_ray = _per_ray_kernels(n, n_rays)
+        if per_ray:
+            # one kernel: weights + the three per-ray sums (csrc/render_rays.cu)
+            weights, trans = torch.empty_like(field), torch.empty_like(field)
+            alphas = torch.empty_like(field) if from_density else None
+            if n_rays > 0:
+                with torch.cuda.device(dev):
+                    rc = _C.lib().nfb_render_rays_fwd(
+                        int(from_density), None if from_density else _p(field), _p(t_starts), _p(t_ends),
+                        _p(field) if from_density else None, _p(rgbs), _p(packed_info), n_rays, n,
+                        _p(weights), _p(trans), _p(alphas), colors.data_ptr(), opacity.data_ptr(),
+                        depth.data_ptr(), _RAYS_L, _C.stream_ptr(dev))
+                _C.check(rc, "render_rays_fwd")
+        else:
+            if from_density:
+                weights, trans, alphas, _ = weight_fwd(True, None, t_starts, t_ends, field, None,
+                                                       packed_info, 0, True, True, True)
+            else:
+                weights, trans, _, _ = weight_fwd(False, field, None, None, None, None, packed_info, 0,
+                                                  True, True, False)
+                alphas = None
+            if n_rays > 0:
+                with torch.cuda.device(dev):
+                    ws, ws_bytes, epoch = _C.workspace(dev, max(n, 1))
+                    rc = _C.lib().nfb_composite_fwd(
+                        _p(weights), _p(rgbs), _p(t_starts), _p(t_ends), _p(packed_info), n_rays, n,
+                        colors.data_ptr(), opacity.data_ptr(), depth.data_ptr(), ws.data_ptr(), ws_bytes,
+                        epoch, _C.stream_ptr(dev))
+                _C.check(rc, "composite_fwd")
+        ctx.per_ray = per_ray
         ctx.set_materialize_grads(False)
         ctx.from_density = from_density
         ctx.n_rays = n_rays
@@ -243,12 +271,20 @@ class RenderComposite(torch.autograd.Function):
         if n > 0:
             fd = ctx.from_density
             with torch.cuda.device(dev):
-                ws, ws_bytes, epoch = _C.workspace(dev, n)
-                rc = _C.lib().nfb_composite_bwd(
-                    int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),
-                    _p(_cg(g_trans)), _p(_cg(g_alphas)) if fd else None,
-                    None if fd else _p(field), _p(t_starts), _p(t_ends), _p(field) if fd else None,
-                    _p(rgbs), _p(trans), _p(ray_indices), _p(packed_info), ctx.n_rays, n,
-                    g_field.data_ptr(), _p(g_rgbs), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+                if ctx.per_ray:
+                    rc = _C.lib().nfb_render_rays_bwd(
+                        int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),
+                        _p(_cg(g_trans)), _p(_cg(g_alphas)) if fd else None,
+                        None if fd else _p(field), _p(t_starts), _p(t_ends), _p(field) if fd else None,
+                        _p(rgbs), _p(trans), _p(packed_info), ctx.n_rays, n,
+                        g_field.data_ptr(), _p(g_rgbs), _RAYS_L, _C.stream_ptr(dev))
+                else:
+                    ws, ws_bytes, epoch = _C.workspace(dev, n)
+                    rc = _C.lib().nfb_composite_bwd(
+                        int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),
+                        _p(_cg(g_trans)), _p(_cg(g_alphas)) if fd else None,
+                        None if fd else _p(field), _p(t_starts), _p(t_ends), _p(field) if fd else None,
+                        _p(rgbs), _p(trans), _p(ray_indices), _p(packed_info), ctx.n_rays, n,
+                        g_field.data_ptr(), _p(g_rgbs), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
             _C.check(rc, "composite_bwd")
         return (g_field if need_field else None), g_rgbs, None, None, None, None, None, None

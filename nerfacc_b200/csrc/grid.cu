@@ -196,7 +196,8 @@ struct FillPolicy {
 };
 
 // ---------------------------------------------------------------------------------- kernels
-// Persistent CTAs: dynamic shared memory = [mip words][event queue kQ x blockDim floats].
+// Persistent CTAs: dynamic shared memory = [mip words][event queue kQ x blockDim floats]
+// [prepared-ray pool: warps x kPoolWords x 32 words].
 constexpr int kMarchThreads = 512;
 
 template <bool MIP, class Policy>
@@ -206,8 +207,9 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
     extern __shared__ uint32_t s_dyn[];
     const GridSpec G = stage_mip(Gp, s_dyn);
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
+    uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * kMarchThreads);
     march_engine<MIP>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
-                 A.hits, A.n_rays, G, opt, P, s_evt, ray_counter);
+                 A.hits, A.n_rays, G, opt, P, s_evt, s_pool, ray_counter);
 }
 
 // Pass 2 of OccGridEstimator.sampling when pass 1 left a run buffer: no marching at all.
@@ -338,7 +340,8 @@ constexpr size_t kCounterBytes = 64;  // ray counter + overflow counter, at the 
 template <class Policy>
 static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& opt, const Policy& P,
                         unsigned long long* counter, cudaStream_t s) {
-    const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float);
+    const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float) +
+                        (size_t)kPoolWords * kMarchThreads * sizeof(uint32_t);
     auto kernel = G.mip != nullptr ? march_kernel<true, Policy> : march_kernel<false, Policy>;
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
         set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
@@ -349,7 +352,7 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
         return NFB_ERR_CUDA;
     }
     long long b = ceil_div<long long>(A.n_rays, kMarchThreads);
-    const long long cap = (long long)sm_count() * (smem <= 100 * 1024 ? 2 : 1);
+    const long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
     if (b > cap) b = cap;
     if (b < 1) b = 1;
     kernel<<<(unsigned)b, kMarchThreads, smem, s>>>(A, G, opt, P, counter);

@@ -224,34 +224,126 @@ struct NoPiece {
 // The reference walks every ray with one thread: DDA step, occupancy test, and — inside the
 // same loop — the skip / emit recurrences.  On a GPU that interleaving is what hurts: lanes of
 // a warp reach occupied cells at different times, so the expensive emit code runs with two or
-// three lanes active.  Here the work of a ray is split into a PRODUCER and a CONSUMER that a
-// warp executes in lock step:
+// three lanes active, and lanes whose ray is finished idle until the longest ray of the warp
+// ends.  Here a warp runs three convergent phases in lock step:
+//   prepare   when the warp's pool of ready rays is empty, all 32 lanes fetch one ray each
+//             (one atomicAdd of 32 on a global counter), intersect it with the level boxes, find
+//             its first segment and set up the DDA — and park the result in a per-warp pool in
+//             shared memory.  The ~500 instructions of set-up run with 32 active lanes instead
+//             of the 2-3 that happen to need a ray at that moment;
 //   produce   a tight, branch-free DDA loop (<= kRoundSteps cells per round) that touches only
-//             the grid and appends EVENTS (kind, t) to a per-lane queue in shared memory.  With
-//             a constant dt consecutive cells of the same kind fold into one event, because both
-//             recurrences are idempotent in their target: a ray through a trained scene yields
-//             a handful of events, not hundreds;
+//             the grid and appends EVENTS (kind, t) to a per-lane queue in shared memory.  A
+//             lane whose ray has ended pops a prepared ray from the pool at the next round (a
+//             dozen shared-memory loads), so the DDA keeps ~all lanes busy.  With a constant dt
+//             consecutive cells of the same kind fold into one event, because both recurrences
+//             are idempotent in their target: a ray through a trained scene yields a handful of
+//             events, not hundreds;
 //   consume   when a queue fills up, all lanes replay their queued events together through
 //             ONE advance() call site.  The queue also carries the ray boundaries (EV_RAY), so
 //             the producer of a lane may be several rays ahead of its consumer and the replay
 //             finds every lane with work.
-// Lanes whose DDA has finished a ray fetch the next one from a global counter (persistent
-// threads).  Results are addressed by ray id; nothing depends on which lane marched which ray.
+// Results are addressed by ray id; nothing depends on which lane marched which ray.
 //
 // Event kinds (t = exit of the cell / start of the segment):
 //   EV_EMPTY  empty cell(s):     skip to t, continuous = false        (grid.cu:189-206)
 //   EV_OCC    occupied cell(s):  emit samples up to t                 (grid.cu:208-262)
 //   EV_SEG    segment start:     if (!continuous) skip to t           (grid.cu:150-163)
 //   EV_RAY    a new ray starts:  payload = ray id; retires the previous ray of the lane
-constexpr int kQ = 16;           // events queued per lane
-constexpr int kRoundSteps = 32;  // DDA cells per lane and round
+constexpr int kQ = 16;          // events queued per lane
+constexpr int kRoundSteps = 16; // DDA cells per lane between two refill checks
+constexpr int kPoolWords = 16;  // words per prepared ray (x 32 slots per warp)
 enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2, EV_RAY = 3 };
+
+// DDA state of one ray segment (utils_grid.cuh:58-114).
+struct Dda {
+    float tdist[3], delta[3];
+    int cur[3], stepi[3], stop[3];
+};
+
+// Next ray/box segment at or after event seg_i (grid.cu:128-149).
+__device__ __forceinline__ bool find_segment(const RayEvents& ev, int m, int& seg_i, float near, float far,
+                                             float& tmin, float& tmax, int& level) {
+    while (seg_i < 2 * m - 1) {
+        const int i = seg_i++;
+        const bool entering = ev.idx[i] < m;
+        level = ev.idx[i] % m;
+        if (!((ev.hit_mask >> level) & 1u)) continue;
+        if (!entering) {
+            if (ev.idx[i + 1] < m) continue;  // next event enters a box: we are in a gap
+            level = ev.idx[i + 1] % m;
+            if (!((ev.hit_mask >> level) & 1u)) continue;
+        }
+        tmin = fmaxf(ev.t[i], near);
+        tmax = fminf(ev.t[i + 1], far);
+        if (tmin >= tmax) continue;
+        return true;
+    }
+    return false;
+}
+
+// setup_traversal, utils_grid.cuh:58-114.
+__device__ __forceinline__ void setup_dda(const float (&o)[3], const float (&d)[3], const GridSpec& G, int level,
+                                          float tmin, float tmax, Dda& S) {
+    const float eps = 1e-6f;
+    const float* __restrict__ bb = G.aabbs + 6 * level;
+    const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax, eps);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float ok = o[k], dk = d[k];
+        const float invk = __fdiv_rn(1.0f, dk);
+        const float bmin = bb[k], bmax = bb[3 + k];
+        const float resf = (float)G.res[k];
+        const float ext = __fsub_rn(bmax, bmin);
+        const float vox = __fdiv_rn(ext, resf);
+        const float rs = __fmaf_rn(dk, ts, ok);  // FFMA site 1
+        const float re = __fmaf_rn(dk, te, ok);
+        S.cur[k] = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(rs, bmin), ext), resf)), 0, G.res[k] - 1);
+        const int fin = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(re, bmin), ext), resf)), 0, G.res[k] - 1);
+        const int start_index = S.cur[k] + (dk > 0.0f ? 1 : 0);
+        // FFMA site 2: fma(bmin + fma(float(idx), vox, -rs), inv, tmin)
+        const float tm = __fmaf_rn(__fadd_rn(bmin, __fmaf_rn((float)start_index, vox, -rs)), invk, tmin);
+        const float sf = (dk == 0.0f) ? 0.0f : (dk > 0.0f ? 1.0f : -1.0f);
+        S.tdist[k] = (dk == 0.0f) ? tmax : tm;
+        S.stepi[k] = (int)sf;
+        S.delta[k] = (dk == 0.0f) ? tmax : __fmul_rn(__fmul_rn(vox, invk), sf);
+        // The walk leaves when the index reaches fin + step (utils_grid.cuh:123) or the grid
+        // edge, whichever lies ahead: one stop value per axis.
+        const int ovf = fin + S.stepi[k];
+        const bool ahead = S.stepi[k] > 0 ? ovf > S.cur[k] : (S.stepi[k] < 0 ? ovf < S.cur[k] : true);
+        S.stop[k] = ahead ? ovf : (S.stepi[k] > 0 ? G.res[k] : -1);
+    }
+}
+
+__device__ __forceinline__ void load_events(const float (&o)[3], const float (&d)[3], long long r,
+                                            const float* __restrict__ t_sorted,
+                                            const int64_t* __restrict__ t_indices,
+                                            const uint8_t* __restrict__ hits, const GridSpec& G,
+                                            RayEvents& ev) {
+    const int m = G.n_grids;
+    if (t_sorted != nullptr) {
+        ev.hit_mask = 0;
+        for (int l = 0; l < m; ++l)
+            if (hits[r * m + l]) ev.hit_mask |= (1u << l);
+        for (int i = 0; i < 2 * m; ++i) {
+            ev.t[i] = __ldg(t_sorted + r * 2 * m + i);
+            ev.idx[i] = (int8_t)__ldg(t_indices + r * 2 * m + i);
+        }
+    } else {
+        float inv[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) inv[k] = __fdiv_rn(1.0f, d[k]);
+        compute_events(o, inv, G, ev);
+    }
+}
 
 // Policy interface (see grid.cu):
 //   typename Sink;  bool accept(r);  void skipped(r);  Sink begin(r);
 //   void end(r, Sink&, nS, nI, t_last);
 // Sink: run(t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
 // and one(t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
+//
+// Shared memory: s_evt = [kQ][blockDim.x] floats (event queue), s_pool = [warps][kPoolWords][32]
+// words (prepared rays).
 template <bool MIP, class Policy>
 __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const float* __restrict__ rays_d,
@@ -261,9 +353,8 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const int64_t* __restrict__ t_indices,
                                              const uint8_t* __restrict__ hits, long long n_rays,
                                              const GridSpec& G, const MarchOpts& opt, Policy& P,
-                                             float* __restrict__ s_evt /* [kQ][blockDim.x] */,
+                                             float* __restrict__ s_evt, uint32_t* __restrict__ s_pool,
                                              unsigned long long* __restrict__ ray_counter) {
-    const float eps = 1e-6f;
     const int m = G.n_grids;
     const float step = opt.step_size, cone = opt.cone_angle;
     const int cap = opt.limit > 0 ? opt.limit : 0x7fffffff;
@@ -273,17 +364,23 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     const bool eager = opt.limit > 0;  // with a sample cap, replay every round (bounds wasted DDA work)
     const int lane = lane_id();
     const int tid = threadIdx.x, nthr = blockDim.x;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    uint32_t* __restrict__ pool = s_pool + warp_id() * (kPoolWords * 32);
 
+    // ---- warp-uniform pool state
+    int pool_head = 0, pool_cnt = 0;
+    bool exhausted = false;
     // ---- producer state (the DDA of the ray being walked)
-    bool have_ray = false, exhausted = false;
-    float far = 0.0f, near = 0.0f;
+    bool have_ray = false;
     long long r = -1;
     RayEvents ev;
+    bool ev_valid = false;
     int seg_i = 0, seg_steps = 0;
     const int max_seg_steps = G.res[0] + G.res[1] + G.res[2] + 8;  // a DDA cannot take more
-    bool in_seg = false, first_seg = true;
-    float tdist[3], delta[3], tmax_seg = 0.0f;
-    int cur[3], stepi[3], stop[3], cstride[3];
+    bool in_seg = false;
+    Dda D = {};
+    float tmax_seg = 0.0f;
+    int cstride[3];
     int cell = 0;  // linear index of the current cell (host side guarantees it fits 31 bits)
     int mip_base = 0;
     int pend_kind = -1;
@@ -305,6 +402,107 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     };
     auto push_pending = [&]() {
         if (pend_kind >= 0) { push(pend_kind, pend_t); pend_kind = -1; }
+    };
+    auto enter_segment = [&](int level) {
+        cstride[0] = D.stepi[0] * G.res[1] * G.res[2];
+        cstride[1] = D.stepi[1] * G.res[2];
+        cstride[2] = D.stepi[2];
+        cell = level * (int)G.cells_per_level + (D.cur[0] * G.res[1] + D.cur[1]) * G.res[2] + D.cur[2];
+        mip_base = level * G.mip_cells_per_level;
+        in_seg = true;
+        seg_steps = 0;
+    };
+
+    // ------------------------------------------------------------------ prepare (all 32 lanes)
+    auto prepare = [&]() {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(ray_counter, 32ull);
+        base = __shfl_sync(kFull, base, 0);
+        if ((long long)base + 32 >= n_rays) exhausted = true;
+        const long long cand = (long long)base + lane;
+        bool ok = cand < n_rays;
+        if (ok && !P.accept(cand)) { P.skipped(cand); ok = false; }
+        Dda S = {};
+        float tmin = 0.0f, tmax = 0.0f;
+        int level = 0, si = 0;
+        bool found = false;
+        if (ok) {
+            float o[3], d[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { o[k] = __ldg(rays_o + 3 * cand + k); d[k] = __ldg(rays_d + 3 * cand + k); }
+            const float near = near_arr ? __ldg(near_arr + cand) : near_s;
+            const float far = far_arr ? __ldg(far_arr + cand) : far_s;
+            RayEvents pev;
+            load_events(o, d, cand, t_sorted, t_indices, hits, G, pev);
+            found = find_segment(pev, m, si, near, far, tmin, tmax, level);
+            if (found) setup_dda(o, d, G, level, tmin, tmax, S);
+        }
+        const unsigned okm = __ballot_sync(kFull, ok);
+        if (ok) {
+            uint32_t* __restrict__ e = pool + __popc(okm & lt_mask);
+            e[0 * 32] = (uint32_t)(int)cand;
+            e[1 * 32] = (found ? 1u : 0u) | ((uint32_t)level << 1) | ((uint32_t)si << 8) |
+                        ((uint32_t)(S.stepi[0] + 1) << 16) | ((uint32_t)(S.stepi[1] + 1) << 18) |
+                        ((uint32_t)(S.stepi[2] + 1) << 20);
+            if (found) {
+                e[2 * 32] = __float_as_uint(tmin);
+                e[3 * 32] = __float_as_uint(tmax);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    e[(4 + k) * 32] = __float_as_uint(S.tdist[k]);
+                    e[(7 + k) * 32] = __float_as_uint(S.delta[k]);
+                    e[(10 + k) * 32] = (uint32_t)S.cur[k];
+                    e[(13 + k) * 32] = (uint32_t)S.stop[k];
+                }
+            }
+        }
+        pool_head = 0;
+        pool_cnt = __popc(okm);
+        __syncwarp();
+    };
+
+    // ------------------------------------------------------------------ pop (warp-collective)
+    auto refill = [&]() {
+        const bool need = !have_ray && nq <= kQ - 4;  // room for EV_RAY and the first events
+        const unsigned mask = __ballot_sync(kFull, need);
+        if (mask == 0u) return;
+        if (pool_head == pool_cnt) {
+            if (exhausted) return;
+            prepare();
+        }
+        const int k = __popc(mask & lt_mask);
+        const int avail = pool_cnt - pool_head;
+        if (need && k < avail) {
+            const uint32_t* __restrict__ e = pool + pool_head + k;
+            r = (long long)(int)e[0];
+            const uint32_t misc = e[32];
+            push(EV_RAY, __int_as_float((int)r));
+            ev_valid = false;
+            seg_i = (int)((misc >> 8) & 0xffu);
+            pend_kind = -1;
+            in_seg = false;
+            if (misc & 1u) {
+                const float tmin = __uint_as_float(e[2 * 32]);
+                tmax_seg = __uint_as_float(e[3 * 32]);
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    D.tdist[a] = __uint_as_float(e[(4 + a) * 32]);
+                    D.delta[a] = __uint_as_float(e[(7 + a) * 32]);
+                    D.cur[a] = (int)e[(10 + a) * 32];
+                    D.stop[a] = (int)e[(13 + a) * 32];
+                    D.stepi[a] = (int)((misc >> (16 + 2 * a)) & 3u) - 1;
+                }
+                // right after the ray starts `continuous` is false: the segment start is a plain skip
+                pend_kind = EV_EMPTY;
+                pend_t = tmin;
+                enter_segment((int)((misc >> 1) & 0x7fu));
+                have_ray = true;
+            }
+            // a ray without any segment is just its EV_RAY marker (zero samples)
+        }
+        const int want = __popc(mask);
+        pool_head += want < avail ? want : avail;
+        __syncwarp();
     };
 
     auto consume = [&]() {
@@ -336,20 +534,35 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     continuous = true;
                     t_last = t;
                 }
-            } else if (const_dt || !emit) {
+            } else if (const_dt) {
                 if (doit) {
-                    const float dt = const_dt ? step : calc_dt(t_last, cone, step);
                     if (emit) {
-                        t_last = advance(t_last, dt, t, cap, nS, [&](float t0, float q, int k) {
+                        t_last = advance(t_last, step, t, cap, nS, [&](float t0, float q, int k) {
                             sink.run(t0, q, k, continuous, nS, nI);
                             nI += continuous ? k : k + 1;
                             continuous = true;
                         });
                     } else {
-                        t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
+                        t_last = advance(t_last, step, t, 0x7fffffff, dummy, NoPiece());
                     }
                 }
-            } else {  // cone_angle > 0: dt follows t, a true serial recurrence
+            } else if (!emit) {
+                // cone_angle > 0, skip: dt is fixed at the cell's entry (grid.cu:157-161, 199-203).
+                // Cells are about as long as dt: a few literal steps first, the closed form for
+                // what remains.
+                if (doit) {
+                    const float dt = calc_dt(t_last, cone, step);
+                    bool more = true;
+#pragma unroll 1
+                    for (int i = 0; i < 6; ++i) {
+                        if (__fmaf_rn(dt, 0.5f, t_last) >= t) { more = false; break; }
+                        const float t1 = __fadd_rn(t_last, dt);
+                        if (!(t1 > t_last)) { more = false; break; }
+                        t_last = t1;
+                    }
+                    if (more) t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
+                }
+            } else {  // cone_angle > 0, emit: dt follows t, a true serial recurrence
                 while (nS < cap) {
                     const float dt = calc_dt(t_last, cone, step);
                     if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
@@ -374,137 +587,53 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     };
 
     while (true) {
-        // ------------------------------------------------------------------ refill
-        // (needs room for the EV_RAY marker and the first events of the ray)
-#pragma unroll 1
-        for (int attempt = 0; attempt < 4; ++attempt) {
-            const bool need = !have_ray && !exhausted && nq <= kQ - 4;
-            const unsigned mask = __ballot_sync(kFull, need);
-            if (mask == 0u) break;
-            unsigned long long base = 0;
-            if (lane == __ffs(mask) - 1) base = atomicAdd(ray_counter, (unsigned long long)__popc(mask));
-            base = __shfl_sync(kFull, base, __ffs(mask) - 1);
-            if (need) {
-                const long long cand = (long long)base + __popc(mask & ((1u << lane) - 1u));
-                if (cand >= n_rays) {
-                    exhausted = true;
-                } else if (!P.accept(cand)) {
-                    P.skipped(cand);
-                } else {
-                    r = cand;
-                    float o[3], d[3], inv[3];
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) {
-                        o[k] = __ldg(rays_o + 3 * r + k);
-                        d[k] = __ldg(rays_d + 3 * r + k);
-                        inv[k] = __fdiv_rn(1.0f, d[k]);
-                    }
-                    near = near_arr ? __ldg(near_arr + r) : near_s;
-                    far = far_arr ? __ldg(far_arr + r) : far_s;
-                    if (t_sorted != nullptr) {
-                        ev.hit_mask = 0;
-                        for (int l = 0; l < m; ++l)
-                            if (hits[r * m + l]) ev.hit_mask |= (1u << l);
-                        for (int i = 0; i < 2 * m; ++i) {
-                            ev.t[i] = __ldg(t_sorted + r * 2 * m + i);
-                            ev.idx[i] = (int8_t)__ldg(t_indices + r * 2 * m + i);
-                        }
-                    } else {
-                        compute_events(o, inv, G, ev);
-                    }
-                    have_ray = true; in_seg = false; seg_i = 0; pend_kind = -1; first_seg = true;
-                    push(EV_RAY, __int_as_float((int)r));
-                }
-            }
-        }
+        refill();
         if (!__any_sync(kFull, have_ray)) {
-            if (__all_sync(kFull, exhausted || nq > kQ - 4)) {
-                consume();
-                if (__all_sync(kFull, exhausted)) break;
-            }
+            // nothing to walk: queues are full (the replay frees them), the pool came back empty
+            // (masked rays; try again), or the work is done
+            consume();
+            if (exhausted && pool_head == pool_cnt) break;
             continue;
         }
         // ------------------------------------------------------------------ produce
         int steps = 0;
         while (have_ray && steps < kRoundSteps && nq <= kQ - 3) {
             if (!in_seg) {
-                // next ray/box segment (grid.cu:128-149)
-                bool found = false;
+                // a later segment of a multi-level march (the first one came prepared)
+                if (m == 1) { push_pending(); have_ray = false; break; }
+                float o[3], d[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { o[k] = __ldg(rays_o + 3 * r + k); d[k] = __ldg(rays_d + 3 * r + k); }
+                if (!ev_valid) { load_events(o, d, r, t_sorted, t_indices, hits, G, ev); ev_valid = true; }
+                const float near = near_arr ? __ldg(near_arr + r) : near_s;
+                const float far = far_arr ? __ldg(far_arr + r) : far_s;
                 float tmin = 0.0f;
                 int level = 0;
-                while (seg_i < 2 * m - 1) {
-                    const int i = seg_i++;
-                    const bool entering = ev.idx[i] < m;
-                    level = ev.idx[i] % m;
-                    if (!((ev.hit_mask >> level) & 1u)) continue;
-                    if (!entering) {
-                        if (ev.idx[i + 1] < m) continue;  // next event enters a box: we are in a gap
-                        level = ev.idx[i + 1] % m;
-                        if (!((ev.hit_mask >> level) & 1u)) continue;
-                    }
-                    tmin = fmaxf(ev.t[i], near);
-                    tmax_seg = fminf(ev.t[i + 1], far);
-                    if (tmin >= tmax_seg) continue;
-                    found = true;
+                if (!find_segment(ev, m, seg_i, near, far, tmin, tmax_seg, level)) {
+                    push_pending();
+                    have_ray = false;
                     break;
                 }
-                if (!found) { push_pending(); have_ray = false; break; }
-                // "if (!continuous) skip to tmin": right after the ray starts or after empty
-                // cells `continuous` is known to be false and the event is a plain skip
-                if (first_seg) {
-                    pend_kind = EV_EMPTY; pend_t = tmin; first_seg = false;
-                } else if (pend_kind == EV_EMPTY && fold_empty) {
+                // "if (!continuous) skip to tmin": after empty cells `continuous` is known to be
+                // false and the event is a plain skip
+                if (pend_kind == EV_EMPTY && fold_empty) {
                     pend_t = tmin;
                 } else {
                     push_pending();
                     push(EV_SEG, tmin);
                 }
-                // setup_traversal, utils_grid.cuh:58-114 (the ray is re-read: it is not kept in
-                // registers across the DDA loop)
-                const float* __restrict__ bb = G.aabbs + 6 * level;
-                const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax_seg, eps);
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float ok = __ldg(rays_o + 3 * r + k), dk = __ldg(rays_d + 3 * r + k);
-                    const float invk = __fdiv_rn(1.0f, dk);
-                    const float bmin = bb[k], bmax = bb[3 + k];
-                    const float resf = (float)G.res[k];
-                    const float ext = __fsub_rn(bmax, bmin);
-                    const float vox = __fdiv_rn(ext, resf);
-                    const float rs = __fmaf_rn(dk, ts, ok);  // FFMA site 1
-                    const float re = __fmaf_rn(dk, te, ok);
-                    cur[k] = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(rs, bmin), ext), resf)), 0, G.res[k] - 1);
-                    const int fin = clampi(__float2int_rz(__fmul_rn(__fdiv_rn(__fsub_rn(re, bmin), ext), resf)), 0, G.res[k] - 1);
-                    const int start_index = cur[k] + (dk > 0.0f ? 1 : 0);
-                    // FFMA site 2: fma(bmin + fma(float(idx), vox, -rs), inv, tmin)
-                    const float tm = __fmaf_rn(__fadd_rn(bmin, __fmaf_rn((float)start_index, vox, -rs)), invk, tmin);
-                    const float sf = (dk == 0.0f) ? 0.0f : (dk > 0.0f ? 1.0f : -1.0f);
-                    tdist[k] = (dk == 0.0f) ? tmax_seg : tm;
-                    stepi[k] = (int)sf;
-                    delta[k] = (dk == 0.0f) ? tmax_seg : __fmul_rn(__fmul_rn(vox, invk), sf);
-                    // The walk leaves when the index reaches fin + step (utils_grid.cuh:123) or the
-                    // grid edge, whichever lies ahead: one stop value per axis.
-                    const int ovf = fin + stepi[k];
-                    const bool ahead = stepi[k] > 0 ? ovf > cur[k] : (stepi[k] < 0 ? ovf < cur[k] : true);
-                    stop[k] = ahead ? ovf : (stepi[k] > 0 ? G.res[k] : -1);
-                }
-                cstride[0] = stepi[0] * G.res[1] * G.res[2];
-                cstride[1] = stepi[1] * G.res[2];
-                cstride[2] = stepi[2];
-                cell = level * (int)G.cells_per_level + (cur[0] * G.res[1] + cur[1]) * G.res[2] + cur[2];
-                mip_base = level * G.mip_cells_per_level;
-                in_seg = true;
-                seg_steps = 0;
+                setup_dda(o, d, G, level, tmin, tmax_seg, D);
+                enter_segment(level);
                 continue;
             }
             // the DDA proper (grid.cu:183-281), branch-free; leaves the loop when the segment
             // ends, the round is over or the queue is (nearly) full
             do {
-                const float t_trav = fminf(fminf(tdist[0], fminf(tdist[1], tdist[2])), tmax_seg);
+                const float t_trav = fminf(fminf(D.tdist[0], fminf(D.tdist[1], D.tdist[2])), tmax_seg);
                 uint32_t cbit = 1u;
                 if (MIP) {
-                    const int ci = mip_base + ((cur[0] >> G.mip_shift) * G.mres[1] + (cur[1] >> G.mip_shift)) * G.mres[2] +
-                                   (cur[2] >> G.mip_shift);
+                    const int ci = mip_base + ((D.cur[0] >> G.mip_shift) * G.mres[1] + (D.cur[1] >> G.mip_shift)) * G.mres[2] +
+                                   (D.cur[2] >> G.mip_shift);
                     cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
                 }
                 // fine bit, fetched only under a set mip bit
@@ -514,17 +643,18 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 if (kind != pend_kind || !(kind == EV_OCC ? fold_occ : fold_empty)) { push_pending(); pend_kind = kind; }
                 pend_t = t_trav;
                 // single_traversal, utils_grid.cuh:116-142: x if strictly smallest, else y if < z, else z
-                const bool px = tdist[0] < tdist[1] && tdist[0] < tdist[2];
-                const bool py = !px && tdist[1] < tdist[2];
+                const bool px = D.tdist[0] < D.tdist[1] && D.tdist[0] < D.tdist[2];
+                const bool py = !px && D.tdist[1] < D.tdist[2];
                 const bool pz = !px && !py;
-                cur[0] += px ? stepi[0] : 0;
-                cur[1] += py ? stepi[1] : 0;
-                cur[2] += pz ? stepi[2] : 0;
-                tdist[0] = px ? __fadd_rn(tdist[0], delta[0]) : tdist[0];
-                tdist[1] = py ? __fadd_rn(tdist[1], delta[1]) : tdist[1];
-                tdist[2] = pz ? __fadd_rn(tdist[2], delta[2]) : tdist[2];
+                D.cur[0] += px ? D.stepi[0] : 0;
+                D.cur[1] += py ? D.stepi[1] : 0;
+                D.cur[2] += pz ? D.stepi[2] : 0;
+                D.tdist[0] = px ? __fadd_rn(D.tdist[0], D.delta[0]) : D.tdist[0];
+                D.tdist[1] = py ? __fadd_rn(D.tdist[1], D.delta[1]) : D.tdist[1];
+                D.tdist[2] = pz ? __fadd_rn(D.tdist[2], D.delta[2]) : D.tdist[2];
                 cell += px ? cstride[0] : (py ? cstride[1] : cstride[2]);
-                const bool leave = (px && cur[0] == stop[0]) || (py && cur[1] == stop[1]) || (pz && cur[2] == stop[2]);
+                const bool leave = (px && D.cur[0] == D.stop[0]) || (py && D.cur[1] == D.stop[1]) ||
+                                   (pz && D.cur[2] == D.stop[2]);
                 if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
                 ++steps;
             } while (in_seg && steps < kRoundSteps && nq <= kQ - 3);

@@ -257,11 +257,19 @@ def test_rendering_end_to_end(device):
 
 
 @pytest.mark.parametrize("mode", ["density", "alpha"])
-def test_rendering_fused_composite_vs_oracle(device, mode):
-    """rendering() on flattened inputs (fused weights + composite forward, one fused backward)
-    against the oracle's composition of volrend.py:140-156, incl. empty rays, a long ray that
-    spans several tiles, a background colour, and an extra loss on extras['weights']."""
+@pytest.mark.parametrize("path", ["per_ray", "per_ray_L4", "per_ray_L32", "tiles"])
+def test_rendering_fused_composite_vs_oracle(device, mode, path, monkeypatch):
+    """rendering() on flattened inputs — the per-ray kernels (csrc/render_rays.cu, lanes per ray
+    chosen / forced) and the flat tile kernels (volrend.cu + composite.cu) — against the oracle's
+    composition of volrend.py:140-156, incl. empty rays, a long ray that spans several tiles, a
+    background colour, and an extra loss on extras['weights']."""
     import nerfacc_b200 as nf
+    from nerfacc_b200 import _render_ops
+
+    if path == "tiles":
+        monkeypatch.setattr(_render_ops, "_PER_RAY_MAX_MEAN", 0)
+    elif path != "per_ray":
+        monkeypatch.setattr(_render_ops, "_RAYS_L", int(path.split("L")[1]))
 
     counts = ragged_counts(3000, mean=14, seed=5, long_rays=((17, 9000), (1500, 1)))
     pi = packed_info_from_counts(counts)
