@@ -36,12 +36,18 @@ struct RayArgs {
     const int64_t* __restrict__ t_indices;   // [n_rays, 2m]
     const uint8_t* __restrict__ hits;        // [n_rays, m]
     long long n_rays;
+    // optional work list: march rays ray_list[0..n_work) instead of 0..n_rays (the fill pass
+    // re-marches only the rays whose runs overflowed the run buffer)
+    const int* __restrict__ ray_list;
+    long long n_work;
 };
 
 // ---------------------------------------------------------------------------------- sinks
+// Sink methods take the policy first: it is a kernel parameter (constant bank), so what a sink
+// needs from it costs no registers.
 struct CountSink {
-    __device__ __forceinline__ void run(float, float, int, bool, int, int) const {}
-    __device__ __forceinline__ void one(float, float, bool, int, int) const {}
+    template <class P> __device__ __forceinline__ void run(const P&, float, float, int, bool, int, int) const {}
+    template <class P> __device__ __forceinline__ void one(const P&, float, float, bool, int, int) const {}
 };
 
 // Run buffer written by the count pass when marching with a constant dt (cone_angle == 0,
@@ -52,29 +58,50 @@ struct CountSink {
 constexpr int kRunSlots = 8;
 struct __align__(16) Run { float t0, q; int n, s0; };
 
+// Runs beyond a ray's kRunSlots inline slots go to a global pool (bump-allocated, kPoolPerRay
+// entries per ray on average), expanded by traverse_expand_pool_kernel; only when the pool is
+// full is a ray flagged for a second march.
+constexpr int kPoolPerRay = 2;
+struct RunPool {
+    Run* __restrict__ runs;
+    int* __restrict__ ray;
+    unsigned long long* __restrict__ cursor;
+    unsigned long long cap;
+};
+
 struct RunSink {
-    Run* __restrict__ slots;
     Run cur;
-    int idx;
-    bool have;
-    __device__ __forceinline__ void flush() {
+    int idx, r;
+    bool have, failed;
+    template <class P> __device__ __forceinline__ void flush(const P& pol) {
         if (have) {
-            if (idx < kRunSlots) *reinterpret_cast<int4*>(slots + idx) = *reinterpret_cast<const int4*>(&cur);
+            if (idx < kRunSlots) {
+                *reinterpret_cast<int4*>(pol.runs + (long long)r * kRunSlots + idx) = *reinterpret_cast<const int4*>(&cur);
+            } else if (!failed) {
+                const unsigned long long k = atomicAdd(pol.pool.cursor, 1ull);
+                if (k < pol.pool.cap) {
+                    *reinterpret_cast<int4*>(pol.pool.runs + k) = *reinterpret_cast<const int4*>(&cur);
+                    pol.pool.ray[k] = r;
+                } else {
+                    failed = true;
+                }
+            }
             ++idx;
             have = false;
         }
     }
-    __device__ __forceinline__ void run(float t0, float q, int k, bool, int nS, int) {
+    template <class P>
+    __device__ __forceinline__ void run(const P& pol, float t0, float q, int k, bool, int nS, int) {
         // consecutive pieces of one arithmetic progression merge
         if (have && q == cur.q && nS == cur.s0 + cur.n && t0 == __fmaf_rn((float)cur.n, cur.q, cur.t0)) {
             cur.n += k;
             return;
         }
-        flush();
+        flush(pol);
         cur.t0 = t0; cur.q = q; cur.n = k; cur.s0 = nS;
         have = true;
     }
-    __device__ __forceinline__ void one(float, float, bool, int, int) { idx = kRunSlots + 1; }
+    template <class P> __device__ __forceinline__ void one(const P&, float, float, bool, int, int) { failed = true; }
 };
 
 struct SamplingSink {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177), one lane per ray
@@ -82,15 +109,17 @@ struct SamplingSink {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177
     float* __restrict__ t_starts;
     float* __restrict__ t_ends;
     long long base, r;
-    __device__ __forceinline__ void one(float t_last, float t_next, bool, int nS, int) const {
+    template <class P>
+    __device__ __forceinline__ void one(const P&, float t_last, float t_next, bool, int nS, int) const {
         const long long i = base + nS;
         ray_indices[i] = r;
         t_starts[i] = t_last;
         t_ends[i] = t_next;
     }
-    __device__ __forceinline__ void run(float t0, float q, int k, bool, int nS, int) const {
+    template <class P>
+    __device__ __forceinline__ void run(const P& pol, float t0, float q, int k, bool, int nS, int) const {
         for (int j = 0; j < k; ++j)
-            one(__fmaf_rn((float)j, q, t0), __fmaf_rn((float)(j + 1), q, t0), true, nS + j, 0);
+            one(pol, __fmaf_rn((float)j, q, t0), __fmaf_rn((float)(j + 1), q, t0), true, nS + j, 0);
     }
 };
 
@@ -99,7 +128,8 @@ struct FullSink {  // traverse_grids outputs (grid.cu:218-255)
     uint8_t* __restrict__ iv_left; uint8_t* __restrict__ iv_right;
     float* __restrict__ sm_vals; int64_t* __restrict__ sm_ray; uint8_t* __restrict__ sm_valid;
     long long iv_base, sm_base, r;
-    __device__ __forceinline__ void one(float t_last, float t_next, bool continuous, int nS, int nI) const {
+    template <class P>
+    __device__ __forceinline__ void one(const P&, float t_last, float t_next, bool continuous, int nS, int nI) const {
         long long e = iv_base + nI;
         if (!continuous) {
             iv_vals[e] = t_last; iv_ray[e] = r; iv_left[e] = 1; iv_right[e] = 0;
@@ -113,9 +143,10 @@ struct FullSink {  // traverse_grids outputs (grid.cu:218-255)
         sm_ray[s] = r;
         sm_valid[s] = 1;
     }
-    __device__ __forceinline__ void run(float t0, float q, int k, bool continuous, int nS, int nI) const {
+    template <class P>
+    __device__ __forceinline__ void run(const P& pol, float t0, float q, int k, bool continuous, int nS, int nI) const {
         for (int j = 0; j < k; ++j) {
-            one(__fmaf_rn((float)j, q, t0), __fmaf_rn((float)(j + 1), q, t0), continuous, nS + j, nI);
+            one(pol, __fmaf_rn((float)j, q, t0), __fmaf_rn((float)(j + 1), q, t0), continuous, nS + j, nI);
             nI += continuous ? 1 : 2;
             continuous = true;
         }
@@ -131,13 +162,15 @@ struct CountPolicy {
     int64_t* __restrict__ interval_info;
     float* __restrict__ term;
     Run* __restrict__ runs;
-    int* __restrict__ n_runs;
+    int* __restrict__ n_runs;  // inline runs of the ray, or kRunSlots + 1: march it again
+    int* __restrict__ overflow_list;
     unsigned long long* __restrict__ n_overflow;
+    RunPool pool;
     __device__ __forceinline__ bool accept(long long) const { return true; }
     __device__ __forceinline__ void skipped(long long) const {}
     __device__ __forceinline__ Sink begin(long long r) const {
         Sink s;
-        if constexpr (RUNS) { s.slots = runs + r * kRunSlots; s.idx = 0; s.have = false; }
+        if constexpr (RUNS) { s.idx = 0; s.r = (int)r; s.have = false; s.failed = false; }
         return s;
     }
     __device__ __forceinline__ void end(long long r, Sink& s, int nS, int nI, float t_last) const {
@@ -145,9 +178,9 @@ struct CountPolicy {
         if (interval_info) interval_info[2 * r + 1] = nI;
         if (term) term[r] = t_last;
         if constexpr (RUNS) {
-            s.flush();
-            n_runs[r] = s.idx;
-            if (s.idx > kRunSlots) atomicAdd(n_overflow, 1ull);
+            s.flush(*this);
+            n_runs[r] = s.failed ? kRunSlots + 1 : (s.idx < kRunSlots ? s.idx : kRunSlots);
+            if (s.failed) overflow_list[atomicAdd(n_overflow, 1ull)] = (int)r;
         }
     }
 };
@@ -209,7 +242,7 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
     uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * kMarchThreads);
     march_engine<MIP>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
-                 A.hits, A.n_rays, G, opt, P, s_evt, s_pool, ray_counter);
+                 A.hits, A.ray_list, A.ray_list ? A.n_work : A.n_rays, G, opt, P, s_evt, s_pool, ray_counter);
 }
 
 // Pass 2 of OccGridEstimator.sampling when pass 1 left a run buffer: no marching at all.
@@ -259,6 +292,28 @@ traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info
             }
         }
         __syncwarp();
+    }
+}
+
+// The pooled runs (rays with more than kRunSlots runs): one warp per run.
+__global__ void __launch_bounds__(kExpandWarps * 32)
+traverse_expand_pool_kernel(const int64_t* __restrict__ sample_info, const RunPool pool,
+                            int64_t* __restrict__ ray_indices, float* __restrict__ t_starts,
+                            float* __restrict__ t_ends) {
+    unsigned long long cnt = *pool.cursor;
+    if (cnt > pool.cap) cnt = pool.cap;
+    const int lane = lane_id();
+    for (unsigned long long e = (unsigned long long)blockIdx.x * kExpandWarps + warp_id(); e < cnt;
+         e += (unsigned long long)gridDim.x * kExpandWarps) {
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(pool.runs + e));
+        const Run run = *reinterpret_cast<const Run*>(&raw);
+        const long long rb = __ldg(pool.ray + e);
+        long long i = load_chunk(sample_info, rb).start + run.s0 + lane;
+        for (int j = lane; j < run.n; j += 32, i += 32) {
+            ray_indices[i] = rb;
+            t_starts[i] = __fmaf_rn((float)j, run.q, run.t0);
+            t_ends[i] = __fmaf_rn((float)(j + 1), run.q, run.t0);
+        }
     }
 }
 
@@ -351,7 +406,9 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
         set_error("ray counter memset failed");
         return NFB_ERR_CUDA;
     }
-    long long b = ceil_div<long long>(A.n_rays, kMarchThreads);
+    // a warp takes 32 rays at a time: one CTA per 32 rays until the machine is full, so that
+    // small launches (a re-march list, a test-time chunk) spread over all SMs
+    long long b = ceil_div<long long>(A.ray_list ? A.n_work : A.n_rays, 32);
     const long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
     if (b > cap) b = cap;
     if (b < 1) b = 1;
@@ -380,6 +437,7 @@ static RayArgs to_args(const nfb_rays_t* r) {
     a.rays_o = r->rays_o; a.rays_d = r->rays_d; a.rays_mask = r->rays_mask;
     a.near_arr = r->near_planes; a.far_arr = r->far_planes; a.near_s = r->near_plane; a.far_s = r->far_plane;
     a.t_sorted = r->t_sorted; a.t_indices = r->t_indices; a.hits = r->hits; a.n_rays = r->n_rays;
+    a.ray_list = nullptr; a.n_work = 0;
     return a;
 }
 static GridSpec to_grid(const nfb_grid_t* g) {
@@ -401,6 +459,18 @@ static GridSpec to_grid(const nfb_grid_t* g) {
     return G;
 }
 static MarchOpts to_opts(const nfb_march_t* m) { return MarchOpts{m->step_size, m->cone_angle, m->traverse_steps_limit}; }
+
+static size_t run_ints_bytes(size_t n) { return (2 * n * sizeof(int) + 15) & ~(size_t)15; }
+// the pieces of a run buffer of n rays (see nfb_traverse_run_bytes); cursor = counters + 2
+static RunPool pool_of(void* run_buf, long long n, unsigned long long* cursor) {
+    char* base = static_cast<char*>(run_buf) + (size_t)n * kRunSlots * sizeof(Run) + run_ints_bytes((size_t)n);
+    RunPool P;
+    P.runs = reinterpret_cast<Run*>(base);
+    P.cap = (unsigned long long)n * kPoolPerRay;
+    P.ray = reinterpret_cast<int*>(base + P.cap * sizeof(Run));
+    P.cursor = cursor;
+    return P;
+}
 
 static unsigned long long* counters_of(void* scratch, size_t scratch_bytes, long long n_rays) {
     const size_t need = nfb_traverse_scratch_bytes(n_rays);
@@ -467,7 +537,9 @@ NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int32_t n_grids, const i
 
 NFB_API size_t nfb_traverse_run_bytes(int64_t n_rays) {
     const size_t n = (size_t)(n_rays > 0 ? n_rays : 0);
-    return n * nfb::kRunSlots * sizeof(nfb::Run) + n * sizeof(int) + 16;
+    // inline runs | n_runs, overflow list (ints, padded to 16 B) | pooled runs | their ray ids
+    return n * nfb::kRunSlots * sizeof(nfb::Run) + nfb::run_ints_bytes(n) +
+           n * nfb::kPoolPerRay * (sizeof(nfb::Run) + sizeof(int)) + 16;
 }
 
 NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
@@ -497,13 +569,15 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
         P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
         P.runs = static_cast<Run*>(run_buf);
         P.n_runs = reinterpret_cast<int*>(P.runs + rays->n_rays * kRunSlots);
+        P.overflow_list = P.n_runs + rays->n_rays;
         P.n_overflow = counters + 1;
-        cudaMemsetAsync(counters + 1, 0, sizeof(unsigned long long), s);
+        P.pool = pool_of(run_buf, rays->n_rays, counters + 2);
+        cudaMemsetAsync(counters + 1, 0, 2 * sizeof(unsigned long long), s);
         rc = launch_march(A, G, to_opts(march), P, counters, s);
     } else {
         CountPolicy<false> P;
         P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
-        P.runs = nullptr; P.n_runs = nullptr; P.n_overflow = nullptr;
+        P.runs = nullptr; P.n_runs = nullptr; P.overflow_list = nullptr; P.n_overflow = nullptr; P.pool = RunPool{};
         cudaMemsetAsync(counters + 1, 0, sizeof(unsigned long long), s);
         rc = launch_march(A, G, to_opts(march), P, counters, s);
     }
@@ -539,7 +613,21 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
             rays->n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends);
         count_launch();
         NFB_CHECK_LAUNCH("traverse_expand");
+        {   // pooled runs; the count stays on the device (the kernel reads the cursor)
+            unsigned long long* ctr = counters_of(scratch, scratch_bytes, rays->n_rays);
+            NFB_CHECK_ARG(ctr != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
+            const RunPool pool = pool_of(const_cast<void*>(run_buf), rays->n_rays, ctr + 2);
+            traverse_expand_pool_kernel<<<sm_count() * 4, kExpandWarps * 32, 0, s>>>(
+                sample_info, pool, ray_indices, t_starts, t_ends);
+            count_launch();
+            NFB_CHECK_LAUNCH("traverse_expand_pool");
+        }
         if (n_overflowed == 0) return NFB_OK;
+        // the few rays with more than kRunSlots runs: re-march exactly those (the count pass
+        // left their ids in the overflow list)
+        NFB_CHECK_ARG(n_overflowed > 0 && n_overflowed <= rays->n_rays, "bad n_overflowed");
+        A.ray_list = n_runs + rays->n_rays;
+        A.n_work = n_overflowed;
     }
     unsigned long long* counters = counters_of(scratch, scratch_bytes, rays->n_rays);
     NFB_CHECK_ARG(counters != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
@@ -547,7 +635,7 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
     P.rays_mask = nullptr; P.near_arr = A.near_arr; P.near_s = A.near_s;
     P.sm_starts = sample_info; P.sm_stride = 2;
     P.sample_info = const_cast<int64_t*>(sample_info); P.interval_info = nullptr; P.single_pass = false;
-    P.term = nullptr; P.only_overflowed = n_runs;
+    P.term = nullptr; P.only_overflowed = nullptr;
     P.proto.ray_indices = ray_indices; P.proto.t_starts = t_starts; P.proto.t_ends = t_ends;
     return launch_march(A, to_grid(grid), to_opts(march), P, counters, s);
 }

@@ -339,8 +339,8 @@ __device__ __forceinline__ void load_events(const float (&o)[3], const float (&d
 // Policy interface (see grid.cu):
 //   typename Sink;  bool accept(r);  void skipped(r);  Sink begin(r);
 //   void end(r, Sink&, nS, nI, t_last);
-// Sink: run(t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
-// and one(t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
+// Sink: run(P, t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
+// and one(P, t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
 //
 // Shared memory: s_evt = [kQ][blockDim.x] floats (event queue), s_pool = [warps][kPoolWords][32]
 // words (prepared rays).
@@ -351,7 +351,8 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const float* __restrict__ far_arr, float far_s,
                                              const float* __restrict__ t_sorted,
                                              const int64_t* __restrict__ t_indices,
-                                             const uint8_t* __restrict__ hits, long long n_rays,
+                                             const uint8_t* __restrict__ hits,
+                                             const int* __restrict__ ray_list, long long n_work,
                                              const GridSpec& G, const MarchOpts& opt, Policy& P,
                                              float* __restrict__ s_evt, uint32_t* __restrict__ s_pool,
                                              unsigned long long* __restrict__ ray_counter) {
@@ -418,9 +419,10 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(ray_counter, 32ull);
         base = __shfl_sync(kFull, base, 0);
-        if ((long long)base + 32 >= n_rays) exhausted = true;
-        const long long cand = (long long)base + lane;
-        bool ok = cand < n_rays;
+        if ((long long)base + 32 >= n_work) exhausted = true;
+        bool ok = (long long)base + lane < n_work;
+        // work item -> ray id (identity unless a work list is given)
+        const long long cand = !ok ? 0 : (ray_list ? (long long)__ldg(ray_list + base + lane) : (long long)base + lane);
         if (ok && !P.accept(cand)) { P.skipped(cand); ok = false; }
         Dda S = {};
         float tmin = 0.0f, tmax = 0.0f;
@@ -528,7 +530,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 if (!emit) {
                     if (doit) t_last = t;
                 } else {
-                    sink.one(t_last, t, continuous, nS, nI);
+                    sink.one(P, t_last, t, continuous, nS, nI);
                     nI += continuous ? 1 : 2;
                     nS += 1;
                     continuous = true;
@@ -538,7 +540,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 if (doit) {
                     if (emit) {
                         t_last = advance(t_last, step, t, cap, nS, [&](float t0, float q, int k) {
-                            sink.run(t0, q, k, continuous, nS, nI);
+                            sink.run(P, t0, q, k, continuous, nS, nI);
                             nI += continuous ? k : k + 1;
                             continuous = true;
                         });
@@ -568,7 +570,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
                     const float t_next = __fadd_rn(t_last, dt);
                     if (!(t_next > t_last)) break;  // stuck
-                    sink.one(t_last, t_next, continuous, nS, nI);
+                    sink.one(P, t_last, t_next, continuous, nS, nI);
                     nI += continuous ? 1 : 2;
                     nS += 1;
                     continuous = true;

@@ -53,8 +53,8 @@ struct RenderRaysArgs {
 
 template <int L>
 __device__ __forceinline__ unsigned group_mask(int lane) {
-    if (L == 32) return 0xffffffffu;
-    return ((1u << L) - 1u) << ((lane / L) * L);
+    if constexpr (L == 32) return 0xffffffffu;
+    else return ((1u << L) - 1u) << ((lane / L) * L);
 }
 
 template <int L, bool DENSITY>
