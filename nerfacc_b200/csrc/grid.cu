@@ -70,36 +70,25 @@ struct RunPool {
 };
 
 struct RunSink {
-    Run cur;
     int idx, r;
-    bool have, failed;
-    template <class P> __device__ __forceinline__ void flush(const P& pol) {
-        if (have) {
-            if (idx < kRunSlots) {
-                *reinterpret_cast<int4*>(pol.runs + (long long)r * kRunSlots + idx) = *reinterpret_cast<const int4*>(&cur);
-            } else if (!failed) {
-                const unsigned long long k = atomicAdd(pol.pool.cursor, 1ull);
-                if (k < pol.pool.cap) {
-                    *reinterpret_cast<int4*>(pol.pool.runs + k) = *reinterpret_cast<const int4*>(&cur);
-                    pol.pool.ray[k] = r;
-                } else {
-                    failed = true;
-                }
-            }
-            ++idx;
-            have = false;
-        }
-    }
+    bool failed;
+    // Every piece advance() hands over becomes one run: pieces are contiguous only at binade
+    // crossings, so merging them here would save few slots and cost registers in the hot loop.
     template <class P>
     __device__ __forceinline__ void run(const P& pol, float t0, float q, int k, bool, int nS, int) {
-        // consecutive pieces of one arithmetic progression merge
-        if (have && q == cur.q && nS == cur.s0 + cur.n && t0 == __fmaf_rn((float)cur.n, cur.q, cur.t0)) {
-            cur.n += k;
-            return;
+        const int4 v = make_int4(__float_as_int(t0), __float_as_int(q), k, nS);
+        if (idx < kRunSlots) {
+            *reinterpret_cast<int4*>(pol.runs + (long long)r * kRunSlots + idx) = v;
+        } else if (!failed) {
+            const unsigned long long e = atomicAdd(pol.pool.cursor, 1ull);
+            if (e < pol.pool.cap) {
+                *reinterpret_cast<int4*>(pol.pool.runs + e) = v;
+                pol.pool.ray[e] = r;
+            } else {
+                failed = true;
+            }
         }
-        flush(pol);
-        cur.t0 = t0; cur.q = q; cur.n = k; cur.s0 = nS;
-        have = true;
+        ++idx;
     }
     template <class P> __device__ __forceinline__ void one(const P&, float, float, bool, int, int) { failed = true; }
 };
@@ -170,7 +159,7 @@ struct CountPolicy {
     __device__ __forceinline__ void skipped(long long) const {}
     __device__ __forceinline__ Sink begin(long long r) const {
         Sink s;
-        if constexpr (RUNS) { s.idx = 0; s.r = (int)r; s.have = false; s.failed = false; }
+        if constexpr (RUNS) { s.idx = 0; s.r = (int)r; s.failed = false; }
         return s;
     }
     __device__ __forceinline__ void end(long long r, Sink& s, int nS, int nI, float t_last) const {
@@ -178,7 +167,6 @@ struct CountPolicy {
         if (interval_info) interval_info[2 * r + 1] = nI;
         if (term) term[r] = t_last;
         if constexpr (RUNS) {
-            s.flush(*this);
             n_runs[r] = s.failed ? kRunSlots + 1 : (s.idx < kRunSlots ? s.idx : kRunSlots);
             if (s.failed) overflow_list[atomicAdd(n_overflow, 1ull)] = (int)r;
         }
