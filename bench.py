@@ -446,7 +446,7 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU")
-    ap.add_argument("--cpu-rays", type=int, default=1 << 17, help="rays per step of the CPU sample")
+    ap.add_argument("--cpu-rays", type=int, default=1 << 20, help="rays per step of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=2,
                     help="ray blocks per step of the end-to-end leg (copies overlap compute across blocks)")
