@@ -166,9 +166,17 @@ def cpu_step(P) -> int:
     return int(ri.shape[0])
 
 
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def time_cpu(n_rays: int, steps: int, warmup: int, seed: int = 1234):
     import oracle
 
+    oracle.set_num_threads(host_cores())  # torchrun pins OMP_NUM_THREADS=1 for its workers
     P = cpu_problem(n_rays, seed)
     for _ in range(warmup):
         cpu_step(P)
@@ -251,6 +259,8 @@ def run_ours(args) -> None:
     if world > 1:
         import torch.distributed as dist
 
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     n_rays = args.rays

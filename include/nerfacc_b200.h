@@ -331,7 +331,9 @@ NFB_API int nfb_render_rays_bwd(int from_density, const float* g_colors, const f
  *   bias       : per-ray offset in (0,1] (the reference's `1 - curand_uniform`, drawn by the
  *                caller), or NULL for the unstratified 0.5
  *   max_in / max_out: upper bounds of the per-ray counts (size shared-memory staging; 0 = unknown,
- *                search in global memory). */
+ *                search in global memory).
+ *   out_centres: may be NULL when only the edges are wanted (batched rows, or rows that fit the
+ *                shared-memory staging). */
 NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const int64_t* in_info,
                                     int64_t n_rays, int64_t n_in, int64_t max_in,
                                     const int64_t* n_out_per_ray, int64_t n_out, int64_t max_out,

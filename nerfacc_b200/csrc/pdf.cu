@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_kernel(con
         if (cnt <= 0 || n_out <= 0) continue;
         const int n_in = (int)cnt, last = n_in - 1;
         // stage the rows: [cdfs n_in][vals n_in][centres n_out]
+        // (without a centres output the edges need the shared-memory copy: host guarantees it fits)
         const bool staged = 2 * n_in + n_out <= p.smem_floats_per_warp;
         const float* cdf = p.cdfs + in0;
         const float* val = p.vals + in0;
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_kernel(con
                 const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), __fsub_rn(u_upper, u_lower));
                 t = __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
             }
-            p.out_centres[s0 + sid] = t;
+            if (p.out_centres) p.out_centres[s0 + sid] = t;
             if (cen) cen[sid] = t;
         }
         if (p.out_edges == nullptr) { __syncwarp(); continue; }
@@ -115,6 +116,89 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_kernel(con
             }
         }
         __syncwarp();
+    }
+}
+
+// Batched rows ([n_rays, n_in] -> [n_rays, n_out]): a CTA owns a tile of RT consecutive rays.
+// Their input rows are one contiguous span of global memory, staged with block-wide coalesced
+// loads (all in flight at once); each warp then resamples its rays entirely out of shared
+// memory, and the output tiles (again contiguous spans) leave with block-wide coalesced stores.
+// No per-ray global-memory latency chain remains, which is what bounds the warp-per-ray kernel
+// on short rows.  Shared memory: RT * (2*n_in + 2*n_out + 1) floats.
+struct PdfTileArgs {
+    const float* vals; const float* cdfs; const float* bias;
+    float* out_edges; float* out_centres;  // out_centres may be nullptr
+    long long n_rays;
+    int n_in, n_out, rt;
+};
+
+__global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kernel(const PdfTileArgs p) {
+    extern __shared__ float s_pdf[];
+    const int lane = lane_id(), w = warp_id(), tid = threadIdx.x;
+    const int n_in = p.n_in, n_out = p.n_out, last = n_in - 1;
+    float* s_cdf = s_pdf;                                  // [rt][n_in]
+    float* s_val = s_cdf + (size_t)p.rt * n_in;            // [rt][n_in]
+    float* s_cen = s_val + (size_t)p.rt * n_in;            // [rt][n_out]
+    float* s_edge = s_cen + (size_t)p.rt * n_out;          // [rt][n_out + 1]
+    const long long n_tiles = (p.n_rays + p.rt - 1) / p.rt;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long r0 = tile * p.rt;
+        const int rays = (int)((p.n_rays - r0 < p.rt) ? (p.n_rays - r0) : p.rt);
+        const float* __restrict__ gc = p.cdfs + r0 * n_in;
+        const float* __restrict__ gv = p.vals + r0 * n_in;
+        for (int i = tid; i < rays * n_in; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
+        __syncthreads();
+        for (int j = w; j < rays; j += kPdfWarps) {
+            const float* cdf = s_cdf + (size_t)j * n_in;
+            const float* val = s_val + (size_t)j * n_in;
+            float* cen = s_cen + (size_t)j * n_out;
+            float* edge = s_edge + (size_t)j * (n_out + 1);
+            const float u_floor = cdf[0], u_ceil = cdf[last];
+            const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
+            const float b = p.bias ? __ldg(p.bias + r0 + j) : 0.5f;
+            const float t_min = val[0], t_max = val[last];
+            for (int sid = lane; sid < n_out; sid += 32) {
+                const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
+                const int q = upper_bound(cdf, 0, last, u);
+                const int p0 = max(min(q - 1, last), 0), p1 = max(min(q, last), 0);
+                const float u_lower = cdf[p0], u_upper = cdf[p1], t_lower = val[p0], t_upper = val[p1];
+                float t;
+                if (__fsub_rn(u_upper, u_lower) < 1e-10f) {
+                    t = __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f);
+                } else {
+                    const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), __fsub_rn(u_upper, u_lower));
+                    t = __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
+                }
+                cen[sid] = t;
+            }
+            __syncwarp();
+            // compute_intervels_kernel, pdf.cu:169-241
+            for (int sid = lane; sid < n_out; sid += 32) {
+                if (sid == 0) {
+                    const float t = cen[0], t_next = n_out > 1 ? cen[1] : cen[0];
+                    const float half = __fmul_rn(__fsub_rn(t_next, t), 0.5f);
+                    edge[0] = fmaxf(__fsub_rn(t, half), t_min);
+                    if (n_out == 1) edge[1] = fminf(__fadd_rn(t, half), t_max);
+                } else {
+                    const float t = cen[sid], t_prev = cen[sid - 1];
+                    edge[sid] = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                    if (sid == n_out - 1) {
+                        const float half = __fmul_rn(__fsub_rn(t, t_prev), 0.5f);
+                        edge[sid + 1] = fminf(__fadd_rn(t, half), t_max);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (p.out_edges) {
+            float* __restrict__ ge = p.out_edges + r0 * (n_out + 1);
+            for (int i = tid; i < rays * (n_out + 1); i += kPdfWarps * 32) ge[i] = s_edge[i];
+        }
+        if (p.out_centres) {
+            float* __restrict__ gs = p.out_centres + r0 * n_out;
+            for (int i = tid; i < rays * n_out; i += kPdfWarps * 32) gs[i] = s_cen[i];
+        }
+        __syncthreads();
     }
 }
 
@@ -188,21 +272,46 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
     using namespace nfb;
     NFB_CHECK_ARG(n_rays >= 0, "negative size");
     if (n_rays == 0) return NFB_OK;
-    NFB_CHECK_ARG(vals && cdfs && out_centres, "null pointer");
+    NFB_CHECK_ARG(vals && cdfs && (out_centres || out_edges), "null pointer");
     NFB_CHECK_ARG(in_info != nullptr || n_in > 0, "need in_info or n_in");
     NFB_CHECK_ARG(in_info == nullptr || aligned16(in_info), "packed_info must be 16-byte aligned");
     if (n_out_per_ray) NFB_CHECK_ARG(edge_info && sample_info, "per-ray counts need edge_info and sample_info");
     else NFB_CHECK_ARG(n_out > 0, "n_out must be positive");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (in_info == nullptr && n_out_per_ray == nullptr) {
+        // batched in, batched out: CTA tiles of rays when a useful tile fits in shared memory
+        const long long per_ray = 2 * n_in + 2 * n_out + 1;
+        int rt = 32;
+        while (rt > 4 && per_ray * rt * 4 > 72 * 1024) rt >>= 1;
+        if (per_ray * rt * 4 <= 72 * 1024 && n_in < (1 << 20) && n_out < (1 << 20)) {
+            PdfTileArgs t{};
+            t.vals = vals; t.cdfs = cdfs; t.bias = bias; t.out_edges = out_edges; t.out_centres = out_centres;
+            t.n_rays = n_rays; t.n_in = (int)n_in; t.n_out = (int)n_out; t.rt = rt;
+            const size_t smem = (size_t)per_ray * rt * 4;
+            if (smem > 48 * 1024)
+                cudaFuncSetAttribute(importance_sampling_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            long long blocks = ceil_div<long long>(n_rays, rt);
+            const long long cap = (long long)sm_count() * 8;
+            if (blocks > cap) blocks = cap;
+            importance_sampling_tile_kernel<<<(unsigned)blocks, kPdfWarps * 32, smem, st>>>(t);
+            count_launch();
+            NFB_CHECK_LAUNCH("importance_sampling_tile");
+            return NFB_OK;
+        }
+    }
     PdfArgs a{};
     a.vals = vals; a.cdfs = cdfs; a.in_info = in_info; a.n_in = n_in;
     a.n_out_per_ray = n_out_per_ray; a.n_out = n_out; a.edge_info = edge_info; a.sample_info = sample_info;
     a.bias = bias; a.out_edges = out_edges; a.out_centres = out_centres; a.n_rays = n_rays;
     const long long mi = in_info ? max_in : n_in, mo = n_out_per_ray ? max_out : n_out;
     a.smem_floats_per_warp = pdf_smem_floats((mi > 0 && mo > 0) ? 2 * mi + mo : 0);
+    NFB_CHECK_ARG(out_centres != nullptr || out_edges != nullptr, "nothing to compute");
+    NFB_CHECK_ARG(out_centres != nullptr || (mi > 0 && mo > 0 && 2 * mi + mo <= a.smem_floats_per_warp),
+                  "rows too long to resample without a centres output");
     const size_t smem = (size_t)a.smem_floats_per_warp * 4 * kPdfWarps;
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(importance_sampling_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    importance_sampling_kernel<<<pdf_blocks(n_rays), kPdfWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    importance_sampling_kernel<<<pdf_blocks(n_rays), kPdfWarps * 32, smem, st>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("importance_sampling");
     return NFB_OK;

@@ -79,7 +79,7 @@ class PropNetEstimator(AbstractEstimator):
         intervals = RayIntervals(vals=cdfs)
 
         for level_fn, level_samples in zip(prop_sigma_fns, prop_samples):
-            intervals, _ = importance_sampling(intervals, cdfs, level_samples, stratified)
+            intervals, _ = importance_sampling(intervals, cdfs, level_samples, stratified, _samples=False)
             t_vals = _transform_stot(sampling_type, intervals.vals, near_plane, far_plane)
             t_starts, t_ends = t_vals[..., :-1], t_vals[..., 1:]
             with torch.set_grad_enabled(requires_grad):
@@ -90,7 +90,7 @@ class PropNetEstimator(AbstractEstimator):
                 if requires_grad:
                     self.prop_cache.append((intervals, cdfs))
 
-        intervals, _ = importance_sampling(intervals, cdfs, num_samples, stratified)
+        intervals, _ = importance_sampling(intervals, cdfs, num_samples, stratified, _samples=False)
         t_vals = _transform_stot(sampling_type, intervals.vals, near_plane, far_plane)
         if requires_grad:
             self.prop_cache.append((intervals, None))

@@ -78,6 +78,7 @@ def importance_sampling(
     stratified: bool = False,
     *,
     _bias: Optional[Tensor] = None,
+    _samples: bool = True,
 ) -> Tuple[RayIntervals, RaySamples]:
     """Inverse-transform resampling of every ray (reference nerfacc/pdf.py:66-139).
 
@@ -120,14 +121,16 @@ def importance_sampling(
     if not per_ray:
         n_out = int(n_intervals_per_ray)
         lead = vals.shape[:-1] if vals.dim() > 1 else (n_rays,)
-        centres = torch.empty(lead + (n_out,), dtype=torch.float32, device=dev)
+        # callers that only want the intervals (PropNetEstimator) skip the centres' write-out
+        want_samples = _samples or vals.dim() == 1
+        centres = torch.empty(lead + (n_out,), dtype=torch.float32, device=dev) if want_samples else None
         edges = torch.empty(lead + (n_out + 1,), dtype=torch.float32, device=dev)
         if n_rays > 0 and n_out > 0:
             with torch.cuda.device(dev):
                 rc = _C.lib().nfb_importance_sampling(
                     vals.data_ptr(), cdfs.data_ptr(), _C.ptr(in_info), n_rays, n_in, n_in,
                     None, n_out, n_out, None, None, _C.ptr(bias),
-                    edges.data_ptr(), centres.data_ptr(), _C.stream_ptr(dev))
+                    edges.data_ptr(), _C.ptr(centres), _C.stream_ptr(dev))
             _C.check(rc, "importance_sampling")
         return RayIntervals(vals=edges), RaySamples(vals=centres)
 

@@ -33,6 +33,10 @@ def num_threads() -> int:
     return int(lib().orc_num_threads())
 
 
+def set_num_threads(n: int) -> None:
+    lib().orc_set_num_threads(C.c_int(int(n)))
+
+
 def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 

@@ -201,6 +201,8 @@ def main():
         row(f"importance_sampling [{n5},{n_in}] -> n={n_out}", 8 * n_in * n5 + (8 * n_out + 4) * n5,
             lambda lv=lv, cd=cd, n_out=n_out: nf.importance_sampling(nf.RayIntervals(vals=lv), cd, n_out),
             (lambda lv=lv, cd=cd, n_out=n_out: R.importance_sampling(lv, cd, n_out)) if have_ref else None)
+        row(f"  ... intervals only (PropNetEstimator's call)", 8 * n_in * n5 + (4 * n_out + 8) * n5,
+            lambda lv=lv, cd=cd, n_out=n_out: nf.importance_sampling(nf.RayIntervals(vals=lv), cd, n_out, _samples=False))
         iv, _ = nf.importance_sampling(nf.RayIntervals(vals=lv), cd, n_out)
         lv = iv.vals
         wgt = torch.rand((n5, n_out), device=dev, generator=g0) + 1e-3
