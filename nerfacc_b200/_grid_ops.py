@@ -13,7 +13,7 @@ from torch import Tensor
 from . import _C
 
 _BITS: Dict[int, Tuple[weakref.ref, int, Tensor, Optional[Tensor], int]] = {}
-_MIP_BYTES_MAX = 128 * 1024  # mip kept in shared memory by the marching kernels
+_MIP_BYTES_MAX = 40 * 1024  # mip kept in shared memory by the marching kernels (2 CTAs per SM must fit)
 
 
 def occupancy_bits(binaries: Tensor) -> Tuple[Tensor, Optional[Tensor], int]:

@@ -221,7 +221,7 @@ struct FillPolicy {
 // [prepared-ray pool: warps x kPoolWords x 32 words].
 constexpr int kMarchThreads = 512;
 
-template <bool MIP, class Policy>
+template <bool MIP, bool DIRECT, class Policy>
 __global__ void __launch_bounds__(kMarchThreads, 2)
 march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
              unsigned long long* ray_counter) {
@@ -229,7 +229,7 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
     const GridSpec G = stage_mip(Gp, s_dyn);
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
     uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * kMarchThreads);
-    march_engine<MIP>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
+    march_engine<MIP, DIRECT>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
                  A.hits, A.ray_list, A.ray_list ? A.n_work : A.n_rays, G, opt, P, s_evt, s_pool, ray_counter);
 }
 
@@ -385,7 +385,10 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
                         unsigned long long* counter, cudaStream_t s) {
     const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float) +
                         (size_t)kPoolWords * kMarchThreads * sizeof(uint32_t);
-    auto kernel = G.mip != nullptr ? march_kernel<true, Policy> : march_kernel<false, Policy>;
+    // cone stepping (dt follows t) folds nothing: events are applied in place, without the queue
+    const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
+    auto kernel = G.mip != nullptr ? (direct ? march_kernel<true, true, Policy> : march_kernel<true, false, Policy>)
+                                   : (direct ? march_kernel<false, true, Policy> : march_kernel<false, false, Policy>);
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
         set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
         return NFB_ERR_CUDA;

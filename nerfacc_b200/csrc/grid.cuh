@@ -344,7 +344,7 @@ __device__ __forceinline__ void load_events(const float (&o)[3], const float (&d
 //
 // Shared memory: s_evt = [kQ][blockDim.x] floats (event queue), s_pool = [warps][kPoolWords][32]
 // words (prepared rays).
-template <bool MIP, class Policy>
+template <bool MIP, bool DIRECT, class Policy>
 __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const float* __restrict__ rays_d,
                                              const float* __restrict__ near_arr, float near_s,
@@ -414,6 +414,78 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         seg_steps = 0;
     };
 
+    // ---- the t_last recurrence: one ray boundary / one event
+    auto begin_ray = [&](long long rid) {
+        if (c_have) P.end(c_r, sink, nS, nI, t_last);
+        c_r = rid;
+        t_last = near_arr ? __ldg(near_arr + c_r) : near_s;
+        continuous = false; capped = false; nS = 0; nI = 0;
+        sink = P.begin(c_r);
+        c_have = true;
+    };
+    auto apply = [&](int kind, float t) {
+        if (capped) return;
+        const bool emit = (kind == EV_OCC);
+        const bool doit = !(kind == EV_SEG && continuous);
+        if (step <= 0.0f) {  // one interval per occupied voxel crossing
+            if (!emit) {
+                if (doit) t_last = t;
+            } else {
+                sink.one(P, t_last, t, continuous, nS, nI);
+                nI += continuous ? 1 : 2;
+                nS += 1;
+                continuous = true;
+                t_last = t;
+            }
+        } else if (const_dt) {
+            if (doit) {
+                if (emit) {
+                    t_last = advance(t_last, step, t, cap, nS, [&](float t0, float q, int k) {
+                        sink.run(P, t0, q, k, continuous, nS, nI);
+                        nI += continuous ? k : k + 1;
+                        continuous = true;
+                    });
+                } else {
+                    t_last = advance(t_last, step, t, 0x7fffffff, dummy, NoPiece());
+                }
+            }
+        } else if (!emit) {
+            // cone_angle > 0, skip: dt is fixed at the cell's entry (grid.cu:157-161, 199-203).
+            // Cells are about as long as dt: a few literal steps first, the closed form for
+            // what remains.
+            if (doit) {
+                const float dt = calc_dt(t_last, cone, step);
+                bool more = true;
+#pragma unroll 1
+                for (int i = 0; i < 6; ++i) {
+                    if (__fmaf_rn(dt, 0.5f, t_last) >= t) { more = false; break; }
+                    const float t1 = __fadd_rn(t_last, dt);
+                    if (!(t1 > t_last)) { more = false; break; }
+                    t_last = t1;
+                }
+                if (more) t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
+            }
+        } else {  // cone_angle > 0, emit: dt follows t, a true serial recurrence
+            while (nS < cap) {
+                const float dt = calc_dt(t_last, cone, step);
+                if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
+                const float t_next = __fadd_rn(t_last, dt);
+                if (!(t_next > t_last)) break;  // stuck
+                sink.one(P, t_last, t_next, continuous, nS, nI);
+                nI += continuous ? 1 : 2;
+                nS += 1;
+                continuous = true;
+                t_last = t_next;
+                if (t_next >= t) break;
+            }
+        }
+        if (kind == EV_EMPTY) continuous = false;
+        if (nS >= cap) {
+            capped = true;
+            if (have_ray && r == c_r) { have_ray = false; pend_kind = -1; }  // stop walking it
+        }
+    };
+
     // ------------------------------------------------------------------ prepare (all 32 lanes)
     auto prepare = [&]() {
         unsigned long long base = 0;
@@ -478,7 +550,8 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             const uint32_t* __restrict__ e = pool + pool_head + k;
             r = (long long)(int)e[0];
             const uint32_t misc = e[32];
-            push(EV_RAY, __int_as_float((int)r));
+            if constexpr (DIRECT) begin_ray(r);
+            else push(EV_RAY, __int_as_float((int)r));
             ev_valid = false;
             seg_i = (int)((misc >> 8) & 0xffu);
             pend_kind = -1;
@@ -495,10 +568,14 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     D.stepi[a] = (int)((misc >> (16 + 2 * a)) & 3u) - 1;
                 }
                 // right after the ray starts `continuous` is false: the segment start is a plain skip
-                pend_kind = EV_EMPTY;
-                pend_t = tmin;
-                enter_segment((int)((misc >> 1) & 0x7fu));
                 have_ray = true;
+                if constexpr (DIRECT) {
+                    apply(EV_EMPTY, tmin);
+                } else {
+                    pend_kind = EV_EMPTY;
+                    pend_t = tmin;
+                }
+                enter_segment((int)((misc >> 1) & 0x7fu));
             }
             // a ray without any segment is just its EV_RAY marker (zero samples)
         }
@@ -514,120 +591,67 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             if (j >= nq) continue;
             const int kind = (int)((kinds >> (2 * j)) & 3u);
             const float t = s_evt[j * nthr + tid];
-            if (kind == EV_RAY) {
-                if (c_have) P.end(c_r, sink, nS, nI, t_last);
-                c_r = (long long)__float_as_int(t);
-                t_last = near_arr ? __ldg(near_arr + c_r) : near_s;
-                continuous = false; capped = false; nS = 0; nI = 0;
-                sink = P.begin(c_r);
-                c_have = true;
-                continue;
-            }
-            if (capped) continue;
-            const bool emit = (kind == EV_OCC);
-            const bool doit = !(kind == EV_SEG && continuous);
-            if (step <= 0.0f) {  // one interval per occupied voxel crossing
-                if (!emit) {
-                    if (doit) t_last = t;
-                } else {
-                    sink.one(P, t_last, t, continuous, nS, nI);
-                    nI += continuous ? 1 : 2;
-                    nS += 1;
-                    continuous = true;
-                    t_last = t;
-                }
-            } else if (const_dt) {
-                if (doit) {
-                    if (emit) {
-                        t_last = advance(t_last, step, t, cap, nS, [&](float t0, float q, int k) {
-                            sink.run(P, t0, q, k, continuous, nS, nI);
-                            nI += continuous ? k : k + 1;
-                            continuous = true;
-                        });
-                    } else {
-                        t_last = advance(t_last, step, t, 0x7fffffff, dummy, NoPiece());
-                    }
-                }
-            } else if (!emit) {
-                // cone_angle > 0, skip: dt is fixed at the cell's entry (grid.cu:157-161, 199-203).
-                // Cells are about as long as dt: a few literal steps first, the closed form for
-                // what remains.
-                if (doit) {
-                    const float dt = calc_dt(t_last, cone, step);
-                    bool more = true;
-#pragma unroll 1
-                    for (int i = 0; i < 6; ++i) {
-                        if (__fmaf_rn(dt, 0.5f, t_last) >= t) { more = false; break; }
-                        const float t1 = __fadd_rn(t_last, dt);
-                        if (!(t1 > t_last)) { more = false; break; }
-                        t_last = t1;
-                    }
-                    if (more) t_last = advance(t_last, dt, t, 0x7fffffff, dummy, NoPiece());
-                }
-            } else {  // cone_angle > 0, emit: dt follows t, a true serial recurrence
-                while (nS < cap) {
-                    const float dt = calc_dt(t_last, cone, step);
-                    if (__fmaf_rn(dt, 0.5f, t_last) >= t) break;
-                    const float t_next = __fadd_rn(t_last, dt);
-                    if (!(t_next > t_last)) break;  // stuck
-                    sink.one(P, t_last, t_next, continuous, nS, nI);
-                    nI += continuous ? 1 : 2;
-                    nS += 1;
-                    continuous = true;
-                    t_last = t_next;
-                    if (t_next >= t) break;
-                }
-            }
-            if (kind == EV_EMPTY) continuous = false;
-            if (nS >= cap) {
-                capped = true;
-                if (have_ray && r == c_r) { have_ray = false; pend_kind = -1; }  // stop walking it
-            }
+            if (kind == EV_RAY) begin_ray((long long)__float_as_int(t));
+            else apply(kind, t);
         }
         nq = 0;
         kinds = 0;
     };
+    // DIRECT (cone stepping: no event folds, dt follows t): events are applied where they arise,
+    // as the reference does, instead of going through the queue
+    auto event = [&](int kind, float t) {
+        if constexpr (DIRECT) apply(kind, t);
+        else push(kind, t);
+    };
 
     while (true) {
-        refill();
-        if (!__any_sync(kFull, have_ray)) {
-            // nothing to walk: queues are full (the replay frees them), the pool came back empty
-            // (masked rays; try again), or the work is done
-            consume();
-            if (exhausted && pool_head == pool_cnt) break;
-            continue;
-        }
-        // ------------------------------------------------------------------ produce
-        int steps = 0;
-        while (have_ray && steps < kRoundSteps && nq <= kQ - 3) {
-            if (!in_seg) {
-                // a later segment of a multi-level march (the first one came prepared)
-                if (m == 1) { push_pending(); have_ray = false; break; }
-                float o[3], d[3];
+        // ------------------------------------------------------------------ switch / retire
+        // One round = (a) the lanes whose segment ended switch to their next segment or retire
+        // the ray, then (b) all lanes walk up to kRoundSteps cells together.  Keeping (a) out of
+        // the walk matters for nested grids: a lane that switched inside the walk would run the
+        // rest of its round alone.
+        if (have_ray && !in_seg && nq <= kQ - 3) {
+            // a later segment of a multi-level march (the first one came prepared)
+            bool found = false;
+            float tmin = 0.0f;
+            int level = 0;
+            float o[3], d[3];
+            if (m > 1) {
 #pragma unroll
                 for (int k = 0; k < 3; ++k) { o[k] = __ldg(rays_o + 3 * r + k); d[k] = __ldg(rays_d + 3 * r + k); }
                 if (!ev_valid) { load_events(o, d, r, t_sorted, t_indices, hits, G, ev); ev_valid = true; }
                 const float near = near_arr ? __ldg(near_arr + r) : near_s;
                 const float far = far_arr ? __ldg(far_arr + r) : far_s;
-                float tmin = 0.0f;
-                int level = 0;
-                if (!find_segment(ev, m, seg_i, near, far, tmin, tmax_seg, level)) {
-                    push_pending();
-                    have_ray = false;
-                    break;
-                }
+                found = find_segment(ev, m, seg_i, near, far, tmin, tmax_seg, level);
+            }
+            if (!found) {
+                push_pending();
+                have_ray = false;
+            } else {
                 // "if (!continuous) skip to tmin": after empty cells `continuous` is known to be
                 // false and the event is a plain skip
                 if (pend_kind == EV_EMPTY && fold_empty) {
                     pend_t = tmin;
                 } else {
                     push_pending();
-                    push(EV_SEG, tmin);
+                    event(EV_SEG, tmin);
                 }
                 setup_dda(o, d, G, level, tmin, tmax_seg, D);
                 enter_segment(level);
-                continue;
             }
+        }
+        // ------------------------------------------------------------------ refill
+        refill();
+        if (!__any_sync(kFull, have_ray)) {
+            // nothing to walk: queues are full (the replay frees them), the pool came back empty
+            // (masked rays; try again), or the work is done
+            if constexpr (!DIRECT) consume();
+            if (exhausted && pool_head == pool_cnt) break;
+            continue;
+        }
+        // ------------------------------------------------------------------ produce
+        int steps = 0;
+        if (have_ray && in_seg && nq <= kQ - 3) {
             // the DDA proper (grid.cu:183-281), branch-free; leaves the loop when the segment
             // ends, the round is over or the queue is (nearly) full
             do {
@@ -642,8 +666,12 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 uint32_t word = 0u;
                 if (cbit) word = __ldg(G.occ_bits + (cell >> 5));
                 const int kind = (int)((word >> (cell & 31)) & 1u);  // EV_OCC == 1, EV_EMPTY == 0
-                if (kind != pend_kind || !(kind == EV_OCC ? fold_occ : fold_empty)) { push_pending(); pend_kind = kind; }
-                pend_t = t_trav;
+                if constexpr (DIRECT) {
+                    apply(kind, t_trav);
+                } else {
+                    if (kind != pend_kind || !(kind == EV_OCC ? fold_occ : fold_empty)) { push_pending(); pend_kind = kind; }
+                    pend_t = t_trav;
+                }
                 // single_traversal, utils_grid.cuh:116-142: x if strictly smallest, else y if < z, else z
                 const bool px = D.tdist[0] < D.tdist[1] && D.tdist[0] < D.tdist[2];
                 const bool py = !px && D.tdist[1] < D.tdist[2];
@@ -659,10 +687,12 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                    (pz && D.cur[2] == D.stop[2]);
                 if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
                 ++steps;
-            } while (in_seg && steps < kRoundSteps && nq <= kQ - 3);
+            } while (in_seg && steps < kRoundSteps && nq <= kQ - 3 && (!DIRECT || have_ray));
         }
         // ------------------------------------------------------------------ consume
-        if (eager || __any_sync(kFull, nq > kQ - 6)) consume();
+        if constexpr (!DIRECT) {
+            if (eager || __any_sync(kFull, nq > kQ - 6)) consume();
+        }
     }
     if (c_have) P.end(c_r, sink, nS, nI, t_last);
 }
