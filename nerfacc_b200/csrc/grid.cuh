@@ -457,7 +457,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 const float dt = calc_dt(t_last, cone, step);
                 bool more = true;
 #pragma unroll 1
-                for (int i = 0; i < 6; ++i) {
+                for (int i = 0; i < 12; ++i) {
                     if (__fmaf_rn(dt, 0.5f, t_last) >= t) { more = false; break; }
                     const float t1 = __fadd_rn(t_last, dt);
                     if (!(t1 > t_last)) { more = false; break; }
