@@ -53,7 +53,7 @@ struct CountSink {
 // Run buffer written by the count pass when marching with a constant dt (cone_angle == 0,
 // step_size > 0): per ray up to kRunSlots runs (t0, q, n, s0) — n samples whose edges are
 // t0 + j*q, the first of them sample s0 of the ray — followed by one int32 run count per ray
-// (> kRunSlots: the ray overflowed and is re-marched by the fill pass).  Only the slots in use
+// (kRunSlots + 1: the run pool was full and the ray is marched again by the fill pass).  Only the slots in use
 // are ever touched, so the traffic is ~2 sectors per ray, not the reserved 128 bytes.
 constexpr int kRunSlots = 8;
 struct __align__(16) Run { float t0, q; int n, s0; };
@@ -157,6 +157,7 @@ struct CountPolicy {
     RunPool pool;
     __device__ __forceinline__ bool accept(long long) const { return true; }
     __device__ __forceinline__ void skipped(long long) const {}
+    __device__ __forceinline__ bool wants_term() const { return term != nullptr; }
     __device__ __forceinline__ Sink begin(long long r) const {
         Sink s;
         if constexpr (RUNS) { s.idx = 0; s.r = (int)r; s.failed = false; }
@@ -184,13 +185,12 @@ struct FillPolicy {
     // two-pass: skip rays whose count (info[2r+1]) is zero; single pass: write the counts
     int64_t* sample_info; int64_t* interval_info; bool single_pass;
     float* term;
-    const int* __restrict__ only_overflowed;  // n_runs of the count pass: march overflowed rays only
     Sink proto;
     __device__ __forceinline__ bool masked(long long r) const { return rays_mask != nullptr && !rays_mask[r]; }
+    __device__ __forceinline__ bool wants_term() const { return term != nullptr; }
     __device__ __forceinline__ bool accept(long long r) const {
         if (masked(r)) return false;
         if (!single_pass && sample_info[2 * r + 1] == 0) return false;  // grid.cu:103-106
-        if (only_overflowed != nullptr && only_overflowed[r] <= kRunSlots) return false;
         return true;
     }
     __device__ __forceinline__ void skipped(long long r) const {
@@ -238,7 +238,8 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
 // output.  Each lane stages its ray's runs in shared memory; then the whole warp expands run
 // after run — lane j of the warp writes sample j, j+32, ... of the run — so ray_indices /
 // t_starts / t_ends are written as contiguous warp stores instead of 32 scattered scalars.
-// Rays whose run list overflowed are left to a march_kernel launch restricted to them.
+// Runs beyond a ray's inline slots are expanded from the pool by traverse_expand_pool_kernel;
+// rays flagged kRunSlots + 1 (pool full) are left to a march_kernel launch over a work list.
 constexpr int kExpandWarps = 8;
 __global__ void __launch_bounds__(kExpandWarps * 32)
 traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info,
@@ -626,7 +627,7 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
     P.rays_mask = nullptr; P.near_arr = A.near_arr; P.near_s = A.near_s;
     P.sm_starts = sample_info; P.sm_stride = 2;
     P.sample_info = const_cast<int64_t*>(sample_info); P.interval_info = nullptr; P.single_pass = false;
-    P.term = nullptr; P.only_overflowed = nullptr;
+    P.term = nullptr;
     P.proto.ray_indices = ray_indices; P.proto.t_starts = t_starts; P.proto.t_ends = t_ends;
     return launch_march(A, to_grid(grid), to_opts(march), P, counters, s);
 }
@@ -651,7 +652,6 @@ NFB_API int nfb_traverse_fill(const nfb_rays_t* rays, const nfb_grid_t* grid,
     FillPolicy<true> P{};
     P.near_arr = A.near_arr; P.near_s = A.near_s;
     P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
-    P.only_overflowed = nullptr;
     P.proto.iv_vals = iv_vals; P.proto.iv_ray = iv_ray_indices; P.proto.iv_left = iv_is_left; P.proto.iv_right = iv_is_right;
     P.proto.sm_vals = sm_vals; P.proto.sm_ray = sm_ray_indices; P.proto.sm_valid = sm_is_valid;
     if (over_allocate) {

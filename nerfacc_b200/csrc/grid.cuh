@@ -338,7 +338,7 @@ __device__ __forceinline__ void load_events(const float (&o)[3], const float (&d
 
 // Policy interface (see grid.cu):
 //   typename Sink;  bool accept(r);  void skipped(r);  Sink begin(r);
-//   void end(r, Sink&, nS, nI, t_last);
+//   void end(r, Sink&, nS, nI, t_last);  bool wants_term();
 // Sink: run(P, t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
 // and one(P, t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
 //
@@ -625,6 +625,9 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 found = find_segment(ev, m, seg_i, near, far, tmin, tmax_seg, level);
             }
             if (!found) {
+                // the ray is over: a trailing skip only moves t_last, which nobody reads unless the
+                // termination planes are wanted
+                if (pend_kind == EV_EMPTY && !P.wants_term()) pend_kind = -1;
                 push_pending();
                 have_ray = false;
             } else {

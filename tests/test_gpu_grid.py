@@ -287,3 +287,23 @@ def test_ema_update_with_duplicates_and_compaction(device):
     ri = np.sort(rng.integers(0, 999, m)); ts = rng.random(m).astype(np.float32); te = ts + 1
     a, b2, c = _occ_ops.compact_samples(*[torch.from_numpy(x).to(device) for x in (mask, ri, ts, te)], 999)
     assert (a.cpu().numpy() == ri[mask]).all() and (b2.cpu().numpy() == ts[mask]).all() and (c.cpu().numpy() == te[mask]).all()
+
+
+def test_sampling_run_pool_overflow(device):
+    """Busy grid (40 % random cells): dozens of runs per ray, far beyond the 8 inline slots and
+    the run pool (2 per ray), so most rays take the re-march work list — bit-exact all the same."""
+    import nerfacc_b200 as nf
+
+    rng = np.random.default_rng(123)
+    n_rays, res = 5000, 48
+    o = (rng.standard_normal((n_rays, 3)) * 0.3).astype(np.float32)
+    d = rng.standard_normal((n_rays, 3)).astype(np.float32); d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    bins = rng.random((1, res, res, res)) < 0.4
+    est = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=res, levels=1).to(device)
+    est.binaries = torch.from_numpy(bins).to(device)
+    to, td = _gpu(device, o, d)
+    ri, ts, te = est.sampling(to, td, render_step_size=4e-3)
+    r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, est.aabbs.cpu().numpy(), render_step_size=4e-3)
+    assert ri.shape[0] == r_ri.shape[0] > 50 * n_rays
+    assert (ri.cpu().numpy() == r_ri).all()
+    assert (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
