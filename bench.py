@@ -411,6 +411,10 @@ def run_ours(args) -> None:
         kd = kernels[dom]
         roofline = {"kernel": dom, "bound": "hbm", "achieved": kd["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": kd["frac"], "traffic": None, "peak_source": peak_src,
+                    "note": ("the dominant kernel is the DDA march: an instruction-issue-bound serial walk per ray "
+                             "(ncu: issue slots ~77 % busy, DRAM <1 %; profiles/r01_c_ncu_step_summary.txt), so its "
+                             "HBM fraction is small by nature; the step's streaming kernels are in `kernels` and "
+                             "`hbm_kernels`"),
                     "algorithmic_bytes_per_launch": kd["bytes"], "avg_launch_ms": kd["avg_ms"]}
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
@@ -418,6 +422,15 @@ def run_ours(args) -> None:
         except Exception:
             pass
 
+    # time-weighted HBM fraction of the step's streaming (HBM-bound) kernels, the march aside
+    stream_names = [k for k in kernels if "bytes" in kernels[k] and k != "traverse_count"]
+    hbm_kernels = None
+    if stream_names:
+        by = sum(kernels[k]["bytes"] * kernels[k]["launches_per_step"] for k in stream_names)
+        tm = sum(kernels[k]["avg_ms"] * kernels[k]["launches_per_step"] for k in stream_names)
+        hbm_kernels = {"kernels": stream_names, "bytes_per_step": by, "ms_per_step": tm,
+                       "achieved": by / (tm * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                       "frac": by / (tm * 1e-3) / 1e9 / peak}
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -442,7 +455,7 @@ def run_ours(args) -> None:
                             "pinned-host rays in, colours/opacity/depth out to pinned host, every step; "
                             "H2D / compute / D2H on three streams"},
         "gpu_launches": launches,
-        "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu, "clocks": clk,
+        "roofline": roofline, "hbm_kernels": hbm_kernels, "kernels": kernels, "cpu_baseline": cpu, "clocks": clk,
     }
     print(json.dumps(line), flush=True)
     if dist is not None:

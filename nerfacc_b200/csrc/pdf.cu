@@ -121,25 +121,28 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_kernel(con
 
 // Batched rows ([n_rays, n_in] -> [n_rays, n_out]): a CTA owns a tile of RT consecutive rays.
 // Their input rows are one contiguous span of global memory, staged with block-wide coalesced
-// loads (all in flight at once); each warp then resamples its rays entirely out of shared
-// memory, and the output tiles (again contiguous spans) leave with block-wide coalesced stores.
-// No per-ray global-memory latency chain remains, which is what bounds the warp-per-ray kernel
-// on short rows.  Shared memory: RT * (2*n_in + 2*n_out + 1) floats.
+// loads (all in flight at once); each warp then resamples its rays out of shared memory.  The
+// interval edges need the neighbouring centres: those travel between lanes by shuffle (lane 0
+// carries the last centre of the previous 32), so centres and edges go straight from registers
+// to global memory as coalesced row stores — no second pass, no staging of the outputs.
+// With few input bins (n_in - 1 <= 32 and well below n_out) the per-bin slope
+// (t_upper - t_lower) / (u_upper - u_lower) is computed once per bin instead of once per sample
+// (same operands, same IEEE quotient).  Shared memory: RT * 2 * n_in floats (+ 64 per warp).
 struct PdfTileArgs {
     const float* vals; const float* cdfs; const float* bias;
-    float* out_edges; float* out_centres;  // out_centres may be nullptr
+    float* out_edges; float* out_centres;  // either may be nullptr
     long long n_rays;
     int n_in, n_out, rt;
+    bool bin_slopes;
 };
 
 __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kernel(const PdfTileArgs p) {
     extern __shared__ float s_pdf[];
     const int lane = lane_id(), w = warp_id(), tid = threadIdx.x;
     const int n_in = p.n_in, n_out = p.n_out, last = n_in - 1;
-    float* s_cdf = s_pdf;                                  // [rt][n_in]
-    float* s_val = s_cdf + (size_t)p.rt * n_in;            // [rt][n_in]
-    float* s_cen = s_val + (size_t)p.rt * n_in;            // [rt][n_out]
-    float* s_edge = s_cen + (size_t)p.rt * n_out;          // [rt][n_out + 1]
+    float* s_cdf = s_pdf;                              // [rt][n_in]
+    float* s_val = s_cdf + (size_t)p.rt * n_in;        // [rt][n_in]
+    float* s_bin = s_val + (size_t)p.rt * n_in + w * 64;  // per warp: [32] slope, [32] degenerate midpoint
     const long long n_tiles = (p.n_rays + p.rt - 1) / p.rt;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long r0 = tile * p.rt;
@@ -151,52 +154,66 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
         for (int j = w; j < rays; j += kPdfWarps) {
             const float* cdf = s_cdf + (size_t)j * n_in;
             const float* val = s_val + (size_t)j * n_in;
-            float* cen = s_cen + (size_t)j * n_out;
-            float* edge = s_edge + (size_t)j * (n_out + 1);
+            float* __restrict__ ge = p.out_edges ? p.out_edges + (r0 + j) * (n_out + 1) : nullptr;
+            float* __restrict__ gs = p.out_centres ? p.out_centres + (r0 + j) * n_out : nullptr;
             const float u_floor = cdf[0], u_ceil = cdf[last];
             const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
             const float b = p.bias ? __ldg(p.bias + r0 + j) : 0.5f;
             const float t_min = val[0], t_max = val[last];
-            for (int sid = lane; sid < n_out; sid += 32) {
-                const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
-                const int q = upper_bound(cdf, 0, last, u);
-                const int p0 = max(min(q - 1, last), 0), p1 = max(min(q, last), 0);
-                const float u_lower = cdf[p0], u_upper = cdf[p1], t_lower = val[p0], t_upper = val[p1];
-                float t;
-                if (__fsub_rn(u_upper, u_lower) < 1e-10f) {
-                    t = __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f);
-                } else {
-                    const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), __fsub_rn(u_upper, u_lower));
-                    t = __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
+            if (p.bin_slopes) {
+                if (lane < last) {
+                    const float du = __fsub_rn(cdf[lane + 1], cdf[lane]);
+                    const bool flat = du < 1e-10f;
+                    // a flat bin (pdf.cu:159-160) keeps its midpoint in the second slot; other bins a NaN there
+                    s_bin[lane] = __fdiv_rn(__fsub_rn(val[lane + 1], val[lane]), du);
+                    s_bin[32 + lane] = flat ? __fmul_rn(__fadd_rn(val[lane], val[lane + 1]), 0.5f) : __int_as_float(0x7fc00000);
                 }
-                cen[sid] = t;
+                __syncwarp();
             }
-            __syncwarp();
-            // compute_intervels_kernel, pdf.cu:169-241
-            for (int sid = lane; sid < n_out; sid += 32) {
-                if (sid == 0) {
-                    const float t = cen[0], t_next = n_out > 1 ? cen[1] : cen[0];
-                    const float half = __fmul_rn(__fsub_rn(t_next, t), 0.5f);
-                    edge[0] = fmaxf(__fsub_rn(t, half), t_min);
-                    if (n_out == 1) edge[1] = fminf(__fadd_rn(t, half), t_max);
-                } else {
-                    const float t = cen[sid], t_prev = cen[sid - 1];
-                    edge[sid] = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
-                    if (sid == n_out - 1) {
-                        const float half = __fmul_rn(__fsub_rn(t, t_prev), 0.5f);
-                        edge[sid + 1] = fminf(__fadd_rn(t, half), t_max);
+            float carry_prev = 0.0f;  // centre of sample i0 - 1
+            for (int i0 = 0; i0 < n_out; i0 += 32) {
+                const int sid = i0 + lane;
+                const bool valid = sid < n_out;
+                float t = 0.0f;
+                if (valid) {
+                    const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
+                    const int q = upper_bound(cdf, 0, last, u);
+                    const int p0 = max(min(q - 1, last), 0), p1 = max(min(q, last), 0);
+                    const float u_lower = cdf[p0], t_lower = val[p0];
+                    if (p.bin_slopes && p1 == p0 + 1) {
+                        const float mid = s_bin[32 + p0];
+                        t = (mid == mid) ? mid : __fmaf_rn(__fsub_rn(u, u_lower), s_bin[p0], t_lower);
+                    } else {
+                        const float u_upper = cdf[p1], t_upper = val[p1];
+                        if (__fsub_rn(u_upper, u_lower) < 1e-10f) {
+                            t = __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f);
+                        } else {
+                            const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), __fsub_rn(u_upper, u_lower));
+                            t = __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
+                        }
+                    }
+                    if (gs) gs[sid] = t;
+                }
+                // compute_intervels_kernel, pdf.cu:169-241
+                float t_prev = __shfl_up_sync(kFull, t, 1);
+                if (lane == 0) t_prev = carry_prev;
+                const float t_next = __shfl_down_sync(kFull, t, 1);
+                carry_prev = __shfl_sync(kFull, t, 31);
+                if (valid && ge) {
+                    if (sid == 0) {
+                        const float half = __fmul_rn(__fsub_rn(n_out > 1 ? t_next : t, t), 0.5f);
+                        ge[0] = fmaxf(__fsub_rn(t, half), t_min);
+                        if (n_out == 1) ge[1] = fminf(__fadd_rn(t, half), t_max);
+                    } else {
+                        ge[sid] = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                        if (sid == n_out - 1) {
+                            const float half = __fmul_rn(__fsub_rn(t, t_prev), 0.5f);
+                            ge[sid + 1] = fminf(__fadd_rn(t, half), t_max);
+                        }
                     }
                 }
             }
-        }
-        __syncthreads();
-        if (p.out_edges) {
-            float* __restrict__ ge = p.out_edges + r0 * (n_out + 1);
-            for (int i = tid; i < rays * (n_out + 1); i += kPdfWarps * 32) ge[i] = s_edge[i];
-        }
-        if (p.out_centres) {
-            float* __restrict__ gs = p.out_centres + r0 * n_out;
-            for (int i = tid; i < rays * n_out; i += kPdfWarps * 32) gs[i] = s_cen[i];
+            __syncwarp();
         }
         __syncthreads();
     }
@@ -280,16 +297,16 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (in_info == nullptr && n_out_per_ray == nullptr) {
         // batched in, batched out: CTA tiles of rays when a useful tile fits in shared memory
-        const long long per_ray = 2 * n_in + 2 * n_out + 1;
-        int rt = 32;
-        while (rt > 4 && per_ray * rt * 4 > 72 * 1024) rt >>= 1;
-        if (per_ray * rt * 4 <= 72 * 1024 && n_in < (1 << 20) && n_out < (1 << 20)) {
+        const long long per_ray = 2 * n_in;
+        const long long fixed = (long long)kPdfWarps * 64;
+        int rt = 64;
+        while (rt > 4 && (per_ray * rt + fixed) * 4 > 48 * 1024) rt >>= 1;
+        if ((per_ray * rt + fixed) * 4 <= 48 * 1024 && n_in < (1 << 20) && n_out < (1 << 20)) {
             PdfTileArgs t{};
             t.vals = vals; t.cdfs = cdfs; t.bias = bias; t.out_edges = out_edges; t.out_centres = out_centres;
             t.n_rays = n_rays; t.n_in = (int)n_in; t.n_out = (int)n_out; t.rt = rt;
-            const size_t smem = (size_t)per_ray * rt * 4;
-            if (smem > 48 * 1024)
-                cudaFuncSetAttribute(importance_sampling_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            t.bin_slopes = (n_in - 1 <= 32) && (2 * (n_in - 1) <= n_out);
+            const size_t smem = (size_t)(per_ray * rt + fixed) * 4;
             long long blocks = ceil_div<long long>(n_rays, rt);
             const long long cap = (long long)sm_count() * 8;
             if (blocks > cap) blocks = cap;
