@@ -584,15 +584,38 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         __syncwarp();
     };
 
+    // Replay of the queued events.  Each lane keeps its own cursor: at every step the warp runs
+    // the ONE code path (ray boundary / skip / emit) that most lanes are waiting for, and only
+    // those lanes move on.  Lanes whose rays are at different phases thereby fall into step
+    // (skip, emit, skip, emit, ...) instead of splitting every queue position three ways.
     auto consume = [&]() {
-        const int maxq = __reduce_max_sync(kFull, nq);
+        int jq = 0;
 #pragma unroll 1
-        for (int j = 0; j < maxq; ++j) {
-            if (j >= nq) continue;
-            const int kind = (int)((kinds >> (2 * j)) & 3u);
-            const float t = s_evt[j * nthr + tid];
-            if (kind == EV_RAY) begin_ray((long long)__float_as_int(t));
-            else apply(kind, t);
+        while (true) {
+            int kind = 0, path = 0;  // path: 0 nothing left, 1 ray boundary, 2 skip, 3 emit, 4 no-op
+            float t = 0.0f;
+            if (jq < nq) {
+                kind = (int)((kinds >> (2 * jq)) & 3u);
+                t = s_evt[jq * nthr + tid];
+                if (kind == EV_RAY) path = 1;
+                else if (capped || (kind == EV_SEG && continuous)) path = 4;
+                else path = (kind == EV_OCC) ? 3 : 2;
+            }
+            if (path == 4) ++jq;  // nothing to do for this event: it costs no turn
+            const unsigned m_ray = __ballot_sync(kFull, path == 1);
+            const unsigned m_skip = __ballot_sync(kFull, path == 2);
+            const unsigned m_emit = __ballot_sync(kFull, path == 3);
+            if ((m_ray | m_skip | m_emit) == 0u) {
+                if (__ballot_sync(kFull, path == 4) == 0u) break;
+                continue;
+            }
+            const int c_ray = __popc(m_ray), c_skip = __popc(m_skip), c_emit = __popc(m_emit);
+            const int chosen = (c_skip >= c_emit && c_skip >= c_ray) ? 2 : (c_emit >= c_ray ? 3 : 1);
+            if (path == chosen) {
+                if (chosen == 1) begin_ray((long long)__float_as_int(t));
+                else apply(kind, t);
+                ++jq;
+            }
         }
         nq = 0;
         kinds = 0;
