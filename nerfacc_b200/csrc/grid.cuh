@@ -717,7 +717,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         }
         // ------------------------------------------------------------------ consume
         if constexpr (!DIRECT) {
-            if (eager || __any_sync(kFull, nq > kQ - 6)) consume();
+            if (eager || __any_sync(kFull, nq > kQ - 4)) consume();
         }
     }
     if (c_have) P.end(c_r, sink, nS, nI, t_last);
