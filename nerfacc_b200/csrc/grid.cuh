@@ -250,7 +250,7 @@ struct NoPiece {
 //   EV_SEG    segment start:     if (!continuous) skip to t           (grid.cu:150-163)
 //   EV_RAY    a new ray starts:  payload = ray id; retires the previous ray of the lane
 constexpr int kQ = 16;          // events queued per lane
-constexpr int kRoundSteps = 16; // DDA cells per lane between two refill checks
+constexpr int kRoundSteps = 32; // DDA cells per lane between two refill checks
 constexpr int kPoolWords = 16;  // words per prepared ray (x 32 slots per warp)
 enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2, EV_RAY = 3 };
 
