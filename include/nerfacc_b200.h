@@ -82,6 +82,25 @@ NFB_API int nfb_prod_scan_bwd_f32(const float* grad_out, const float* in, const 
                                   int64_t n, int exclusive, int canonical, void* workspace,
                                   size_t workspace_bytes, uint32_t epoch, nfb_stream_t stream);
 
+/*
+ * Head bits: the ray boundaries of a canonical packed_info as one bit per sample (bit i set iff
+ * sample i is the first of a ray; bit n always set), `nfb_head_bits_bytes(n)` bytes.  Built once
+ * per packed_info (the call clears `bits` itself) and shared by every scan over that layout:
+ * the `_bits` scans below read 1 bit per sample instead of searching packed_info per tile, and
+ * every warp works on its own (warp-granular look-back, no block barrier).  Same results as
+ * nfb_scan_f32 / nfb_prod_scan_bwd_f32 with canonical=1 (reference: csrc/scan.cu:9-304).
+ */
+NFB_API size_t nfb_head_bits_bytes(int64_t n_elements);
+NFB_API int nfb_head_bits(const int64_t* packed_info, int64_t n_rays, int64_t n, uint32_t* bits,
+                          nfb_stream_t stream);
+NFB_API int nfb_scan_bits_f32(const float* in, float* out, const uint32_t* head_bits, int64_t n,
+                              int op, int exclusive, int reverse, void* workspace,
+                              size_t workspace_bytes, uint32_t epoch, nfb_stream_t stream);
+NFB_API int nfb_prod_scan_bwd_bits_f32(const float* grad_out, const float* in, const float* out,
+                                       float* grad_in, const uint32_t* head_bits, int64_t n,
+                                       int exclusive, void* workspace, size_t workspace_bytes,
+                                       uint32_t epoch, nfb_stream_t stream);
+
 /* ------------------------------------------------------------------------------------
  * Fused volume-rendering weights (forward).
  * Replaces the torch composites render_transmittance_from_alpha/density,

@@ -61,6 +61,11 @@ _PROTOS = {
                      c_ptr, c_size, c_u32, c_ptr],
     "nfb_prod_scan_bwd_f32": [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_int,
                               c_ptr, c_size, c_u32, c_ptr],
+    "nfb_head_bits_bytes": [c_i64],
+    "nfb_head_bits": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
+    "nfb_scan_bits_f32": [c_ptr, c_ptr, c_ptr, c_i64, c_int, c_int, c_int, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_prod_scan_bwd_bits_f32": [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_int, c_ptr, c_size, c_u32,
+                                   c_ptr],
     "nfb_render_weight_fwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64,
                               c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_f32, c_ptr, c_size, c_u32, c_ptr],
     "nfb_render_weight_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
@@ -104,6 +109,7 @@ _RESTYPES = {
     "nfb_last_error": C.c_char_p,
     "nfb_launch_count": C.c_longlong,
     "nfb_workspace_bytes": C.c_size_t,
+    "nfb_head_bits_bytes": C.c_size_t,
     "nfb_occ_binarize_workspace_bytes": C.c_size_t,
     "nfb_compact_workspace_bytes": C.c_size_t,
     "nfb_traverse_run_bytes": C.c_size_t,

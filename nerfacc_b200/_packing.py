@@ -17,7 +17,8 @@ from typing import Dict, Optional, Tuple
 
 import torch
 
-_CANONICAL: Dict[int, Tuple[weakref.ref, int]] = {}
+_CANONICAL: Dict[int, Tuple[weakref.ref, int, Optional[int]]] = {}
+_HEAD_BITS: Dict[int, Tuple[weakref.ref, int, torch.Tensor]] = {}
 _PACKED_OF: Dict[int, Tuple[weakref.ref, int, torch.Tensor, int]] = {}
 
 
@@ -27,10 +28,43 @@ def _drop(table, key):
     return cb
 
 
-def mark_canonical(packed_info: torch.Tensor) -> torch.Tensor:
+def mark_canonical(packed_info: torch.Tensor, total: Optional[int] = None) -> torch.Tensor:
+    """`total`: set when the layout is also dense — the chunks tile [0, total) without gaps
+    (not the case for over-allocated traversals)."""
     key = id(packed_info)
-    _CANONICAL[key] = (weakref.ref(packed_info, _drop(_CANONICAL, key)), packed_info._version)
+    _CANONICAL[key] = (weakref.ref(packed_info, _drop(_CANONICAL, key)), packed_info._version,
+                       None if total is None else int(total))
     return packed_info
+
+
+def dense_total(packed_info: torch.Tensor) -> Optional[int]:
+    ent = _CANONICAL.get(id(packed_info))
+    if ent is None or ent[0]() is not packed_info or ent[1] != packed_info._version:
+        return None
+    return ent[2]
+
+
+def head_bits(packed_info: torch.Tensor, n: int) -> Optional[torch.Tensor]:
+    """The 1-bit-per-sample ray boundaries of a dense canonical `packed_info` over n samples
+    (nfb_head_bits), built on first use and kept as long as the packed_info tensor lives;
+    None when the layout is not known to be dense."""
+    if dense_total(packed_info) != int(n) or n == 0:
+        return None
+    key = id(packed_info)
+    ent = _HEAD_BITS.get(key)
+    if ent is not None and ent[0]() is packed_info and ent[1] == packed_info._version:
+        return ent[2]
+    from . import _C
+
+    dev = packed_info.device
+    lib = _C.lib()
+    bits = torch.empty((int(lib.nfb_head_bits_bytes(n)) + 3) // 4, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.nfb_head_bits(packed_info.data_ptr(), packed_info.shape[0], n, bits.data_ptr(),
+                               _C.stream_ptr(dev))
+    _C.check(rc, "head_bits")
+    _HEAD_BITS[key] = (weakref.ref(packed_info, _drop(_HEAD_BITS, key)), packed_info._version, bits)
+    return bits
 
 
 def is_canonical(packed_info: torch.Tensor) -> bool:

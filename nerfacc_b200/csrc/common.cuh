@@ -77,6 +77,30 @@ __device__ __forceinline__ void stg_stream(float* p, float v) {
     asm volatile("st.global.L1::no_allocate.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
 }
 
+// Predicated forms: the access happens only when `on`; the registers keep their value otherwise.
+// The predicate lives inside the asm so that a tile-edge test never becomes a branch: a branch
+// around a load makes ptxas merge the result through a temporary, and the MOV that follows the
+// LDG then waits for the data — four dependent DRAM round trips per thread instead of four
+// loads in flight.
+__device__ __forceinline__ void ldg_stream4_if(bool on, const float* p, float& a, float& b, float& c, float& d) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %5, 0;\n\t"
+                 "@q ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "+f"(a), "+f"(b), "+f"(c), "+f"(d) : "l"(p), "r"((int)on));
+}
+__device__ __forceinline__ void ldg_stream_if(bool on, const float* p, float& a) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t"
+                 "@q ld.global.nc.L1::no_allocate.f32 %0, [%1];\n\t}" : "+f"(a) : "l"(p), "r"((int)on));
+}
+__device__ __forceinline__ void stg_stream4_if(bool on, float* p, float a, float b, float c, float d) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %5, 0;\n\t"
+                 "@q st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};\n\t}"
+                 :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "r"((int)on) : "memory");
+}
+__device__ __forceinline__ void stg_stream_if(bool on, float* p, float a) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\t"
+                 "@q st.global.L1::no_allocate.f32 [%0], %1;\n\t}" :: "l"(p), "f"(a), "r"((int)on) : "memory");
+}
+
 // 64-bit relaxed device-scope accesses for look-back status words.
 __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");

@@ -60,35 +60,35 @@ struct TileGeom {
     __device__ __forceinline__ static int logical(int P) { return REV ? (kTile - 1 - P) : P; }
 
     // Load this thread's k-th vector (logical component order); items past the end of
-    // the array read as `fill`.
+    // the array read as `fill`.  Branch-free for whole vectors (see ldg_stream4_if); only a
+    // tile that crosses the end of the array, or misaligned pointers, take the scalar path.
     __device__ __forceinline__ void load(const float* __restrict__ p, bool vec_ok, int k, float fill,
                                          float (&v)[4]) const {
         const long long g = base + voff(k);
-        if (vec_ok && g + 3 < n) {
-            const float4 q = ldg_stream4(p + g);
-            if (REV) { v[0] = q.w; v[1] = q.z; v[2] = q.y; v[3] = q.x; }
-            else { v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w; }
-        } else {
+        const bool whole = vec_ok && g + 3 < n;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[c] = fill;
+        if (REV) ldg_stream4_if(whole, p + g, v[3], v[2], v[1], v[0]);
+        else ldg_stream4_if(whole, p + g, v[0], v[1], v[2], v[3]);
+        if (!(vec_ok && base + kTile <= n)) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const long long gi = g + (REV ? 3 - c : c);
-                v[c] = (gi < n) ? ldg_stream(p + gi) : fill;
+                ldg_stream_if(!whole && gi < n, p + gi, v[c]);
             }
         }
     }
     __device__ __forceinline__ void store(float* __restrict__ p, bool vec_ok, int k,
                                           const float (&v)[4]) const {
         const long long g = base + voff(k);
-        if (vec_ok && g + 3 < n) {
-            float4 q;
-            if (REV) { q.w = v[0]; q.z = v[1]; q.y = v[2]; q.x = v[3]; }
-            else { q.x = v[0]; q.y = v[1]; q.z = v[2]; q.w = v[3]; }
-            stg_stream4(p + g, q);
-        } else {
+        const bool whole = vec_ok && g + 3 < n;
+        if (REV) stg_stream4_if(whole, p + g, v[3], v[2], v[1], v[0]);
+        else stg_stream4_if(whole, p + g, v[0], v[1], v[2], v[3]);
+        if (!(vec_ok && base + kTile <= n)) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const long long gi = g + (REV ? 3 - c : c);
-                if (gi < n) stg_stream(p + gi, v[c]);
+                stg_stream_if(!whole && gi < n, p + gi, v[c]);
             }
         }
     }
@@ -196,6 +196,83 @@ __device__ __forceinline__ float lookback_carry(unsigned long long* st, int slot
     return acc;
 }
 
+// ------------------------------------------------------------------ head bits
+// One bit per item instead of a search through packed_info: bit i is set iff item i is the
+// first item of a ray, bit n is always set.  Because a canonical layout covers [0, n) without
+// gaps, "item i is the last of its ray" is bit i+1, so the same array serves both scan
+// directions.  ceil((n+1)/32)+2 words (the reverse read funnels two words).
+static inline size_t head_bits_words(long long n) { return (size_t)((n + 1 + 31) / 32 + 2); }
+
+// Head bits (bit c = logical component c) of the vector whose first physical item is g (a
+// multiple of 4); 0 outside [0, n).
+template <bool REV>
+__device__ __forceinline__ uint32_t head_nibble(const uint32_t* __restrict__ bits, long long g, long long n) {
+    if (g >= n || g < 0) return 0u;
+    if (!REV) return (__ldg(bits + (g >> 5)) >> (unsigned)(g & 31)) & 0xfu;
+    const long long h = g + 1;  // tails of [g, g+4) are heads of [g+1, g+5)
+    const uint32_t lo = __ldg(bits + (h >> 5)), hi = __ldg(bits + (h >> 5) + 1);
+    return __brev(__funnelshift_r(lo, hi, (unsigned)(h & 31)) & 0xfu) >> 28;  // logical c = 3 - physical
+}
+// bit c -> byte c (the form vec_flags / flag_at use)
+__device__ __forceinline__ uint32_t nibble_to_flags(uint32_t b) { return (b * 0x00204081u) & 0x01010101u; }
+
+// ------------------------------------------------------------------ warp look-back
+// Decoupled look-back at warp granularity (one status word per 512 items, no block barrier
+// anywhere): all 32 lanes inspect 32 predecessors per round.  Same fold order as
+// lookback_carry: from the nearest final word forward, left to right.
+template <class Op>
+__device__ __noinline__ float warp_lookback_far(unsigned long long* st, long long tile, uint32_t epoch) {
+    const int lane = lane_id();
+    long long hi = tile - 1, k_final;
+    while (true) {  // pass 1: nearest predecessor whose word is final, all nearer ones published
+        const long long idx = hi - lane;
+        uint32_t state = 2u;
+        if (idx >= 0) {
+            const uint32_t meta = (uint32_t)(ld_relaxed_u64(st + idx) >> 32);
+            state = ((meta >> 2) == epoch) ? (meta & 3u) : 0u;
+        }
+        const unsigned fin = __ballot_sync(kFull, state == 2u), none = __ballot_sync(kFull, state == 0u);
+        if (fin) {
+            const int f = __ffs(fin) - 1;
+            if ((none & ((1u << f) - 1u)) == 0u) { k_final = hi - f; break; }
+        } else if (none == 0u) {
+            hi -= 32;
+            continue;
+        }
+        __nanosleep(100);
+    }
+    float acc = Op::identity();
+    for (long long b = k_final; b < tile; b += 32) {  // pass 2: fold forward
+        const long long idx = b + lane;
+        const unsigned long long w = (idx < tile) ? ld_relaxed_u64(st + idx) : 0ull;
+        const float val = __uint_as_float((uint32_t)w);
+        const bool fin = (((uint32_t)(w >> 32)) & 3u) == 2u;
+        const int cnt = (tile - b < 32) ? (int)(tile - b) : 32;
+        for (int j = 0; j < cnt; ++j) {
+            const float vj = __shfl_sync(kFull, val, j);
+            const bool fj = __shfl_sync(kFull, (int)fin, j) != 0;
+            acc = fj ? vj : Op::apply(acc, vj);
+        }
+    }
+    return acc;
+}
+
+// The common case first: the word right before this tile is final (its warp held a ray
+// boundary, or has finished its own look-back) — one broadcast load per poll.
+template <class Op>
+__device__ __forceinline__ float warp_lookback_carry(unsigned long long* st, long long tile, uint32_t epoch) {
+    while (true) {
+        const unsigned long long w = ld_relaxed_u64(st + tile - 1);
+        const uint32_t meta = (uint32_t)(w >> 32);
+        if ((meta >> 2) == epoch && (meta & 3u) != 0u) {
+            if ((meta & 3u) == 2u) return __uint_as_float((uint32_t)w);
+            break;
+        }
+        __nanosleep(100);
+    }
+    return warp_lookback_far<Op>(st, tile, epoch);
+}
+
 // ------------------------------------------------------------------ tile scan
 struct TileSmem {
     uint32_t flags[kTile / 4 + 2];
@@ -215,17 +292,20 @@ struct TileSmem {
 //                   i.e. its full result is Op(E[k], v[k][c]); otherwise it is v[k][c].
 // `slot` selects the look-back word (kernels scanning several quantities call this once
 // per quantity with different slots).  Contains two block barriers.
-template <class Op, bool LOOKBACK = true>
-__device__ __forceinline__ void tile_segscan(float (&v)[kVec][4], const uint32_t (&f)[kVec],
-                                             float (&E)[kVec], unsigned long long* status,
-                                             int slot, uint32_t epoch, TileSmem& sm) {
-    const int lane = lane_id(), w = warp_id();
+// The warp part: segmented inclusive scan of the 512 items one warp holds.  wc = aggregate
+// of the items after the warp's last head (of all of them if warp_open), E[k] = value
+// carried into vector k from the warp's earlier items, open_vec[k] <=> no head between the
+// warp's first item and vector k.
+template <class Op, int VEC>
+__device__ __forceinline__ void warp_segscan(float (&v)[VEC][4], const uint32_t (&f)[VEC],
+                                             float (&E)[VEC], bool (&open_vec)[VEC], float& wc,
+                                             bool& warp_open) {
+    const int lane = lane_id();
     const unsigned lt_mask = (1u << lane) - 1u;
-    float wc = Op::identity();  // carry inside the warp, relative to the warp's first item
-    bool warp_open = true;      // no head so far in this warp
-    bool open_vec[kVec];        // vector k is reachable from the warp's first item
+    wc = Op::identity();  // carry inside the warp, relative to the warp's first item
+    warp_open = true;     // no head so far in this warp
 #pragma unroll
-    for (int k = 0; k < kVec; ++k) {
+    for (int k = 0; k < VEC; ++k) {
         // thread-local segmented inclusive scan over the 4 components
 #pragma unroll
         for (int c = 1; c < 4; ++c)
@@ -233,14 +313,14 @@ __device__ __forceinline__ void tile_segscan(float (&v)[kVec][4], const uint32_t
         const bool any = f[k] != 0u;
         const unsigned hmask = __ballot_sync(kFull, any);
         float t = v[k][3];  // after the last head of this lane (or the whole lane)
+        // a partial from distance d is absorbed iff lanes (lane-d, lane] hold no head, i.e.
+        // d <= lane - (nearest head lane at or before this one); without one, d <= lane
+        const unsigned le = hmask & (lt_mask | (1u << lane));
+        const int lim = le ? (lane - 31 + __clz(le)) : lane;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const float y = __shfl_up_sync(kFull, t, d);
-            // absorb lane-d's partial iff lanes (lane-d, lane] hold no head
-            if (lane >= d) {
-                const unsigned span = ((1u << d) - 1u) << (lane - d + 1);
-                if ((hmask & span) == 0u) t = Op::apply(y, t);
-            }
+            if (d <= lim) t = Op::apply(y, t);
         }
         float e = __shfl_up_sync(kFull, t, 1);
         const bool no_head_before = (hmask & lt_mask) == 0u;
@@ -252,6 +332,17 @@ __device__ __forceinline__ void tile_segscan(float (&v)[kVec][4], const uint32_t
         wc = (hmask == 0u) ? Op::apply(wc, t31) : t31;
         warp_open = warp_open && (hmask == 0u);
     }
+}
+
+template <class Op, bool LOOKBACK = true>
+__device__ __forceinline__ void tile_segscan(float (&v)[kVec][4], const uint32_t (&f)[kVec],
+                                             float (&E)[kVec], unsigned long long* status,
+                                             int slot, uint32_t epoch, TileSmem& sm) {
+    const int lane = lane_id(), w = warp_id();
+    float wc;
+    bool warp_open;
+    bool open_vec[kVec];
+    warp_segscan<Op, kVec>(v, f, E, open_vec, wc, warp_open);
     if (lane == 0) { sm.wagg[slot][w] = wc; sm.whead[w] = warp_open ? 0 : 1; }
     __syncthreads();
     // carry into this warp from the earlier warps of the tile (8 entries, serial fold)

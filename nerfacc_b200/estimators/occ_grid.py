@@ -148,7 +148,7 @@ class OccGridEstimator(AbstractEstimator):
                           render_step_size, cone_angle, -1)
         packed_info, _, _, n_samples, _ = marcher.count(False, False, want_runs=True)
         ray_indices, t_starts, t_ends = marcher.fill_sampling(packed_info, n_samples)
-        mark_canonical(packed_info)
+        mark_canonical(packed_info, total=n_samples)
         remember_packed_info(ray_indices, packed_info, marcher.n_rays)
 
         # skip invisible space

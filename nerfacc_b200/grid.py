@@ -131,8 +131,8 @@ def traverse_grids(
         term = torch.empty((n_rays,), dtype=torch.float32, device=dev)
         iv, sm = m.fill_full(True, sample_info, interval_info, n_alloc, 2 * n_alloc,
                              sample_starts, interval_starts, term)
-    mark_canonical(sample_info)
-    mark_canonical(interval_info)
+    mark_canonical(sample_info, total=None if over_allocate else n_samples)
+    mark_canonical(interval_info, total=None if over_allocate else n_edges)
     if not over_allocate:
         remember_packed_info(sm["ray_indices"], sample_info, n_rays)
     intervals = RayIntervals(vals=iv["vals"], packed_info=interval_info, ray_indices=iv["ray_indices"],

@@ -50,6 +50,6 @@ def pack_info(ray_indices: Tensor, n_rays: Optional[int] = None) -> Tensor:
         _C.check(rc, "pack_info")
     if out_dtype != torch.long:
         return packed_info.to(out_dtype)
-    mark_canonical(packed_info)
+    mark_canonical(packed_info, total=ri.numel())
     remember_packed_info(ray_indices, packed_info, n_rays)
     return packed_info

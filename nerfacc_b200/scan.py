@@ -11,7 +11,7 @@ import torch
 from torch import Tensor
 
 from . import _C
-from ._packing import as_packed_info
+from ._packing import as_packed_info, head_bits
 
 _OP_SUM, _OP_PROD = 0, 1
 
@@ -25,8 +25,15 @@ def _scan(inputs: Tensor, packed_info: Tensor, canonical: bool, op: int, exclusi
     n = inputs.numel()
     if n == 0 or packed_info.shape[0] == 0:
         return outputs
+    bits = head_bits(packed_info, n) if (canonical and not normalize) else None
     with torch.cuda.device(dev):
         ws, ws_bytes, epoch = _C.workspace(dev, n)
+        if bits is not None:
+            rc = _C.lib().nfb_scan_bits_f32(
+                inputs.data_ptr(), outputs.data_ptr(), bits.data_ptr(), n, op, int(exclusive),
+                int(reverse), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            _C.check(rc, "scan")
+            return outputs
         rc = _C.lib().nfb_scan_f32(
             inputs.data_ptr(), outputs.data_ptr(), packed_info.data_ptr(), packed_info.shape[0],
             n, op, int(exclusive), int(reverse), int(normalize), int(canonical),
@@ -42,8 +49,15 @@ def _prod_bwd(grad_outputs: Tensor, inputs: Tensor, outputs: Tensor, packed_info
     n = inputs.numel()
     if n == 0 or packed_info.shape[0] == 0:
         return grad_inputs
+    bits = head_bits(packed_info, n) if canonical else None
     with torch.cuda.device(dev):
         ws, ws_bytes, epoch = _C.workspace(dev, n)
+        if bits is not None:
+            rc = _C.lib().nfb_prod_scan_bwd_bits_f32(
+                grad_outputs.data_ptr(), inputs.data_ptr(), outputs.data_ptr(), grad_inputs.data_ptr(),
+                bits.data_ptr(), n, int(exclusive), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            _C.check(rc, "prod_scan_bwd")
+            return grad_inputs
         rc = _C.lib().nfb_prod_scan_bwd_f32(
             grad_outputs.data_ptr(), inputs.data_ptr(), outputs.data_ptr(), grad_inputs.data_ptr(),
             packed_info.data_ptr(), packed_info.shape[0], n, int(exclusive), int(canonical),
