@@ -108,7 +108,7 @@ __device__ __forceinline__ int first_head_128(uint32_t nib) {
 }
 
 template <class Op, bool REV, bool EXCL, int MODE, int VEC>
-__global__ void __launch_bounds__(kThreads, VEC == 4 ? 4 : 2)
+__global__ void __launch_bounds__(kThreads, VEC == 4 ? 4 : 3)
 scan_bits_kernel(const float* __restrict__ in, const float* __restrict__ aux_y,
                  const float* __restrict__ aux_x, float* __restrict__ out,
                  const uint32_t* __restrict__ bits, long long n, long long n_wt,

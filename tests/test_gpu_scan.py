@@ -21,7 +21,27 @@ CASES = [
     dict(n_rays=4, counts=[4096, 4096, 1, 4095]),           # rays ending exactly on tile edges
     dict(n_rays=3, counts=[0, 30000, 3]),                   # one ray spanning 8 tiles (look-back chain)
     dict(n_rays=20000, counts=None),                        # cfg3-shaped ragged mix
+    dict(n_rays=6, counts=[511, 1, 128, 384, 127, 1]),      # boundaries on / next to warp-tile and overhang edges
+    dict(n_rays=9, counts=[500, 140, 0, 129, 383, 1, 1, 640, 7]),  # first boundary of a tile at 128: look-back, at 127: overhang
+    dict(n_rays=2, counts=[3, 2]),                          # shorter than one vector
+    dict(n_rays=40, counts=[700] * 40),                     # every tile continues a ray, some hold no boundary
 ]
+
+# which kernel: "rows" = one warp per ray (any packed_info), "flat" = 4096-item tiles + packed_info
+# search, "bits" = warp tiles from head bits (dense canonical layouts; what the public API takes
+# for packed_info made by pack_info / traverse_grids / sampling)
+LAYOUTS = ["rows", "flat", "bits"]
+
+
+def _mark(pit, layout, n):
+    from nerfacc_b200._packing import head_bits, mark_canonical
+
+    if layout == "flat":
+        mark_canonical(pit)
+    elif layout == "bits":
+        mark_canonical(pit, total=n)
+        assert n == 0 or head_bits(pit, n) is not None
+    return layout != "rows"
 
 
 def _mk(case, seed=0, positive=False):
@@ -38,16 +58,14 @@ def _mk(case, seed=0, positive=False):
 @pytest.mark.parametrize("case", CASES)
 @pytest.mark.parametrize("exclusive", [False, True])
 @pytest.mark.parametrize("reverse", [False, True])
-@pytest.mark.parametrize("canonical", [True, False])
-def test_sum_scan(device, case, exclusive, reverse, canonical):
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_sum_scan(device, case, exclusive, reverse, layout):
     from nerfacc_b200 import scan as S
-    from nerfacc_b200._packing import mark_canonical
 
     x, pi = _mk(case)
     xt = torch.from_numpy(x).to(device)
     pit = torch.from_numpy(pi).to(device)
-    if canonical:
-        mark_canonical(pit)
+    canonical = _mark(pit, layout, x.shape[0])
     out = S._scan(xt, pit, canonical, 0, exclusive, reverse).cpu().numpy()
     ref = oracle.scan(x, pi, "sum", exclusive, reverse)
     ref64 = oracle.scan_f64(x, pi, "sum", exclusive, reverse)
@@ -56,10 +74,10 @@ def test_sum_scan(device, case, exclusive, reverse, canonical):
     assert_close(out, ref, 1e-5, 4e-7 * scale, "ours vs oracle fp32")
 
 
-@pytest.mark.parametrize("case", CASES[:5])
+@pytest.mark.parametrize("case", CASES[:5] + CASES[6:9])
 @pytest.mark.parametrize("exclusive", [False, True])
-@pytest.mark.parametrize("canonical", [True, False])
-def test_prod_scan_and_backward(device, case, exclusive, canonical):
+@pytest.mark.parametrize("layout", LAYOUTS)
+def test_prod_scan_and_backward(device, case, exclusive, layout):
     from nerfacc_b200 import scan as S
 
     x, pi = _mk(case, positive=True)
@@ -67,6 +85,7 @@ def test_prod_scan_and_backward(device, case, exclusive, canonical):
     g = np.random.default_rng(5).standard_normal(x.shape[0]).astype(np.float32)
     xt, gt = torch.from_numpy(x).to(device), torch.from_numpy(g).to(device)
     pit = torch.from_numpy(pi).to(device)
+    canonical = _mark(pit, layout, x.shape[0])
     out = S._scan(xt, pit, canonical, 1, exclusive, False)
     ref = oracle.scan(x, pi, "prod", exclusive)
     assert_close(out.cpu().numpy(), ref, 2e-5, 1e-30, "prod fwd")
@@ -113,3 +132,32 @@ def test_cpu_tensor_raises():
 
     with pytest.raises(RuntimeError):
         nf.inclusive_sum(torch.ones(4), torch.tensor([[0, 4]]))
+
+
+@pytest.mark.parametrize("reverse", [False, True])
+@pytest.mark.parametrize("offset", [0, 1, 3])
+def test_bits_kernels_equal_flat_kernels(device, reverse, offset):
+    """The two canonical kernels give the same bits on the same input (also from misaligned
+    views: the scalar edge path), and the bits path is the one the public API takes after
+    pack_info."""
+    import nerfacc_b200 as nf
+    from nerfacc_b200 import scan as S
+    from nerfacc_b200._packing import head_bits, mark_canonical
+
+    counts = ragged_counts(30000, mean=35.0, seed=4, long_rays=[(5, 3000), (6, 130), (7, 0)])
+    pi = packed_info_from_counts(counts)
+    n = int(counts.sum())
+    rng = np.random.default_rng(2)
+    buf = torch.from_numpy(rng.standard_normal(n + 8).astype(np.float32)).to(device)
+    x = buf[offset:offset + n]
+    a, b = torch.from_numpy(pi).to(device), torch.from_numpy(pi).to(device)
+    mark_canonical(a)
+    mark_canonical(b, total=n)
+    for op in (0, 1):
+        xin = x if op == 0 else (0.75 + 0.25 * x.abs().clamp(max=1.0))
+        for excl in (False, True):
+            o_flat = S._scan(xin, a, True, op, excl, reverse)
+            o_bits = S._scan(xin, b, True, op, excl, reverse)
+            assert torch.equal(o_flat, o_bits), (op, excl)
+    ri = torch.from_numpy(np.repeat(np.arange(len(counts)), counts)).to(device)
+    assert head_bits(nf.pack_info(ri, len(counts)), n) is not None
