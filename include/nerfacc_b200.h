@@ -134,6 +134,23 @@ NFB_API int nfb_render_weight_bwd(int from_density, const float* g_weights, cons
                                   int64_t uniform_len, int64_t n, float* g_in, void* workspace,
                                   size_t workspace_bytes, uint32_t epoch, nfb_stream_t stream);
 
+/* The two calls above for a dense packed layout given as head bits (nfb_head_bits) instead of
+ * packed_info: same per-sample math, warp tiles instead of 4096-sample block tiles. */
+NFB_API int nfb_render_weight_bits_fwd(int from_density, const float* alphas, const float* t_starts,
+                                       const float* t_ends, const float* sigmas,
+                                       const float* prefix_trans, const uint32_t* head_bits,
+                                       int64_t n, float* weights, float* trans, float* alphas_out,
+                                       uint8_t* vis, float early_stop_eps, float alpha_thre,
+                                       void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                       nfb_stream_t stream);
+NFB_API int nfb_render_weight_bits_bwd(int from_density, const float* g_weights, const float* g_trans,
+                                       const float* g_alphas, const float* alphas,
+                                       const float* t_starts, const float* t_ends,
+                                       const float* sigmas, const float* trans,
+                                       const uint32_t* head_bits, int64_t n, float* g_in,
+                                       void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                       nfb_stream_t stream);
+
 /* ------------------------------------------------------------------------------------
  * accumulate_along_rays: out[r, :] (+)= sum_{i in ray r} weights[i] * values[i, :].
  * Replaces the temporary + index_add_ atomics of nerfacc/volrend.py:532-547 (and the

@@ -70,6 +70,10 @@ _PROTOS = {
                               c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_f32, c_ptr, c_size, c_u32, c_ptr],
     "nfb_render_weight_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                               c_i64, c_i64, c_i64, c_ptr, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_render_weight_bits_fwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
+                                   c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_f32, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_render_weight_bits_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                   c_i64, c_ptr, c_ptr, c_size, c_u32, c_ptr],
     "nfb_accumulate_fwd": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int,
                            c_ptr, c_size, c_u32, c_ptr],
     "nfb_accumulate_bwd": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],

@@ -14,6 +14,7 @@ import torch
 from torch import Tensor
 
 from . import _C
+from ._packing import head_bits
 
 
 def _p(t: Optional[Tensor]):
@@ -34,13 +35,20 @@ def weight_fwd(from_density: bool, alphas: Optional[Tensor], t_starts: Optional[
     if n > 0:
         eps, thre = (float(vis[0]), float(vis[1])) if vis is not None else (0.0, 0.0)
         n_rays = packed_info.shape[0] if packed_info is not None else n // max(uniform_len, 1)
+        bits = head_bits(packed_info, n) if packed_info is not None else None
         with torch.cuda.device(dev):
             ws, ws_bytes, epoch = _C.workspace(dev, n)
-            rc = _C.lib().nfb_render_weight_fwd(
-                int(from_density), _p(alphas), _p(t_starts), _p(t_ends), _p(sigmas),
-                _p(prefix_trans), _p(packed_info), n_rays, int(uniform_len), n, _p(weights),
-                _p(trans), _p(alphas_out), _p(mask), eps, thre, ws.data_ptr(), ws_bytes, epoch,
-                _C.stream_ptr(dev))
+            if bits is not None:  # dense layout: warp tiles
+                rc = _C.lib().nfb_render_weight_bits_fwd(
+                    int(from_density), _p(alphas), _p(t_starts), _p(t_ends), _p(sigmas),
+                    _p(prefix_trans), _p(bits), n, _p(weights), _p(trans), _p(alphas_out), _p(mask),
+                    eps, thre, ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            else:
+                rc = _C.lib().nfb_render_weight_fwd(
+                    int(from_density), _p(alphas), _p(t_starts), _p(t_ends), _p(sigmas),
+                    _p(prefix_trans), _p(packed_info), n_rays, int(uniform_len), n, _p(weights),
+                    _p(trans), _p(alphas_out), _p(mask), eps, thre, ws.data_ptr(), ws_bytes, epoch,
+                    _C.stream_ptr(dev))
         _C.check(rc, "render_weight_fwd")
     return weights, trans, alphas_out, mask
 
@@ -55,12 +63,19 @@ def weight_bwd(from_density: bool, g_weights: Optional[Tensor], g_trans: Optiona
     g_in = torch.empty_like(like)
     if n > 0:
         n_rays = packed_info.shape[0] if packed_info is not None else n // max(uniform_len, 1)
+        bits = head_bits(packed_info, n) if packed_info is not None else None
         with torch.cuda.device(dev):
             ws, ws_bytes, epoch = _C.workspace(dev, n)
-            rc = _C.lib().nfb_render_weight_bwd(
-                int(from_density), _p(g_weights), _p(g_trans), _p(g_alphas), _p(alphas),
-                _p(t_starts), _p(t_ends), _p(sigmas), _p(trans), _p(packed_info), n_rays,
-                int(uniform_len), n, _p(g_in), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            if bits is not None:
+                rc = _C.lib().nfb_render_weight_bits_bwd(
+                    int(from_density), _p(g_weights), _p(g_trans), _p(g_alphas), _p(alphas),
+                    _p(t_starts), _p(t_ends), _p(sigmas), _p(trans), _p(bits), n, _p(g_in),
+                    ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            else:
+                rc = _C.lib().nfb_render_weight_bwd(
+                    int(from_density), _p(g_weights), _p(g_trans), _p(g_alphas), _p(alphas),
+                    _p(t_starts), _p(t_ends), _p(sigmas), _p(trans), _p(packed_info), n_rays,
+                    int(uniform_len), n, _p(g_in), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
         _C.check(rc, "render_weight_bwd")
     return g_in
 

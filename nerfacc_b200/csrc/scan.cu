@@ -7,7 +7,7 @@
 //     decoupled look-back (seg_tile.cuh); bandwidth-bound for any ray-length mix.
 //   * scan_rows_kernel  — any non-overlapping packed_info (gaps, arbitrary order) and the
 //     `normalize` option: one warp per ray, shuffle scan over 32-element strips.
-#include "seg_tile.cuh"
+#include "warp_tile.cuh"
 
 namespace nfb {
 
@@ -58,159 +58,43 @@ scan_flat_kernel(const float* __restrict__ in, const float* __restrict__ aux_y,
 }
 
 // ---------------------------------------------------------------- scans from head bits
-// Warp tiles: every warp owns VEC*128 consecutive items and is on its own — no shared memory,
-// no block barrier, no packed_info search (ray boundaries come as 1 bit per item, nfb_head_bits).
-//
-// A tile that does not start on a ray boundary needs the running value of the ray it continues.
-// Waiting for the previous warp to publish it (look-back) puts one L2 round trip under load on
-// every warp's critical path and halves the bytes in flight.  Instead the previous warp finishes
-// that ray itself: every warp also loads the 128 items after its tile (the "overhang") and, if
-// the next tile's first boundary lies among them, writes the items before that boundary — both
-// warps read the same bits, so they agree on who writes what without talking.  Only tiles whose
-// first boundary is further than 128 items away (rays of hundreds of samples) look back.
-template <bool REV>
-__device__ __forceinline__ void load_vec(const float* __restrict__ p, long long g, long long n, bool vec_ok,
-                                         bool slow, float fill, float (&v)[4]) {
-    const bool whole = vec_ok && g >= 0 && g + 3 < n;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) v[c] = fill;
-    if (REV) ldg_stream4_if(whole, p + g, v[3], v[2], v[1], v[0]);
-    else ldg_stream4_if(whole, p + g, v[0], v[1], v[2], v[3]);
-    if (slow) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const long long gi = g + (REV ? 3 - c : c);
-            ldg_stream_if(!whole && gi >= 0 && gi < n, p + gi, v[c]);
-        }
-    }
-}
-// mask: bit c set <=> logical component c is written
-template <bool REV>
-__device__ __forceinline__ void store_vec(float* __restrict__ p, long long g, long long n, bool vec_ok,
-                                          bool slow, const float (&v)[4], uint32_t mask) {
-    const bool whole = vec_ok && g >= 0 && g + 3 < n && mask == 0xfu;
-    if (REV) stg_stream4_if(whole, p + g, v[3], v[2], v[1], v[0]);
-    else stg_stream4_if(whole, p + g, v[0], v[1], v[2], v[3]);
-    if (slow || (mask != 0xfu && mask != 0u)) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const long long gi = g + (REV ? 3 - c : c);
-            stg_stream_if(!whole && ((mask >> c) & 1u) && gi >= 0 && gi < n, p + gi, v[c]);
-        }
-    }
-}
-// position of the first head among a warp's 128 items (4 per lane, nibble flags); 128 = none
-__device__ __forceinline__ int first_head_128(uint32_t nib) {
-    const unsigned hm = __ballot_sync(kFull, nib != 0u);
-    if (hm == 0u) return 128;
-    const int l = __ffs(hm) - 1;
-    return 4 * l + __ffs(__shfl_sync(kFull, nib, l)) - 1;
-}
-
-template <class Op, bool REV, bool EXCL, int MODE, int VEC>
-__global__ void __launch_bounds__(kThreads, VEC == 4 ? 4 : 3)
+// Same results as scan_flat_kernel, on warp tiles (warp_tile.cuh).
+template <class Op, bool REV, bool EXCL, int MODE>
+__global__ void __launch_bounds__(kThreads, 4)
 scan_bits_kernel(const float* __restrict__ in, const float* __restrict__ aux_y,
                  const float* __restrict__ aux_x, float* __restrict__ out,
                  const uint32_t* __restrict__ bits, long long n, long long n_wt,
                  unsigned long long* status, uint32_t epoch, bool vec_ok) {
-    constexpr int W = VEC * 128;
-    const int lane = lane_id();
-    const long long t = (long long)blockIdx.x * kWarps + warp_id();  // logical order == launch order
-    if (t >= n_wt) return;
-    const long long pt = REV ? n_wt - 1 - t : t;
-    const long long base = pt * W;
-    const bool slow = !vec_ok || base + W + 128 > n;
-    const bool has_next = REV ? (pt > 0) : (base + W < n);
-    const long long g0 = REV ? base + (long long)(VEC - 1) * 128 + (31 - lane) * 4 : base + lane * 4;
-    const long long gstep = REV ? -128 : 128;  // physical start of logical vector k: g0 + k * gstep
-    const long long go = has_next ? (REV ? base - 128 + (31 - lane) * 4 : base + W + lane * 4) : -8;
-
-    float v[VEC][4], u[4];
-    uint32_t f[VEC];
+    WarpTile<REV> wt;
+    float v[kWtNV][4];
+    if (!wt.init(bits, n, n_wt, vec_ok)) return;
 #pragma unroll
-    for (int k = 0; k < VEC; ++k) load_vec<REV>(in, g0 + k * gstep, n, vec_ok, slow, Op::identity(), v[k]);
-    load_vec<REV>(in, go, n, vec_ok, slow, Op::identity(), u);
-    uint32_t nib0 = 0u;
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-        const uint32_t nb = head_nibble<REV>(bits, g0 + k * gstep, n);
-        if (k == 0) nib0 = nb;
-        f[k] = nibble_to_flags(nb);
-    }
-    const uint32_t nibo = head_nibble<REV>(bits, go, n);
+    for (int k = 0; k < kWtNV; ++k) wt.load(in, k, Op::identity(), v[k]);
     if (MODE == kProdBwd) {
 #pragma unroll
-        for (int k = 0; k < VEC; ++k) {
+        for (int k = 0; k < kWtNV; ++k) {
             float y[4];
-            load_vec<REV>(aux_y, g0 + k * gstep, n, vec_ok, slow, 0.0f, y);
+            wt.load(aux_y, k, 0.0f, y);
 #pragma unroll
             for (int c = 0; c < 4; ++c) v[k][c] = __fmul_rn(v[k][c], y[c]);
         }
-        float y[4];
-        load_vec<REV>(aux_y, go, n, vec_ok, slow, 0.0f, y);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) u[c] = __fmul_rn(u[c], y[c]);
     }
-    float E[VEC], wc;
-    bool open_vec[VEC], warp_open;
-    warp_segscan<Op, VEC>(v, f, E, open_vec, wc, warp_open);
-
-    const int p_own = first_head_128(nib0);
-    const bool by_pred = t > 0 && p_own > 0 && p_own < 128;  // my first items are the previous warp's overhang
-    const bool need_x = t > 0 && p_own == 128;
-    const bool final_now = (t == 0) || !warp_open;
-    if (lane == 0) st_relaxed_u64(status + t, pack_status(wc, epoch, final_now ? 2u : 1u));
-    float X = Op::identity();
-    if (need_x) {
-        X = warp_lookback_carry<Op>(status, t, epoch);
-        if (!final_now && lane == 0) st_relaxed_u64(status + t, pack_status(Op::apply(X, wc), epoch, 2u));
-    }
+    float E[kWtNV];
+    wt.template scan<Op>(v, E, status, 1, 0, epoch);
 #pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-        const float Ek = open_vec[k] ? Op::apply(X, E[k]) : E[k];
+    for (int k = 0; k < kWtNV; ++k) {
+        if (k == kWtVec && !wt.over) break;
         float o[4];
-        if (EXCL) finish_exclusive<Op>(v[k], f[k], Ek, o);
-        else finish_inclusive<Op>(v[k], f[k], Ek, o);
+        if (EXCL) finish_exclusive<Op>(v[k], wt.f[k], E[k], o);
+        else finish_inclusive<Op>(v[k], wt.f[k], E[k], o);
         if (MODE == kProdBwd) {
             float x[4];
-            load_vec<REV>(aux_x, g0 + k * gstep, n, vec_ok, slow, 1.0f, x);
+            wt.load(aux_x, k, 1.0f, x);
 #pragma unroll
             for (int c = 0; c < 4; ++c) o[c] = __fdiv_rn(o[c], fmaxf(x[c], 1e-10f));
         }
-        uint32_t mask = 0xfu;
-        if (k == 0 && by_pred) {
-            const int d = p_own - 4 * lane;  // components below d belong to the previous warp
-            mask = d <= 0 ? 0xfu : (d >= 4 ? 0u : (0xfu << d) & 0xfu);
-        }
-        store_vec<REV>(out, g0 + k * gstep, n, vec_ok, slow, o, mask);
+        wt.store(out, k, o);
     }
-    if (!has_next) return;
-    const int p_nx = first_head_128(nibo);
-    if (p_nx == 0 || p_nx == 128) return;
-    // finish the ray that runs over the end of my tile: items [0, p_nx) of the next tile
-    const float carry = warp_open ? Op::apply(X, wc) : wc;  // inclusive value at my last item
-#pragma unroll
-    for (int c = 1; c < 4; ++c) u[c] = Op::apply(u[c - 1], u[c]);
-    float tt = u[3];
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const float y = __shfl_up_sync(kFull, tt, d);
-        if (lane >= d) tt = Op::apply(y, tt);
-    }
-    float e = __shfl_up_sync(kFull, tt, 1);
-    e = (lane == 0) ? carry : Op::apply(carry, e);
-    float o[4];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) o[c] = EXCL ? (c == 0 ? e : Op::apply(e, u[c - 1])) : Op::apply(e, u[c]);
-    if (MODE == kProdBwd) {
-        float x[4];
-        load_vec<REV>(aux_x, go, n, vec_ok, slow, 1.0f, x);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) o[c] = __fdiv_rn(o[c], fmaxf(x[c], 1e-10f));
-    }
-    const int d = p_nx - 4 * lane;  // components below d are mine
-    const uint32_t mask = d <= 0 ? 0u : (d >= 4 ? 0xfu : ~(0xfu << d) & 0xfu);
-    store_vec<REV>(out, go, n, vec_ok, slow, o, mask);
 }
 
 // bit start[r] for every non-empty ray, and bit n
@@ -346,13 +230,12 @@ static int launch_scan_bits(const float* in, const float* aux_y, const float* au
     NFB_CHECK_ARG(in && out && bits, "null pointer");
     int rc = prepare_workspace(ws, ws_bytes, n, epoch, s);
     if (rc != NFB_OK) return rc;
-    constexpr int kBitsVec = 4;
-    const long long n_wt = ceil_div<long long>(n, kBitsVec * 128);
+    const long long n_wt = num_warp_tiles(n);
     const long long nt = ceil_div<long long>(n_wt, kWarps);
     const bool vec_ok = aligned16(in) && aligned16(out) && (MODE == kPlain || (aligned16(aux_y) && aligned16(aux_x)));
     auto* st = static_cast<unsigned long long*>(ws);
 #define NFB_LAUNCH_BITS(OP, REV, EXCL) \
-    scan_bits_kernel<OP, REV, EXCL, MODE, kBitsVec><<<(unsigned)nt, kThreads, 0, s>>>(in, aux_y, aux_x, out, bits, n, n_wt, st, epoch, vec_ok)
+    scan_bits_kernel<OP, REV, EXCL, MODE><<<(unsigned)nt, kThreads, 0, s>>>(in, aux_y, aux_x, out, bits, n, n_wt, st, epoch, vec_ok)
     if (op == NFB_OP_SUM) {
         if (reverse) { if (exclusive) NFB_LAUNCH_BITS(SumOp, true, true); else NFB_LAUNCH_BITS(SumOp, true, false); }
         else { if (exclusive) NFB_LAUNCH_BITS(SumOp, false, true); else NFB_LAUNCH_BITS(SumOp, false, false); }

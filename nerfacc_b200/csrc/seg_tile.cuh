@@ -221,14 +221,14 @@ __device__ __forceinline__ uint32_t nibble_to_flags(uint32_t b) { return (b * 0x
 // anywhere): all 32 lanes inspect 32 predecessors per round.  Same fold order as
 // lookback_carry: from the nearest final word forward, left to right.
 template <class Op>
-__device__ __noinline__ float warp_lookback_far(unsigned long long* st, long long tile, uint32_t epoch) {
+__device__ __noinline__ float warp_lookback_far(unsigned long long* st, int stride, long long tile, uint32_t epoch) {
     const int lane = lane_id();
     long long hi = tile - 1, k_final;
     while (true) {  // pass 1: nearest predecessor whose word is final, all nearer ones published
         const long long idx = hi - lane;
         uint32_t state = 2u;
         if (idx >= 0) {
-            const uint32_t meta = (uint32_t)(ld_relaxed_u64(st + idx) >> 32);
+            const uint32_t meta = (uint32_t)(ld_relaxed_u64(st + idx * stride) >> 32);
             state = ((meta >> 2) == epoch) ? (meta & 3u) : 0u;
         }
         const unsigned fin = __ballot_sync(kFull, state == 2u), none = __ballot_sync(kFull, state == 0u);
@@ -244,7 +244,7 @@ __device__ __noinline__ float warp_lookback_far(unsigned long long* st, long lon
     float acc = Op::identity();
     for (long long b = k_final; b < tile; b += 32) {  // pass 2: fold forward
         const long long idx = b + lane;
-        const unsigned long long w = (idx < tile) ? ld_relaxed_u64(st + idx) : 0ull;
+        const unsigned long long w = (idx < tile) ? ld_relaxed_u64(st + idx * stride) : 0ull;
         const float val = __uint_as_float((uint32_t)w);
         const bool fin = (((uint32_t)(w >> 32)) & 3u) == 2u;
         const int cnt = (tile - b < 32) ? (int)(tile - b) : 32;
@@ -260,9 +260,10 @@ __device__ __noinline__ float warp_lookback_far(unsigned long long* st, long lon
 // The common case first: the word right before this tile is final (its warp held a ray
 // boundary, or has finished its own look-back) — one broadcast load per poll.
 template <class Op>
-__device__ __forceinline__ float warp_lookback_carry(unsigned long long* st, long long tile, uint32_t epoch) {
+__device__ __forceinline__ float warp_lookback_carry(unsigned long long* st, int stride, long long tile,
+                                                     uint32_t epoch) {
     while (true) {
-        const unsigned long long w = ld_relaxed_u64(st + tile - 1);
+        const unsigned long long w = ld_relaxed_u64(st + (tile - 1) * stride);
         const uint32_t meta = (uint32_t)(w >> 32);
         if ((meta >> 2) == epoch && (meta & 3u) != 0u) {
             if ((meta & 3u) == 2u) return __uint_as_float((uint32_t)w);
@@ -270,7 +271,7 @@ __device__ __forceinline__ float warp_lookback_carry(unsigned long long* st, lon
         }
         __nanosleep(100);
     }
-    return warp_lookback_far<Op>(st, tile, epoch);
+    return warp_lookback_far<Op>(st, stride, tile, epoch);
 }
 
 // ------------------------------------------------------------------ tile scan
@@ -296,9 +297,9 @@ struct TileSmem {
 // of the items after the warp's last head (of all of them if warp_open), E[k] = value
 // carried into vector k from the warp's earlier items, open_vec[k] <=> no head between the
 // warp's first item and vector k.
-template <class Op, int VEC>
-__device__ __forceinline__ void warp_segscan(float (&v)[VEC][4], const uint32_t (&f)[VEC],
-                                             float (&E)[VEC], bool (&open_vec)[VEC], float& wc,
+template <class Op, int VEC, int NV = VEC>
+__device__ __forceinline__ void warp_segscan(float (&v)[NV][4], const uint32_t (&f)[NV],
+                                             float (&E)[NV], bool (&open_vec)[NV], float& wc,
                                              bool& warp_open) {
     const int lane = lane_id();
     const unsigned lt_mask = (1u << lane) - 1u;

@@ -13,7 +13,7 @@
 // The backward formulas are exactly what torch autograd derives from the reference's
 // composite, including its clamp_min(1e-10) division in the product-scan backward
 // (csrc/scan.cu:299-300), so gradients match the reference, not the "ideal" derivative.
-#include "seg_tile.cuh"
+#include "warp_tile.cuh"
 
 namespace nfb {
 
@@ -29,6 +29,7 @@ struct WeightFwdArgs {
     uint8_t* vis;
     float early_stop_eps, alpha_thre;
     SegSpec seg;
+    const uint32_t* bits;  // head bits (warp-tile kernels) instead of seg
     long long n, n_tiles;
     unsigned long long* status;
     uint32_t epoch;
@@ -121,6 +122,7 @@ struct WeightBwdArgs {
     const float* trans;      // saved forward output (prefix already applied)
     float* g_in;             // grad wrt alphas (alpha mode) or sigmas (density mode)
     SegSpec seg;
+    const uint32_t* bits;
     long long n, n_tiles;
     unsigned long long* status;
     uint32_t epoch;
@@ -185,6 +187,140 @@ __global__ void __launch_bounds__(kThreads) weight_bwd_kernel(const WeightBwdArg
             else o[c] = __fsub_rn(dir[k][c], __fdiv_rn(R[c], sc[k][c]));
         }
         g.store(p.g_in, p.vec_ok, k, o);
+    }
+}
+
+// ---------------------------------------------------------------- the same on warp tiles
+// Dense packed layouts with head bits (warp_tile.cuh): identical math per sample, no block
+// barrier and no look-back wait on the critical path.  n_tiles counts warp tiles here.
+template <bool DENSITY>
+__global__ void __launch_bounds__(kThreads, 3) weight_fwd_bits_kernel(const WeightFwdArgs p) {
+    WarpTile<false> wt;
+    if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
+    float v[kWtNV][4];   // scanned quantity: (1-a) or sd
+    float al[kWtNV][4];  // alphas
+#pragma unroll
+    for (int k = 0; k < kWtNV; ++k) {
+        if (DENSITY) {
+            float ts[4], te[4], s[4];
+            wt.load(p.t_starts, k, 0.0f, ts);
+            wt.load(p.t_ends, k, 0.0f, te);
+            wt.load(p.sigmas, k, 0.0f, s);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                v[k][c] = __fmul_rn(s[c], __fsub_rn(te[c], ts[c]));
+                al[k][c] = __fsub_rn(1.0f, expf(-v[k][c]));
+            }
+        } else {
+            wt.load(p.alphas, k, 0.0f, al[k]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) v[k][c] = __fsub_rn(1.0f, al[k][c]);
+        }
+    }
+    float E[kWtNV];
+    if (DENSITY) wt.template scan<SumOp>(v, E, p.status, 1, 0, p.epoch);
+    else wt.template scan<ProdOp>(v, E, p.status, 1, 0, p.epoch);
+#pragma unroll
+    for (int k = 0; k < kWtNV; ++k) {
+        if (k == kWtVec && !wt.over) break;
+        float T[4];
+        if (DENSITY) {
+            finish_exclusive<SumOp>(v[k], wt.f[k], E[k], T);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) T[c] = expf(-T[c]);
+        } else {
+            finish_exclusive<ProdOp>(v[k], wt.f[k], E[k], T);
+        }
+        if (p.prefix) {
+            float pf[4];
+            wt.load(p.prefix, k, 1.0f, pf);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) T[c] = __fmul_rn(T[c], pf[c]);
+        }
+        if (p.trans) wt.store(p.trans, k, T);
+        if (p.alphas_out) wt.store(p.alphas_out, k, al[k]);
+        if (p.weights) {
+            float w[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) w[c] = __fmul_rn(T[c], al[k][c]);
+            wt.store(p.weights, k, w);
+        }
+        if (p.vis) {  // volrend.py:414-417, 476-479: T >= eps [& a >= thre if thre > 0]
+            const long long gi = wt.g(k);
+            const uint32_t m = wt.mask(k);
+            uint8_t q[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                bool ok = T[c] >= p.early_stop_eps;
+                if (p.alpha_thre > 0.0f) ok = ok && (al[k][c] >= p.alpha_thre);
+                q[c] = ok ? 1 : 0;
+            }
+            if (p.vec_ok && m == 0xfu && gi >= 0 && gi + 3 < p.n) {
+                *reinterpret_cast<uchar4*>(p.vis + gi) = make_uchar4(q[0], q[1], q[2], q[3]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (((m >> c) & 1u) && gi + c >= 0 && gi + c < p.n) p.vis[gi + c] = q[c];
+            }
+        }
+    }
+}
+
+template <bool DENSITY>
+__global__ void __launch_bounds__(kThreads, 2) weight_bwd_bits_kernel(const WeightBwdArgs p) {
+    WarpTile<true> wt;
+    if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
+    float v[kWtNV][4];    // s = (g_T + g_w*a) * T, reverse-exclusive-summed
+    float dir[kWtNV][4];  // direct term
+    float sc[kWtNV][4];   // alpha: max(1-a, 1e-10) ; density: te - ts
+#pragma unroll
+    for (int k = 0; k < kWtNV; ++k) {
+        float T[4], gw[4], gT[4], a[4];
+        wt.load(p.trans, k, 0.0f, T);
+        if (p.g_weights) wt.load(p.g_weights, k, 0.0f, gw);
+        else { gw[0] = gw[1] = gw[2] = gw[3] = 0.0f; }
+        if (p.g_trans) wt.load(p.g_trans, k, 0.0f, gT);
+        else { gT[0] = gT[1] = gT[2] = gT[3] = 0.0f; }
+        if (DENSITY) {
+            float ts[4], te[4], s[4], ga[4];
+            wt.load(p.t_starts, k, 0.0f, ts);
+            wt.load(p.t_ends, k, 0.0f, te);
+            wt.load(p.sigmas, k, 0.0f, s);
+            if (p.g_alphas) wt.load(p.g_alphas, k, 0.0f, ga);
+            else { ga[0] = ga[1] = ga[2] = ga[3] = 0.0f; }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float dt = __fsub_rn(te[c], ts[c]);
+                const float e = expf(-__fmul_rn(s[c], dt));
+                a[c] = __fsub_rn(1.0f, e);
+                sc[k][c] = dt;
+                dir[k][c] = __fmul_rn(__fadd_rn(ga[c], __fmul_rn(gw[c], T[c])), e);
+            }
+        } else {
+            wt.load(p.alphas, k, 0.0f, a);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                sc[k][c] = fmaxf(__fsub_rn(1.0f, a[c]), 1e-10f);
+                dir[k][c] = __fmul_rn(gw[c], T[c]);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            v[k][c] = __fmul_rn(__fadd_rn(gT[c], __fmul_rn(gw[c], a[c])), T[c]);
+    }
+    float E[kWtNV];
+    wt.template scan<SumOp>(v, E, p.status, 1, 0, p.epoch);
+#pragma unroll
+    for (int k = 0; k < kWtNV; ++k) {
+        if (k == kWtVec && !wt.over) break;
+        float R[4], o[4];
+        finish_exclusive<SumOp>(v[k], wt.f[k], E[k], R);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (DENSITY) o[c] = __fmul_rn(__fsub_rn(dir[k][c], R[c]), sc[k][c]);
+            else o[c] = __fsub_rn(dir[k][c], __fdiv_rn(R[c], sc[k][c]));
+        }
+        wt.store(p.g_in, k, o);
     }
 }
 
@@ -278,6 +414,68 @@ NFB_API int nfb_render_weight_bwd(int from_density, const float* g_weights, cons
     else weight_bwd_kernel<false><<<(unsigned)a.n_tiles, kThreads, 0, s>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("render_weight_bwd");
+    return NFB_OK;
+}
+
+/* nfb_render_weight_fwd / _bwd for a dense packed layout given as head bits (nfb_head_bits). */
+NFB_API int nfb_render_weight_bits_fwd(int from_density, const float* alphas, const float* t_starts,
+                                       const float* t_ends, const float* sigmas,
+                                       const float* prefix_trans, const uint32_t* head_bits, int64_t n,
+                                       float* weights, float* trans, float* alphas_out, uint8_t* vis,
+                                       float early_stop_eps, float alpha_thre, void* workspace,
+                                       size_t workspace_bytes, uint32_t epoch, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0, "negative size");
+    if (n == 0) return NFB_OK;
+    NFB_CHECK_ARG(head_bits != nullptr, "null head_bits");
+    if (from_density) NFB_CHECK_ARG(t_starts && t_ends && sigmas, "density mode needs t_starts, t_ends, sigmas");
+    else NFB_CHECK_ARG(alphas != nullptr, "alpha mode needs alphas");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = prep_ws(workspace, workspace_bytes, n, epoch, s);
+    if (rc != NFB_OK) return rc;
+    WeightFwdArgs a{};
+    a.alphas = alphas; a.t_starts = t_starts; a.t_ends = t_ends; a.sigmas = sigmas; a.prefix = prefix_trans;
+    a.weights = weights; a.trans = trans; a.alphas_out = alphas_out; a.vis = vis;
+    a.early_stop_eps = early_stop_eps; a.alpha_thre = alpha_thre;
+    a.bits = head_bits;
+    a.n = n; a.n_tiles = num_warp_tiles(n);
+    a.status = static_cast<unsigned long long*>(workspace); a.epoch = epoch;
+    a.vec_ok = all_aligned16({alphas, t_starts, t_ends, sigmas, prefix_trans, weights, trans, alphas_out}) &&
+               (vis == nullptr || (reinterpret_cast<uintptr_t>(vis) & 3u) == 0);
+    const unsigned grid = (unsigned)ceil_div<long long>(a.n_tiles, kWarps);
+    if (from_density) weight_fwd_bits_kernel<true><<<grid, kThreads, 0, s>>>(a);
+    else weight_fwd_bits_kernel<false><<<grid, kThreads, 0, s>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("render_weight_bits_fwd");
+    return NFB_OK;
+}
+
+NFB_API int nfb_render_weight_bits_bwd(int from_density, const float* g_weights, const float* g_trans,
+                                       const float* g_alphas, const float* alphas, const float* t_starts,
+                                       const float* t_ends, const float* sigmas, const float* trans,
+                                       const uint32_t* head_bits, int64_t n, float* g_in, void* workspace,
+                                       size_t workspace_bytes, uint32_t epoch, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0, "negative size");
+    if (n == 0) return NFB_OK;
+    NFB_CHECK_ARG(head_bits && trans && g_in, "null pointer");
+    if (from_density) NFB_CHECK_ARG(t_starts && t_ends && sigmas, "density mode needs t_starts, t_ends, sigmas");
+    else NFB_CHECK_ARG(alphas != nullptr, "alpha mode needs alphas");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int rc = prep_ws(workspace, workspace_bytes, n, epoch, s);
+    if (rc != NFB_OK) return rc;
+    WeightBwdArgs a{};
+    a.g_weights = g_weights; a.g_trans = g_trans; a.g_alphas = g_alphas; a.alphas = alphas;
+    a.t_starts = t_starts; a.t_ends = t_ends; a.sigmas = sigmas; a.trans = trans; a.g_in = g_in;
+    a.bits = head_bits;
+    a.n = n; a.n_tiles = num_warp_tiles(n);
+    a.status = static_cast<unsigned long long*>(workspace); a.epoch = epoch;
+    a.vec_ok = all_aligned16({g_weights, g_trans, g_alphas, alphas, t_starts, t_ends, sigmas, trans, g_in});
+    const unsigned grid = (unsigned)ceil_div<long long>(a.n_tiles, kWarps);
+    if (from_density) weight_bwd_bits_kernel<true><<<grid, kThreads, 0, s>>>(a);
+    else weight_bwd_bits_kernel<false><<<grid, kThreads, 0, s>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("render_weight_bits_bwd");
     return NFB_OK;
 }
 

@@ -4,8 +4,12 @@ like-for-like bar of SURVEY.md §8(d).  Measurement tooling, not a product path.
 
     python profiles/bench_ops.py [--out gpurun_out/ops.json] [--quick]
 
-Method: CUDA events on the current stream, 5 warm-ups, 20 timed iterations, median; inputs are
-larger than L2 (126 MB) for every S-sized op.  GB/s = algorithmic bytes / time.
+Method: CUDA events on the current stream, 5 warm-ups, then 7 timed groups of 10 back-to-back
+calls (no host sync inside a group, as in a training loop that keeps the stream busy; a
+sync-bracketed single call adds 25-35 us of Python launch latency to these 60-200 us kernels),
+median over groups of the per-call time; inputs are larger than L2 (126 MB) for every S-sized
+op, so consecutive calls do not find their data cached.  GB/s = algorithmic bytes
+/ time.  Both libraries are timed the same way.
 """
 import argparse
 import json
@@ -31,18 +35,19 @@ except Exception:
     pass
 
 
-def timeit(fn, warm=5, iters=20):
+def timeit(fn, warm=5, groups=7, reps=10):
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
     ts = []
-    for _ in range(iters):
+    for _ in range(groups):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        fn()
+        for _ in range(reps):
+            fn()
         b.record()
         b.synchronize()
-        ts.append(a.elapsed_time(b))
+        ts.append(a.elapsed_time(b) / reps)
     return statistics.median(ts)
 
 
