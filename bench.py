@@ -224,6 +224,9 @@ ALGO_BYTES = {
     "render_rays_fwd": lambda S, R, B: 36 * S + 16 * R + 20 * R,
     # read ts,te,sigma,rgb,T (28) write g_sigma,g_rgb (16) + 5 floats/ray
     "render_rays_bwd": lambda S, R, B: 44 * S + 16 * R + 20 * R,
+    # the same on warp tiles: + 1 head bit per sample, one ray id (8 B) and 5 floats per ray
+    "render_bits_fwd": lambda S, R, B: 36 * S + S // 8 + 8 * R + 20 * R,
+    "render_bits_bwd": lambda S, R, B: 44 * S + S // 8 + 8 * R + 20 * R,
 }
 
 

@@ -353,6 +353,31 @@ NFB_API int nfb_render_rays_bwd(int from_density, const float* g_colors, const f
                                 int64_t n, float* g_in, float* g_rgbs, int lanes_per_ray,
                                 nfb_stream_t stream);
 
+/* The same rendering() on warp tiles, for a DENSE canonical layout given as head bits
+ * (nfb_head_bits) plus the API's ray_indices: samples are cut into 512-item tiles independent of
+ * the rays (coalesced 128-bit accesses throughout, cost independent of ray lengths).  Forward:
+ * one segmented scan for T / w and five segmented sums for the per-ray totals; the ray id of a
+ * ray's last sample is a sparse ray_indices load.  colors / opacity / depth are cleared by the
+ * call (rows of rays without samples are zero).  Backward: ray ids are propagated from the
+ * heads inside the tile, the per-ray gradient rows are gathered through them; no dense
+ * ray_indices read.  Replaces nerfacc/volrend.py:116-150 and its autograd, like
+ * nfb_render_rays_fwd / _bwd.  Workspace: nfb_render_bits_workspace_bytes(n). */
+NFB_API size_t nfb_render_bits_workspace_bytes(int64_t n);
+NFB_API int nfb_render_bits_fwd(int from_density, const float* alphas, const float* t_starts,
+                                const float* t_ends, const float* sigmas, const float* rgbs,
+                                const int64_t* ray_indices, const uint32_t* head_bits, int64_t n_rays,
+                                int64_t n, float* weights, float* trans, float* alphas_out,
+                                float* colors, float* opacity, float* depth, void* workspace,
+                                size_t workspace_bytes, uint32_t epoch, nfb_stream_t stream);
+NFB_API int nfb_render_bits_bwd(int from_density, const float* g_colors, const float* g_opacity,
+                                const float* g_depth, const float* g_weights, const float* g_trans,
+                                const float* g_alphas, const float* alphas, const float* t_starts,
+                                const float* t_ends, const float* sigmas, const float* rgbs,
+                                const float* trans, const int64_t* ray_indices,
+                                const uint32_t* head_bits, int64_t n, float* g_in, float* g_rgbs,
+                                void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                nfb_stream_t stream);
+
 /* ------------------------------------------------------------------------------------
  * Inverse-CDF resampling and per-ray search (nerfacc/cuda/csrc/pdf.cu).
  */

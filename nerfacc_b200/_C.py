@@ -86,6 +86,11 @@ _PROTOS = {
                             c_ptr, c_ptr, c_ptr, c_int, c_ptr],
     "nfb_render_rays_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                             c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_int, c_ptr],
+    "nfb_render_bits_workspace_bytes": [c_i64],
+    "nfb_render_bits_fwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr,
+                            c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_render_bits_bwd": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                            c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_size, c_u32, c_ptr],
     "nfb_pack_info": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_ray_aabb_intersect": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_f32, c_f32, c_ptr, c_ptr,
                                c_ptr, c_ptr],
@@ -113,6 +118,7 @@ _RESTYPES = {
     "nfb_last_error": C.c_char_p,
     "nfb_launch_count": C.c_longlong,
     "nfb_workspace_bytes": C.c_size_t,
+    "nfb_render_bits_workspace_bytes": C.c_size_t,
     "nfb_head_bits_bytes": C.c_size_t,
     "nfb_occ_binarize_workspace_bytes": C.c_size_t,
     "nfb_compact_workspace_bytes": C.c_size_t,

@@ -216,6 +216,24 @@ def _per_ray_kernels(n: int, n_rays: int) -> bool:
     return n_rays > 0 and n <= _PER_RAY_MAX_MEAN * n_rays
 
 
+# NFB_RENDER = bits | rays | flat forces one of the three implementations (experiments, tests).
+_RENDER_MODE = os.environ.get("NFB_RENDER", "")
+
+
+def _render_mode(n: int, n_rays: int, packed_info: Tensor) -> str:
+    """bits: dense canonical layout -> warp tiles (csrc/render_bits.cu), whatever the ray
+    lengths; rays: a group of lanes per ray (any chunk layout); flat: CTA tiles with look-back
+    for very long rays in a layout that is not known to be dense."""
+    mode = _RENDER_MODE
+    if mode not in ("bits", "rays", "flat"):
+        mode = "bits"
+    if mode == "bits" and (n == 0 or n_rays == 0 or head_bits(packed_info, n) is None):
+        mode = "rays" if _RENDER_MODE != "flat" else "flat"
+    if mode == "rays" and _RENDER_MODE != "rays" and not _per_ray_kernels(n, n_rays):
+        mode = "flat"
+    return mode
+
+
 class RenderComposite(torch.autograd.Function):
     """rendering() of volrend.py:14-158 for flattened CUDA inputs: one forward and one backward
     kernel (nfb_render_rays_fwd / nfb_render_rays_bwd, a group of lanes per ray) or, when rays
@@ -233,11 +251,27 @@ class RenderComposite(torch.autograd.Function):
         t_starts, t_ends = t_starts.contiguous(), t_ends.contiguous()
         dev = _C.require_cuda(field, rgbs, t_starts, t_ends, packed_info, ray_indices)
         n = field.numel()
-        colors = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)
-        opacity = torch.empty((n_rays, 1), dtype=torch.float32, device=dev)
-        depth = torch.empty((n_rays, 1), dtype=torch.float32, device=dev)
-        per_ray = _per_ray_kernels(n, n_rays)
-        if per_ray:
+        # one [5, n_rays]-sized buffer: the bits kernel clears it with a single memset
+        out5 = torch.empty(5 * n_rays, dtype=torch.float32, device=dev)
+        colors = out5[: 3 * n_rays].view(n_rays, 3)
+        opacity = out5[3 * n_rays: 4 * n_rays].view(n_rays, 1)
+        depth = out5[4 * n_rays:].view(n_rays, 1)
+        mode = _render_mode(n, n_rays, packed_info)
+        per_ray = mode == "rays"
+        if mode == "bits":
+            # warp tiles over the dense layout (csrc/render_bits.cu)
+            weights, trans = torch.empty_like(field), torch.empty_like(field)
+            alphas = torch.empty_like(field) if from_density else None
+            bits = head_bits(packed_info, n)
+            with torch.cuda.device(dev):
+                ws, ws_bytes, epoch = _C.workspace(dev, 8 * n)
+                rc = _C.lib().nfb_render_bits_fwd(
+                    int(from_density), None if from_density else _p(field), _p(t_starts), _p(t_ends),
+                    _p(field) if from_density else None, _p(rgbs), _p(ray_indices), _p(bits), n_rays, n,
+                    _p(weights), _p(trans), _p(alphas), colors.data_ptr(), opacity.data_ptr(),
+                    depth.data_ptr(), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+            _C.check(rc, "render_bits_fwd")
+        elif per_ray:
             # one kernel: weights + the three per-ray sums (csrc/render_rays.cu)
             weights, trans = torch.empty_like(field), torch.empty_like(field)
             alphas = torch.empty_like(field) if from_density else None
@@ -266,6 +300,7 @@ class RenderComposite(torch.autograd.Function):
                         epoch, _C.stream_ptr(dev))
                 _C.check(rc, "composite_fwd")
         ctx.per_ray = per_ray
+        ctx.mode = mode
         ctx.set_materialize_grads(False)
         ctx.from_density = from_density
         ctx.n_rays = n_rays
@@ -286,7 +321,16 @@ class RenderComposite(torch.autograd.Function):
         if n > 0:
             fd = ctx.from_density
             with torch.cuda.device(dev):
-                if ctx.per_ray:
+                if ctx.mode == "bits":
+                    bits = head_bits(packed_info, n)
+                    ws, ws_bytes, epoch = _C.workspace(dev, n)
+                    rc = _C.lib().nfb_render_bits_bwd(
+                        int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),
+                        _p(_cg(g_trans)), _p(_cg(g_alphas)) if fd else None,
+                        None if fd else _p(field), _p(t_starts), _p(t_ends), _p(field) if fd else None,
+                        _p(rgbs), _p(trans), _p(ray_indices), _p(bits), n,
+                        g_field.data_ptr(), _p(g_rgbs), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+                elif ctx.per_ray:
                     rc = _C.lib().nfb_render_rays_bwd(
                         int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),
                         _p(_cg(g_trans)), _p(_cg(g_alphas)) if fd else None,

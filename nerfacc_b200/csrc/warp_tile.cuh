@@ -76,6 +76,17 @@ struct WarpTile {
         over = p_nx > 0 && p_nx < 128;
         return true;
     }
+    // Pull the tile's (and overhang's) part of a stream into L2: lanes touch its 128-byte lines.
+    __device__ __forceinline__ void prefetch_l2(const void* p, int bytes_per_item) const {
+        const long long pt = (g0 - (REV ? (long long)(kWtVec - 1) * 128 + (31 - lane) * 4 : lane * 4));  // tile base
+        long long lo = REV ? pt - 128 : pt, hi = REV ? pt + kWtItems : pt + kWtItems + 128;
+        if (lo < 0) lo = 0;
+        if (hi > n) hi = n;
+        const char* b = reinterpret_cast<const char*>(p) + lo * bytes_per_item;
+        const long long bytes = (hi - lo) * bytes_per_item;
+        for (long long off = (long long)lane * 128; off < bytes; off += 32 * 128)
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(b + off));
+    }
     // physical index of the first item of logical vector k (k == kWtVec: the overhang)
     __device__ __forceinline__ long long g(int k) const { return k < kWtVec ? g0 + k * gstep : go; }
     // bit c set <=> this warp writes logical component c of vector k
@@ -130,7 +141,9 @@ struct WarpTile {
     //        (v[k], f[k], E[k]) to finish_inclusive / finish_exclusive for k = 0..kWtVec-1 and,
     //        when `over`, for k == kWtVec.
     // status: n_slots words per warp tile; `slot` selects the one this scan uses.
-    template <class Op>
+    // ALWAYS: scan the overhang whether or not it is used (kernels with a long tail after the
+    // scan: a branch on `over` here makes the compiler clone that tail for both outcomes).
+    template <class Op, bool ALWAYS = false>
     __device__ __forceinline__ void scan(float (&v)[kWtNV][4], float (&E)[kWtNV], unsigned long long* status,
                                          int n_slots, int slot, uint32_t epoch) const {
         float wc;
@@ -147,7 +160,7 @@ struct WarpTile {
 #pragma unroll
         for (int k = 0; k < kWtVec; ++k)
             if (open_vec[k]) E[k] = Op::apply(X, E[k]);
-        if (!over) return;
+        if (!ALWAYS && !over) return;
         const float carry = warp_open ? Op::apply(X, wc) : wc;  // inclusive value at my last item
         float (&u)[4] = v[kWtVec];
 #pragma unroll

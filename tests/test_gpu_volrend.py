@@ -257,21 +257,35 @@ def test_rendering_end_to_end(device):
 
 
 @pytest.mark.parametrize("mode", ["density", "alpha"])
-@pytest.mark.parametrize("path", ["per_ray", "per_ray_L4", "per_ray_L32", "tiles"])
+@pytest.mark.parametrize("path", ["bits", "bits_odd", "per_ray", "per_ray_L4", "per_ray_L32", "tiles"])
 def test_rendering_fused_composite_vs_oracle(device, mode, path, monkeypatch):
-    """rendering() on flattened inputs — the per-ray kernels (csrc/render_rays.cu, lanes per ray
-    chosen / forced) and the flat tile kernels (volrend.cu + composite.cu) — against the oracle's
-    composition of volrend.py:140-156, incl. empty rays, a long ray that spans several tiles, a
-    background colour, and an extra loss on extras['weights']."""
+    """rendering() on flattened inputs — the warp-tile kernels (csrc/render_bits.cu, the default
+    for dense layouts), the per-ray kernels (csrc/render_rays.cu, lanes per ray chosen / forced)
+    and the flat tile kernels (volrend.cu + composite.cu) — against the oracle's composition of
+    volrend.py:140-156, incl. empty rays, a long ray that spans several tiles, a background
+    colour, and an extra loss on extras['weights']."""
     import nerfacc_b200 as nf
     from nerfacc_b200 import _render_ops
 
-    if path == "tiles":
-        monkeypatch.setattr(_render_ops, "_PER_RAY_MAX_MEAN", 0)
-    elif path != "per_ray":
-        monkeypatch.setattr(_render_ops, "_RAYS_L", int(path.split("L")[1]))
+    if path.startswith("bits"):
+        monkeypatch.setattr(_render_ops, "_RENDER_MODE", "bits")
+    elif path == "tiles":
+        monkeypatch.setattr(_render_ops, "_RENDER_MODE", "flat")
+    else:
+        monkeypatch.setattr(_render_ops, "_RENDER_MODE", "rays")
+        if path != "per_ray":
+            monkeypatch.setattr(_render_ops, "_RAYS_L", int(path.split("L")[1]))
 
-    counts = ragged_counts(3000, mean=14, seed=5, long_rays=((17, 9000), (1500, 1)))
+    if path == "bits_odd":
+        # total not a multiple of 4, rays ending exactly on / one past warp-tile and overhang
+        # boundaries, runs of 1-sample rays, rays of 128..700 samples (look-back between warps)
+        counts = ragged_counts(2000, mean=9, seed=11, long_rays=((3, 509), (4, 3), (5, 128), (6, 127), (7, 700),
+                                                                 (900, 2049), (901, 1), (902, 1), (903, 1),
+                                                                 (1999, 131)))
+        if counts.sum() % 4 == 0:
+            counts[10] += 1
+    else:
+        counts = ragged_counts(3000, mean=14, seed=5, long_rays=((17, 9000), (1500, 1)))
     pi = packed_info_from_counts(counts)
     ri = ray_indices_from_counts(counts)
     n, R = int(counts.sum()), len(counts)
@@ -321,4 +335,6 @@ def test_rendering_fused_composite_vs_oracle(device, mode, path, monkeypatch):
         g_f = oracle.render_weight_from_alpha_bwd(gw, None, field, pi)
     assert_close(rgb_t.grad.cpu().numpy(), g_rgb, 1e-5, 1e-7, "g_rgb")
     scale = float(np.abs(g_f).max())
-    assert_close(f_t.grad.cpu().numpy(), g_f, 1e-4, 2e-6 * scale, "g_field")
+    # (bits_odd has 1-2 sample rays of tiny opacity: depth = d0 / o0 makes the per-ray gradient rows
+    # themselves — torch on the GPU vs numpy here — differ by a few 1e-4 relative after cancellation)
+    assert_close(f_t.grad.cpu().numpy(), g_f, 1e-4, (2e-5 if path == "bits_odd" else 2e-6) * scale, "g_field")
