@@ -230,6 +230,8 @@ typedef struct nfb_grid {
     const float* aabbs;         /* [n_grids, 6] */
     int32_t n_grids;            /* <= 8 (MAX_GRID_LEVELS, csrc/grid.cu:18) */
     int32_t res[3];
+    const int32_t* occ_bounds;  /* optional, from nfb_occupancy_bounds: per level the index box
+                                   (x0,y0,z0,x1,y1,z1) holding every occupied cell, or NULL */
 } nfb_grid_t;
 
 typedef struct nfb_march {
@@ -251,6 +253,13 @@ NFB_API int nfb_ray_aabb_intersect(const float* rays_o, const float* rays_d, con
 NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int32_t n_grids, const int32_t* res_host,
                                uint32_t* bits, uint32_t* mip_bits, int32_t mip_shift,
                                nfb_stream_t stream);
+
+/* bounds [n_grids, 6] int32 (device): per level the inclusive index box of the occupied cells,
+ * (res, res, res, -1, -1, -1) for a level without any.  A march that is past the box on an axis
+ * it moves away along can stop walking: only empty cells follow (the reference walks them to
+ * the end of the grid; nothing is emitted there).  `res_host`: HOST int[3]. */
+NFB_API int nfb_occupancy_bounds(const uint32_t* bits, int32_t n_grids, const int32_t* res_host,
+                                 int32_t* bounds, nfb_stream_t stream);
 
 /* Scratch needed by the traversal entry points (per-ray scan status words + ray counters). */
 NFB_API size_t nfb_traverse_scratch_bytes(int64_t n_rays);

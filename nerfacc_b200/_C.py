@@ -41,7 +41,7 @@ class Rays(C.Structure):
 class Grid(C.Structure):
     """nfb_grid_t"""
     _fields_ = [("occ_bits", c_ptr), ("occ_mip", c_ptr), ("mip_shift", C.c_int32), ("aabbs", c_ptr),
-                ("n_grids", C.c_int32), ("res", C.c_int32 * 3)]
+                ("n_grids", C.c_int32), ("res", C.c_int32 * 3), ("occ_bounds", c_ptr)]
 
 
 class March(C.Structure):
@@ -95,6 +95,7 @@ _PROTOS = {
     "nfb_ray_aabb_intersect": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_f32, c_f32, c_ptr, c_ptr,
                                c_ptr, c_ptr],
     "nfb_pack_occupancy": [c_ptr, C.c_int32, c_ptr, c_ptr, c_ptr, C.c_int32, c_ptr],
+    "nfb_occupancy_bounds": [c_ptr, C.c_int32, c_ptr, c_ptr, c_ptr],
     "nfb_traverse_run_bytes": [c_i64],
     "nfb_traverse_count": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                            c_size, c_ptr, c_size, c_ptr],

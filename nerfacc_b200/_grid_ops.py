@@ -12,19 +12,20 @@ from torch import Tensor
 
 from . import _C
 
-_BITS: Dict[int, Tuple[weakref.ref, int, Tensor, Optional[Tensor], int]] = {}
+_BITS: Dict[int, Tuple[weakref.ref, int, Tensor, Optional[Tensor], int, Optional[Tensor]]] = {}
 _MIP_BYTES_MAX = 40 * 1024  # mip kept in shared memory by the marching kernels (2 CTAs per SM must fit)
 
 
-def occupancy_bits(binaries: Tensor) -> Tuple[Tensor, Optional[Tensor], int]:
+def occupancy_bits(binaries: Tensor) -> Tuple[Tensor, Optional[Tensor], int, Optional[Tensor]]:
     """Bit-packed copy of a bool grid [m, rx, ry, rz] (int32 words, 32 cells each) and its
     "any occupied" mip (one bit per (2^shift)^3 block, sized to fit shared memory), cached per
     tensor object and in-place version so repeated marches through the same grid pack once.
-    Returns (bits, mip or None, shift)."""
+    Returns (bits, mip or None, shift, bounds or None) — bounds: per level the index box of the
+    occupied cells (nfb_occupancy_bounds)."""
     key = id(binaries)
     ent = _BITS.get(key)
     if ent is not None and ent[0]() is binaries and ent[1] == binaries._version:
-        return ent[2], ent[3], ent[4]
+        return ent[2], ent[3], ent[4], ent[5]
     dev = _C.require_cuda(binaries)
     b = binaries.contiguous()
     if b.dtype != torch.bool:
@@ -32,7 +33,7 @@ def occupancy_bits(binaries: Tensor) -> Tuple[Tensor, Optional[Tensor], int]:
     m, res = b.shape[0], [int(v) for v in b.shape[1:]]
     n = b.numel()
     bits = torch.empty(((n + 31) // 32,), dtype=torch.int32, device=dev)
-    mip, shift = None, 0
+    mip, shift, bounds = None, 0, None
     if n:
         for sh in range(1, 9):
             words = (m * math.prod((r + (1 << sh) - 1) >> sh for r in res) + 31) // 32
@@ -46,12 +47,17 @@ def occupancy_bits(binaries: Tensor) -> Tuple[Tensor, Optional[Tensor], int]:
                                              None if mip is None else mip.data_ptr(), shift,
                                              _C.stream_ptr(dev))
         _C.check(rc, "pack_occupancy")
+        bounds = torch.empty((m, 6), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            rc = _C.lib().nfb_occupancy_bounds(bits.data_ptr(), m, res_host, bounds.data_ptr(),
+                                               _C.stream_ptr(dev))
+        _C.check(rc, "occupancy_bounds")
 
     def _drop(_r, key=key):
         _BITS.pop(key, None)
 
-    _BITS[key] = (weakref.ref(binaries, _drop), binaries._version, bits, mip, shift)
-    return bits, mip, shift
+    _BITS[key] = (weakref.ref(binaries, _drop), binaries._version, bits, mip, shift, bounds)
+    return bits, mip, shift, bounds
 
 
 _PINNED: Dict[int, Tensor] = {}
@@ -77,8 +83,8 @@ class Marcher:
         self.rays_o, self.rays_d, self.aabbs = f32(rays_o), f32(rays_d), f32(aabbs)
         self.n_rays = self.rays_o.shape[0]
         assert binaries.dim() == 4 and binaries.shape[0] == self.aabbs.shape[0]
-        self.bits, self.mip, mip_shift = occupancy_bits(binaries)
-        keep = [self.rays_o, self.rays_d, self.aabbs, self.bits, self.mip]
+        self.bits, self.mip, mip_shift, self.bounds = occupancy_bits(binaries)
+        keep = [self.rays_o, self.rays_d, self.aabbs, self.bits, self.mip, self.bounds]
         r = _C.Rays()
         r.rays_o, r.rays_d = self.rays_o.data_ptr(), self.rays_d.data_ptr()
         r.n_rays = self.n_rays
@@ -103,6 +109,8 @@ class Marcher:
         g.occ_bits, g.aabbs, g.n_grids = self.bits.data_ptr(), self.aabbs.data_ptr(), binaries.shape[0]
         if self.mip is not None:
             g.occ_mip, g.mip_shift = self.mip.data_ptr(), mip_shift
+        if self.bounds is not None:
+            g.occ_bounds = self.bounds.data_ptr()
         g.res[0], g.res[1], g.res[2] = binaries.shape[1], binaries.shape[2], binaries.shape[3]
         self._keep, self.rays, self.grid = keep, r, g
         self.march = _C.March(float(step_size), float(cone_angle), int(limit))

@@ -365,6 +365,63 @@ __global__ void pack_mip_kernel(const uint8_t* __restrict__ binaries, int n_grid
     }
 }
 
+// Index box of the occupied cells of each level: bounds[l] = (x0,y0,z0,x1,y1,z1), from the bit
+// field (one thread per 32-cell word, warp-reduced, then six atomics per warp that saw any).
+__global__ void occ_bounds_init_kernel(int n_grids, int rx, int ry, int rz, int* __restrict__ bounds) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_grids * 6) {
+        const int k = i % 6;
+        bounds[i] = k >= 3 ? -1 : (k == 0 ? rx : (k == 1 ? ry : rz));
+    }
+}
+__global__ void occ_bounds_kernel(const uint32_t* __restrict__ bits, int n_grids, int rx, int ry, int rz,
+                                  int* __restrict__ bounds) {
+    const long long per_level = (long long)rx * ry * rz;
+    const long long n_cells = per_level * n_grids;
+    const long long n_words = (n_cells + 31) >> 5;
+    for (long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) & ~31ll; w0 < n_words;
+         w0 += (long long)gridDim.x * blockDim.x) {
+        const long long w = w0 + (threadIdx.x & 31);
+        uint32_t word = w < n_words ? __ldg(bits + w) : 0u;
+        // a warp's 1024 cells may straddle levels: take them one level at a time
+        while (true) {
+            int level = 0x7fffffff;
+            if (word) {
+                const long long c0 = w * 32 + (__ffs(word) - 1);
+                if (c0 < n_cells) level = (int)(c0 / per_level);
+            }
+            level = __reduce_min_sync(kFull, level);
+            if (level == 0x7fffffff) break;
+            int lo[3] = {rx, ry, rz}, hi[3] = {-1, -1, -1};
+            uint32_t rest = 0u;
+            while (word) {
+                const int b = __ffs(word) - 1;
+                word &= word - 1u;
+                const long long c = w * 32 + b;
+                if (c >= n_cells) continue;
+                if ((int)(c / per_level) != level) { rest |= 1u << b; continue; }
+                const long long q = c - (long long)level * per_level;
+                const int z = (int)(q % rz), y = (int)((q / rz) % ry), x = (int)(q / ((long long)rz * ry));
+                lo[0] = min(lo[0], x); lo[1] = min(lo[1], y); lo[2] = min(lo[2], z);
+                hi[0] = max(hi[0], x); hi[1] = max(hi[1], y); hi[2] = max(hi[2], z);
+            }
+            word = rest;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = __reduce_min_sync(kFull, lo[k]);
+                hi[k] = __reduce_max_sync(kFull, hi[k]);
+            }
+            if ((threadIdx.x & 31) == 0 && hi[0] >= 0) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    atomicMin(bounds + 6 * level + k, lo[k]);
+                    atomicMax(bounds + 6 * level + 3 + k, hi[k]);
+                }
+            }
+        }
+    }
+}
+
 static inline unsigned grid_for(long long n, int block, int per_sm = 16) {
     long long b = ceil_div<long long>(n, block);
     const long long cap = (long long)sm_count() * per_sm;
@@ -437,6 +494,7 @@ static GridSpec to_grid(const nfb_grid_t* g) {
     G.occ_bits = g->occ_bits; G.aabbs = g->aabbs; G.n_grids = g->n_grids;
     G.res[0] = g->res[0]; G.res[1] = g->res[1]; G.res[2] = g->res[2];
     G.cells_per_level = (long long)g->res[0] * g->res[1] * g->res[2];
+    G.bounds = g->occ_bounds;
     G.mip = nullptr; G.mip_shift = 0; G.mres[0] = G.mres[1] = G.mres[2] = 0;
     G.mip_cells_per_level = 0; G.mip_words = 0;
     if (g->occ_mip != nullptr && g->mip_shift > 0) {
@@ -524,6 +582,23 @@ NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int32_t n_grids, const i
         count_launch();
     }
     NFB_CHECK_LAUNCH("pack_occupancy");
+    return NFB_OK;
+}
+
+NFB_API int nfb_occupancy_bounds(const uint32_t* bits, int32_t n_grids, const int32_t* res_host,
+                                 int32_t* bounds, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_grids >= 0 && res_host != nullptr, "bad grid shape");
+    if (n_grids == 0) return NFB_OK;
+    NFB_CHECK_ARG(bits && bounds, "null pointer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const long long n_cells = (long long)n_grids * res_host[0] * res_host[1] * res_host[2];
+    occ_bounds_init_kernel<<<1, 64, 0, s>>>(n_grids, res_host[0], res_host[1], res_host[2], bounds);
+    if (n_cells > 0)
+        occ_bounds_kernel<<<grid_for((n_cells + 31) / 32, 256), 256, 0, s>>>(bits, n_grids, res_host[0], res_host[1],
+                                                                             res_host[2], bounds);
+    count_launch(2);
+    NFB_CHECK_LAUNCH("occupancy_bounds");
     return NFB_OK;
 }
 

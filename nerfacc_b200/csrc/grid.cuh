@@ -49,6 +49,8 @@ struct GridSpec {
     int mres[3];
     int mip_cells_per_level;
     int mip_words;
+    // per level the inclusive index box (x0,y0,z0,x1,y1,z1) of the occupied cells, or nullptr
+    const int* __restrict__ bounds;
 };
 
 // Copy the mip into shared memory (all threads of the CTA; ends with a barrier) and return a
@@ -258,6 +260,7 @@ enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2, EV_RAY = 3 };
 struct Dda {
     float tdist[3], delta[3];
     int cur[3], stepi[3], stop[3];
+    int cm;  // bit k: stop[k] was pulled in to the occupied box (leaving there skips empty cells)
 };
 
 // Next ray/box segment at or after event seg_i (grid.cu:128-149).
@@ -282,11 +285,15 @@ __device__ __forceinline__ bool find_segment(const RayEvents& ev, int m, int& se
 }
 
 // setup_traversal, utils_grid.cuh:58-114.
+// `clip`: the walk may also stop where only empty cells can follow — once it is past the box of
+// the level's occupied cells on an axis it moves away along.  Allowed when trailing empty cells
+// leave no trace in the output (their skip is folded or dropped; see march_engine).
 __device__ __forceinline__ void setup_dda(const float (&o)[3], const float (&d)[3], const GridSpec& G, int level,
-                                          float tmin, float tmax, Dda& S) {
+                                          float tmin, float tmax, Dda& S, bool clip) {
     const float eps = 1e-6f;
     const float* __restrict__ bb = G.aabbs + 6 * level;
     const float ts = __fadd_rn(tmin, eps), te = __fsub_rn(tmax, eps);
+    S.cm = 0;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float ok = o[k], dk = d[k];
@@ -311,6 +318,17 @@ __device__ __forceinline__ void setup_dda(const float (&o)[3], const float (&d)[
         const int ovf = fin + S.stepi[k];
         const bool ahead = S.stepi[k] > 0 ? ovf > S.cur[k] : (S.stepi[k] < 0 ? ovf < S.cur[k] : true);
         S.stop[k] = ahead ? ovf : (S.stepi[k] > 0 ? G.res[k] : -1);
+        if (clip && G.bounds != nullptr && S.stepi[k] != 0) {
+            // first index past the occupied box in my direction, but at least one step ahead (the
+            // leave test is an equality on the index just stepped to)
+            if (S.stepi[k] > 0) {
+                const int past = max(__ldg(G.bounds + 6 * level + 3 + k) + 1, S.cur[k] + 1);
+                if (past < S.stop[k]) { S.stop[k] = past; S.cm |= 1 << k; }
+            } else {
+                const int past = min(__ldg(G.bounds + 6 * level + k) - 1, S.cur[k] - 1);
+                if (past > S.stop[k]) { S.stop[k] = past; S.cm |= 1 << k; }
+            }
+        }
     }
 }
 
@@ -362,6 +380,9 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     const bool const_dt = (step > 0.0f) && (cone == 0.0f);
     const bool fold_empty = const_dt || step <= 0.0f;  // consecutive empty cells fold
     const bool fold_occ = const_dt;                    // consecutive occupied cells fold
+    // trailing empty cells of a segment leave no trace when their skip folds into the next event
+    // or is dropped at the end of the ray: the walk may then stop at the occupied box (setup_dda)
+    const bool clip = fold_empty && !P.wants_term();
     const bool eager = opt.limit > 0;  // with a sample cap, replay every round (bounds wasted DDA work)
     const int lane = lane_id();
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -509,7 +530,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             RayEvents pev;
             load_events(o, d, cand, t_sorted, t_indices, hits, G, pev);
             found = find_segment(pev, m, si, near, far, tmin, tmax, level);
-            if (found) setup_dda(o, d, G, level, tmin, tmax, S);
+            if (found) setup_dda(o, d, G, level, tmin, tmax, S, clip);
         }
         const unsigned okm = __ballot_sync(kFull, ok);
         if (ok) {
@@ -517,7 +538,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             e[0 * 32] = (uint32_t)(int)cand;
             e[1 * 32] = (found ? 1u : 0u) | ((uint32_t)level << 1) | ((uint32_t)si << 8) |
                         ((uint32_t)(S.stepi[0] + 1) << 16) | ((uint32_t)(S.stepi[1] + 1) << 18) |
-                        ((uint32_t)(S.stepi[2] + 1) << 20);
+                        ((uint32_t)(S.stepi[2] + 1) << 20) | ((uint32_t)S.cm << 22);
             if (found) {
                 e[2 * 32] = __float_as_uint(tmin);
                 e[3 * 32] = __float_as_uint(tmax);
@@ -567,6 +588,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     D.stop[a] = (int)e[(13 + a) * 32];
                     D.stepi[a] = (int)((misc >> (16 + 2 * a)) & 3u) - 1;
                 }
+                D.cm = (int)((misc >> 22) & 7u);
                 // right after the ray starts `continuous` is false: the segment start is a plain skip
                 have_ray = true;
                 if constexpr (DIRECT) {
@@ -634,6 +656,15 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         // the walk matters for nested grids: a lane that switched inside the walk would run the
         // rest of its round alone.
         if (have_ray && !in_seg && nq <= kQ - 3) {
+            // Left at the occupied box rather than at the end of the segment (the axis stepped last
+            // sits on a pulled-in stop): the cells not walked are empty — stand in for them with
+            // an empty span, whose t is replaced by the next segment's start or dropped below.
+            if (D.cm != 0) {
+                const bool early = ((D.cm & 1) && D.cur[0] == D.stop[0]) || ((D.cm & 2) && D.cur[1] == D.stop[1]) ||
+                                   ((D.cm & 4) && D.cur[2] == D.stop[2]);
+                if (early && pend_kind != EV_EMPTY) { push_pending(); pend_kind = EV_EMPTY; }
+                D.cm = 0;
+            }
             // a later segment of a multi-level march (the first one came prepared)
             bool found = false;
             float tmin = 0.0f;
@@ -662,7 +693,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                     push_pending();
                     event(EV_SEG, tmin);
                 }
-                setup_dda(o, d, G, level, tmin, tmax_seg, D);
+                setup_dda(o, d, G, level, tmin, tmax_seg, D, clip);
                 enter_segment(level);
             }
         }

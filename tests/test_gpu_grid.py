@@ -307,3 +307,55 @@ def test_sampling_run_pool_overflow(device):
     assert ri.shape[0] == r_ri.shape[0] > 50 * n_rays
     assert (ri.cpu().numpy() == r_ri).all()
     assert (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+
+
+def test_occupancy_bounds(device):
+    """nfb_occupancy_bounds vs numpy: levels whose cells do not fill whole 32-bit words or whole
+    warps of words, an empty level, a single cell."""
+    from nerfacc_b200 import _grid_ops
+
+    rng = np.random.default_rng(3)
+    for res in [(5, 7, 9), (33, 31, 37), (128, 128, 128)]:
+        bins = np.zeros((4,) + res, bool)
+        bins[0] = rng.random(res) < 0.01
+        bins[2, res[0] // 2, res[1] - 1, 0] = True
+        lo, hi = [r // 4 for r in res], [r // 2 + 1 for r in res]
+        bins[3, lo[0]:hi[0], lo[1]:hi[1], lo[2]:hi[2]] = rng.random([h - l for l, h in zip(lo, hi)]) < 0.3
+        _, _, _, bounds = _grid_ops.occupancy_bits(torch.from_numpy(bins).to(device))
+        got = bounds.cpu().numpy()
+        for l in range(4):
+            idx = np.argwhere(bins[l])
+            want = list(res) + [-1, -1, -1] if len(idx) == 0 else list(idx.min(0)) + list(idx.max(0))
+            assert got[l].tolist() == want, (res, l, got[l], want)
+
+
+@pytest.mark.parametrize("levels", [1, 3])
+def test_sampling_stops_at_occupied_box(device, levels):
+    """Marches that stop walking at the box of the occupied cells (grid.cuh setup_dda `clip`):
+    small off-centre blobs, an empty outer level, rays starting inside and outside the boxes and
+    moving every way — samples bit-exact against the oracle's full walk."""
+    import nerfacc_b200 as nf
+
+    res, n_rays = 32, 6000
+    rng = np.random.default_rng(17)
+    bins = np.zeros((levels, res, res, res), bool)
+    bins[0, 20:27, 3:9, 11:14] = rng.random((7, 6, 3)) < 0.6
+    bins[0, 5, 25, 30] = True
+    if levels > 1:
+        bins[1, 2:6, 10:30, 28:32] = rng.random((4, 20, 4)) < 0.5  # level 2 stays empty
+    base = np.array([-1, -1, -1, 1, 1, 1], np.float32)
+    aabbs = np.stack([_enlarge(base, 2**i) for i in range(levels)])
+    o = (rng.random((n_rays, 3)) * 6 - 3).astype(np.float32)
+    o[: n_rays // 3] = (rng.random((n_rays // 3, 3)) * 1.6 - 0.8).astype(np.float32)  # inside level 0
+    d = rng.standard_normal((n_rays, 3)).astype(np.float32)
+    d[::7, 0] = 0.0
+    d[::11, 2] = 0.0
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    est = nf.OccGridEstimator(base.tolist(), resolution=res, levels=levels).to(device)
+    est.binaries = torch.from_numpy(bins).to(device)
+    to, td = _gpu(device, o, d)
+    ri, ts, te = est.sampling(to, td, render_step_size=7e-3)
+    r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, aabbs, render_step_size=7e-3)
+    assert ri.shape[0] == r_ri.shape[0] and ri.shape[0] > 1000
+    assert (ri.cpu().numpy() == r_ri).all()
+    assert (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
