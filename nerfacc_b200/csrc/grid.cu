@@ -219,7 +219,7 @@ struct FillPolicy {
 // ---------------------------------------------------------------------------------- kernels
 // Persistent CTAs: dynamic shared memory = [mip words][event queue kQ x blockDim floats]
 // [prepared-ray pool: warps x kPoolWords x 32 words].
-constexpr int kMarchThreads = 512;
+constexpr int kMarchThreads = 384;  // x 2 CTAs/SM: 85 registers per thread (512 x 2 = 64 spills ten loop invariants of the DDA)
 
 template <bool MIP, bool DIRECT, class Policy>
 __global__ void __launch_bounds__(kMarchThreads, 2)
