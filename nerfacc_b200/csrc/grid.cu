@@ -229,8 +229,17 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
     const GridSpec G = stage_mip(Gp, s_dyn);
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
     uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * kMarchThreads);
+    float* s_ck = reinterpret_cast<float*>(s_pool + kPoolWords * kMarchThreads);
+    int* s_nck = reinterpret_cast<int*>(s_ck + kMaxCk);
+    // constant dt from one near plane: all rays walk one t sequence, checkpointed once per CTA
+    if (threadIdx.x == 0) {
+        const bool common = !DIRECT && opt.step_size > 0.0f && opt.cone_angle == 0.0f && A.near_arr == nullptr;
+        *s_nck = common ? make_checkpoints(A.near_s, opt.step_size, s_ck) : 0;
+    }
+    __syncthreads();
     march_engine<MIP, DIRECT>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
-                 A.hits, A.ray_list, A.ray_list ? A.n_work : A.n_rays, G, opt, P, s_evt, s_pool, ray_counter);
+                 A.hits, A.ray_list, A.ray_list ? A.n_work : A.n_rays, G, opt, P, s_evt, s_pool, s_ck, *s_nck,
+                 ray_counter);
 }
 
 // Pass 2 of OccGridEstimator.sampling when pass 1 left a run buffer: no marching at all.
@@ -442,7 +451,7 @@ template <class Policy>
 static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& opt, const Policy& P,
                         unsigned long long* counter, cudaStream_t s) {
     const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float) +
-                        (size_t)kPoolWords * kMarchThreads * sizeof(uint32_t);
+                        (size_t)kPoolWords * kMarchThreads * sizeof(uint32_t) + (kMaxCk + 4) * sizeof(float);
     // cone stepping (dt follows t) folds nothing: events are applied in place, without the queue
     const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
     auto kernel = G.mip != nullptr ? (direct ? march_kernel<true, true, Policy> : march_kernel<true, false, Policy>)

@@ -220,6 +220,47 @@ struct NoPiece {
     NFB_HD void operator()(float, float, int) const {}
 };
 
+// Checkpoints of the common trajectory.  With a constant dt and one near plane for all rays,
+// every ray's t_last walks the SAME sequence near, near+dt, ... (rounded as the hardware rounds):
+// rays differ only in where they stop.  A CTA records a point of that sequence per stretch of
+// constant increment (about one per binade) once; a long skip — a ray's first one runs from the
+// near plane to the scene, a dozen binades — then starts from the last checkpoint that is not
+// past its target instead of re-deriving every binade on the way.
+constexpr int kMaxCk = 64;
+__device__ __forceinline__ int make_checkpoints(float near, float dt, float* __restrict__ ck) {
+    int n = 0, cap_hits = 0;
+    float t = near;
+    while (n < kMaxCk && cap_hits < 4) {
+        ck[n++] = t;
+        // to the end of t's binade (or 4096 steps, whichever comes first)
+        const uint32_t E = __float_as_uint(t) >> 23;
+        const bool binade = t > 0.0f && E >= 1u && E < 254u;  // else (zero, negative, denormal): single steps
+        int cnt = 0;
+        float t2 = t;
+        if (binade) t2 = advance(t, dt, __uint_as_float((E + 1u) << 23), 4096, cnt, NoPiece());
+        if (cnt >= 4096) ++cap_hits;
+        float t3 = t2;
+        if (cnt == 0) {  // already within dt/2 of the binade's top: take the crossing step itself
+            t3 = __fadd_rn(t2, dt);
+            if (!(t3 > t2)) break;
+        }
+        t = t3;
+    }
+    return n;
+}
+// last checkpoint c with !(fma(dt, .5, c) >= target), or `none` if even the first one is past
+__device__ __forceinline__ float checkpoint_before(const float* __restrict__ ck, int n, float dt, float target,
+                                                   float none) {
+    if (n == 0 || __fmaf_rn(dt, 0.5f, ck[0]) >= target) return none;
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__fmaf_rn(dt, 0.5f, ck[mid]) >= target) hi = mid;
+        else lo = mid;
+    }
+    return ck[lo];
+}
+
 // ---------------------------------------------------------------------------------------------
 // The marching engine.
 //
@@ -373,6 +414,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const int* __restrict__ ray_list, long long n_work,
                                              const GridSpec& G, const MarchOpts& opt, Policy& P,
                                              float* __restrict__ s_evt, uint32_t* __restrict__ s_pool,
+                                             const float* __restrict__ s_ck, int n_ck,
                                              unsigned long long* __restrict__ ray_counter) {
     const int m = G.n_grids;
     const float step = opt.step_size, cone = opt.cone_angle;
@@ -467,6 +509,13 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                         continuous = true;
                     });
                 } else {
+                    // a skip over more than a binade: start from the common trajectory's last
+                    // checkpoint before the target (see make_checkpoints)
+                    if (n_ck > 0 && t > t_last && t_last >= 0.0f &&
+                        (__float_as_uint(t) >> 23) > (__float_as_uint(t_last) >> 23) + 1u) {
+                        const float c = checkpoint_before(s_ck, n_ck, step, t, t_last);
+                        if (c > t_last) t_last = c;
+                    }
                     t_last = advance(t_last, step, t, 0x7fffffff, dummy, NoPiece());
                 }
             }

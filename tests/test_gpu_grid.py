@@ -359,3 +359,22 @@ def test_sampling_stops_at_occupied_box(device, levels):
     assert ri.shape[0] == r_ri.shape[0] and ri.shape[0] > 1000
     assert (ri.cpu().numpy() == r_ri).all()
     assert (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+
+
+@pytest.mark.parametrize("near,step", [(0.0, 5e-3), (0.05, 0.0123), (1.3, 1.5 * 2.0**-8), (0.0, 2.0**-7),
+                                       (2.9, 3e-3), (0.0, 0.25)])
+def test_sampling_long_skips_from_checkpoints(device, near, step):
+    """Constant dt from one near plane: long skips start from a checkpoint of the common t
+    sequence (grid.cuh make_checkpoints) — bit-exact against the oracle's step-by-step walk for
+    near planes before / inside the scene and step sizes with short and long mantissas."""
+    import nerfacc_b200 as nf
+
+    o, d, bins, aabbs = _shell_scene(n_rays=1 << 12, res=64, seed=21)
+    est = nf.OccGridEstimator(aabbs[0].tolist(), resolution=64, levels=1).to(device)
+    est.binaries = torch.from_numpy(bins).to(device)
+    to, td = _gpu(device, o, d)
+    ri, ts, te = est.sampling(to, td, render_step_size=step, near_plane=near)
+    r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, aabbs, near_plane=near, render_step_size=step)
+    assert ri.shape[0] == r_ri.shape[0] and ri.shape[0] > 100
+    assert (ri.cpu().numpy() == r_ri).all()
+    assert (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
