@@ -244,48 +244,105 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
 
 // Pass 2 of OccGridEstimator.sampling when pass 1 left a run buffer: no marching at all.
 // One warp owns 32 consecutive rays, whose samples are one contiguous stretch of the packed
-// output.  Each lane stages its ray's runs in shared memory; then the whole warp expands run
-// after run — lane j of the warp writes sample j, j+32, ... of the run — so ray_indices /
-// t_starts / t_ends are written as contiguous warp stores instead of 32 scattered scalars.
+// output.  The lanes list their rays' runs in shared memory in sample order; then the warp
+// walks the OUTPUT: each lane takes four consecutive samples of a 16-byte aligned group, finds
+// their run by binary search in the list and writes ray_indices / t_starts / t_ends as 128-bit
+// stores — full 512-byte warp transactions whatever the run lengths are.
 // Runs beyond a ray's inline slots are expanded from the pool by traverse_expand_pool_kernel;
 // rays flagged kRunSlots + 1 (pool full) are left to a march_kernel launch over a work list.
 constexpr int kExpandWarps = 8;
+constexpr int kExpandRuns = 32 * kRunSlots;  // inline runs of a warp's 32 rays
 __global__ void __launch_bounds__(kExpandWarps * 32)
 traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info,
                        const Run* __restrict__ runs, const int* __restrict__ n_runs,
                        int64_t* __restrict__ ray_indices, float* __restrict__ t_starts,
-                       float* __restrict__ t_ends) {
-    __shared__ Run s_runs[kExpandWarps][32][kRunSlots];
+                       float* __restrict__ t_ends, bool vec_ok) {
+    // the warp's runs in sample order: first sample (relative to the warp's first), length, t0, q, ray
+    __shared__ int s_start[kExpandWarps][kExpandRuns];
+    __shared__ int s_n[kExpandWarps][kExpandRuns];
+    __shared__ float s_t0[kExpandWarps][kExpandRuns];
+    __shared__ float s_q[kExpandWarps][kExpandRuns];
+    __shared__ uint8_t s_ray[kExpandWarps][kExpandRuns];
     const int lane = lane_id(), w = warp_id();
     const long long n_groups = (n_rays + 31) >> 5;
     for (long long g = (long long)blockIdx.x * kExpandWarps + w; g < n_groups;
          g += (long long)gridDim.x * kExpandWarps) {
         const long long r = g * 32 + lane;
-        long long base = 0;
+        long long start = 0, cnt = 0;
         int nr = 0;
         if (r < n_rays) {
-            base = load_chunk(sample_info, r).start;
+            const RayChunk c = load_chunk(sample_info, r);
+            start = c.start; cnt = c.cnt;
             nr = __ldg(n_runs + r);
         }
+        const long long base0 = __shfl_sync(kFull, start, 0);
+        const int span = __reduce_max_sync(kFull, (int)(start + cnt - base0));  // the warp's samples: [base0, base0 + span)
         const int mine = nr <= kRunSlots ? nr : 0;
-        for (int s = 0; s < mine; ++s)
-            *reinterpret_cast<int4*>(&s_runs[w][lane][s]) =
-                __ldg(reinterpret_cast<const int4*>(runs + r * kRunSlots + s));
+        int pos = mine;  // exclusive prefix of the run counts
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int y = __shfl_up_sync(kFull, pos, d);
+            if (lane >= d) pos += y;
+        }
+        const int total = __shfl_sync(kFull, pos, 31);
+        pos -= mine;
+        for (int s = 0; s < mine; ++s) {
+            const int4 v = __ldg(reinterpret_cast<const int4*>(runs + r * kRunSlots + s));
+            s_t0[w][pos + s] = __int_as_float(v.x);
+            s_q[w][pos + s] = __int_as_float(v.y);
+            s_n[w][pos + s] = v.z;
+            s_start[w][pos + s] = (int)(start - base0) + v.w;
+            s_ray[w][pos + s] = (uint8_t)lane;
+        }
         __syncwarp();
-        unsigned todo = __ballot_sync(kFull, mine > 0);
-        while (todo) {
-            const int b = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const int nb = __shfl_sync(kFull, mine, b);
-            const long long base_b = __shfl_sync(kFull, base, b);
-            const long long rb = g * 32 + b;
-            for (int s = 0; s < nb; ++s) {
-                const Run run = s_runs[w][b][s];
-                long long i = base_b + run.s0 + lane;
-                for (int j = lane; j < run.n; j += 32, i += 32) {
-                    ray_indices[i] = rb;
-                    t_starts[i] = __fmaf_rn((float)j, run.q, run.t0);
-                    t_ends[i] = __fmaf_rn((float)(j + 1), run.q, run.t0);
+        if (total > 0) {
+            // Every lane takes four consecutive samples of a 16-byte aligned group and finds the run
+            // its first one lies in by binary search; samples of rays whose runs are pooled or
+            // re-marched lie in no listed run and are left to those passes.
+            const long long first = base0 & ~3ll;
+            for (long long i0 = first + 4 * lane; i0 < base0 + span; i0 += 128) {
+                const int rel = (int)(i0 - base0);  // >= -3
+                const int e0 = rel < 0 ? 0 : rel;
+                int lo = -1, hi = total;  // last run with start <= e0 (or -1)
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (s_start[w][mid] <= e0) lo = mid;
+                    else hi = mid;
+                }
+                int k = lo;
+                long long ri[4];
+                float ts[4], te[4];
+                unsigned ok = 0u;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int e = rel + c;
+                    while (k + 1 < total && s_start[w][k + 1] <= e) ++k;
+                    ri[c] = 0; ts[c] = te[c] = 0.0f;
+                    if (e >= 0 && e < span && k >= 0) {
+                        const int j = e - s_start[w][k];
+                        if (j < s_n[w][k]) {
+                            const float t0 = s_t0[w][k], q = s_q[w][k];
+                            ri[c] = g * 32 + s_ray[w][k];
+                            ts[c] = __fmaf_rn((float)j, q, t0);
+                            te[c] = __fmaf_rn((float)(j + 1), q, t0);
+                            ok |= 1u << c;
+                        }
+                    }
+                }
+                if (ok == 0xfu && vec_ok) {
+                    *reinterpret_cast<longlong2*>(ray_indices + i0) = make_longlong2(ri[0], ri[1]);
+                    *reinterpret_cast<longlong2*>(ray_indices + i0 + 2) = make_longlong2(ri[2], ri[3]);
+                    stg_stream4(t_starts + i0, make_float4(ts[0], ts[1], ts[2], ts[3]));
+                    stg_stream4(t_ends + i0, make_float4(te[0], te[1], te[2], te[3]));
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        if ((ok >> c) & 1u) {
+                            ray_indices[i0 + c] = ri[c];
+                            t_starts[i0 + c] = ts[c];
+                            t_ends[i0 + c] = te[c];
+                        }
+                    }
                 }
             }
         }
@@ -686,7 +743,8 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
         n_runs = reinterpret_cast<const int*>(runs + rays->n_rays * kRunSlots);
         const long long groups = (rays->n_rays + 31) / 32;
         traverse_expand_kernel<<<grid_for(groups, kExpandWarps, 8), kExpandWarps * 32, 0, s>>>(
-            rays->n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends);
+            rays->n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends,
+            aligned16(ray_indices) && aligned16(t_starts) && aligned16(t_ends));
         count_launch();
         NFB_CHECK_LAUNCH("traverse_expand");
         {   // pooled runs; the count stays on the device (the kernel reads the cursor)
