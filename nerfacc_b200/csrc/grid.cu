@@ -527,7 +527,17 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     const long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
     if (b > cap) b = cap;
     if (b < 1) b = 1;
-    kernel<<<(unsigned)b, kMarchThreads, smem, s>>>(A, G, opt, P, counter);
+    // Rays are handed out dynamically, `batch` per warp at a time: 32 when there is work for
+    // many rounds, fewer for small launches so that the last round does not leave most warps idle
+    // behind the few that drew a second batch.
+    MarchOpts o2 = opt;
+    {
+        const long long n_work = A.ray_list ? A.n_work : A.n_rays;
+        const long long warps = b * (kMarchThreads / 32);
+        long long per = ceil_div<long long>(n_work, warps * 2);
+        o2.batch = (int)(per < 8 ? 8 : (per > 32 ? 32 : per));
+    }
+    kernel<<<(unsigned)b, kMarchThreads, smem, s>>>(A, G, o2, P, counter);
     count_launch();
     NFB_CHECK_LAUNCH("march_kernel");
     return NFB_OK;
@@ -574,7 +584,7 @@ static GridSpec to_grid(const nfb_grid_t* g) {
     }
     return G;
 }
-static MarchOpts to_opts(const nfb_march_t* m) { return MarchOpts{m->step_size, m->cone_angle, m->traverse_steps_limit}; }
+static MarchOpts to_opts(const nfb_march_t* m) { return MarchOpts{m->step_size, m->cone_angle, m->traverse_steps_limit, 32}; }
 
 static size_t run_ints_bytes(size_t n) { return (2 * n * sizeof(int) + 15) & ~(size_t)15; }
 // the pieces of a run buffer of n rays (see nfb_traverse_run_bytes); cursor = counters + 2

@@ -69,6 +69,7 @@ struct MarchOpts {
     float step_size;
     float cone_angle;
     int limit;  // traverse_steps_limit, <= 0: none
+    int batch;  // rays a warp fetches at a time (1..32; set by the launcher from the launch size)
 };
 
 // Sorted ray/box events of one ray: 2*m values, the index (< m: entering level idx, else
@@ -559,10 +560,11 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     // ------------------------------------------------------------------ prepare (all 32 lanes)
     auto prepare = [&]() {
         unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(ray_counter, 32ull);
+        const int batch = opt.batch;
+        if (lane == 0) base = atomicAdd(ray_counter, (unsigned long long)batch);
         base = __shfl_sync(kFull, base, 0);
-        if ((long long)base + 32 >= n_work) exhausted = true;
-        bool ok = (long long)base + lane < n_work;
+        if ((long long)base + batch >= n_work) exhausted = true;
+        bool ok = lane < batch && (long long)base + lane < n_work;
         // work item -> ray id (identity unless a work list is given)
         const long long cand = !ok ? 0 : (ray_list ? (long long)__ldg(ray_list + base + lane) : (long long)base + lane);
         if (ok && !P.accept(cand)) { P.skipped(cand); ok = false; }
