@@ -189,7 +189,14 @@ template <bool FAST, bool REV>
 struct VecIO {
     const WarpTile<REV>& wt;
     __device__ __forceinline__ void load(const float* __restrict__ p, int k, float (&v)[4]) const {
-        if (FAST) {
+        if (FAST && k == kWtVec) {
+            // the overhang: only the lanes holding items before the next tile's first head
+            const float* q = p + wt.g0 + k * (REV ? -128 : 128);
+            v[0] = v[1] = v[2] = v[3] = 0.0f;
+            const bool need = wt.over && 4 * wt.lane < wt.p_nx;
+            if (REV) ldg_stream4_if(need, q, v[3], v[2], v[1], v[0]);
+            else ldg_stream4_if(need, q, v[0], v[1], v[2], v[3]);
+        } else if (FAST) {
             const float* q = p + wt.g0 + k * (REV ? -128 : 128);
             if (REV) ldg_nc4(q, v[3], v[2], v[1], v[0]);
             else ldg_nc4(q, v[0], v[1], v[2], v[3]);
@@ -201,9 +208,18 @@ struct VecIO {
         if (FAST) {
             const float* b = p + 3 * (wt.g0 + k * (REV ? -128 : 128));
             float t[12];
-            ldg_l1_4(b, t[0], t[1], t[2], t[3]);
-            ldg_l1_4(b + 4, t[4], t[5], t[6], t[7]);
-            ldg_l1_4(b + 8, t[8], t[9], t[10], t[11]);
+            if (k == kWtVec) {
+                const bool need = wt.over && 4 * wt.lane < wt.p_nx;
+#pragma unroll
+                for (int j = 0; j < 12; ++j) t[j] = 0.0f;
+                ldg_l1_4_if(need, b, t[0], t[1], t[2], t[3]);
+                ldg_l1_4_if(need, b + 4, t[4], t[5], t[6], t[7]);
+                ldg_l1_4_if(need, b + 8, t[8], t[9], t[10], t[11]);
+            } else {
+                ldg_l1_4(b, t[0], t[1], t[2], t[3]);
+                ldg_l1_4(b + 4, t[4], t[5], t[6], t[7]);
+                ldg_l1_4(b + 8, t[8], t[9], t[10], t[11]);
+            }
 #pragma unroll
             for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -413,7 +429,10 @@ __device__ __forceinline__ void render_bwd_stream(const RenderBitsArgs& p, const
     wt.prefetch_l2(p.trans_in, 4);
     wt.prefetch_l2(field, 4);
     wt.prefetch_l2(p.rgbs, 12);
-    wt.prefetch_l2(p.ray_indices, 8);
+    // ray ids are read at the heads only: pull in just those 32-byte sectors (a lane's four items)
+#pragma unroll
+    for (int k = 0; k < kWtVec; ++k)
+        if (wt.f[k] != 0u) asm volatile("prefetch.global.L2 [%0];" :: "l"(p.ray_indices + wt.g(k)));
     if (p.g_weights) wt.prefetch_l2(p.g_weights, 4);
     float wc = 0.0f;  // sum of v over the samples of the open ray behind (later than) the current one
     if (wt.need_x) wc = wait_final(p.status + (wt.t - 1), p.epoch);

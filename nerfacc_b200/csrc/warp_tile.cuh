@@ -79,7 +79,8 @@ struct WarpTile {
     // Pull the tile's (and overhang's) part of a stream into L2: lanes touch its 128-byte lines.
     __device__ __forceinline__ void prefetch_l2(const void* p, int bytes_per_item) const {
         const long long pt = (g0 - (REV ? (long long)(kWtVec - 1) * 128 + (31 - lane) * 4 : lane * 4));  // tile base
-        long long lo = REV ? pt - 128 : pt, hi = REV ? pt + kWtItems : pt + kWtItems + 128;
+        const int ov = over ? p_nx : 0;  // overhang items this warp produces
+        long long lo = REV ? pt - ov : pt, hi = REV ? pt + kWtItems : pt + kWtItems + ov;
         if (lo < 0) lo = 0;
         if (hi > n) hi = n;
         const char* b = reinterpret_cast<const char*>(p) + lo * bytes_per_item;
