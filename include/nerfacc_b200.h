@@ -387,6 +387,17 @@ NFB_API int nfb_render_bits_bwd(int from_density, const float* g_colors, const f
                                 void* workspace, size_t workspace_bytes, uint32_t epoch,
                                 nfb_stream_t stream);
 
+/* accumulate_along_rays (nerfacc/volrend.py:483-547) on the same warp tiles, for a dense canonical
+ * layout given as head bits + the API's ray_indices: out[r, :] (+)= sum over the samples of ray r
+ * of weights[i] * values[i, :] (values == NULL: the sum of weights), dim in 1..4.  Without
+ * add_into the call clears out first (rows of rays without samples are zero).
+ * Workspace: nfb_render_bits_workspace_bytes(n). */
+NFB_API int nfb_accumulate_bits_fwd(const float* weights, const float* values, int64_t dim,
+                                    const int64_t* ray_indices, const uint32_t* head_bits,
+                                    int64_t n_rays, int64_t n, float* out, int add_into,
+                                    void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                    nfb_stream_t stream);
+
 /* ------------------------------------------------------------------------------------
  * Inverse-CDF resampling and per-ray search (nerfacc/cuda/csrc/pdf.cu).
  */

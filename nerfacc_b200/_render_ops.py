@@ -155,7 +155,19 @@ def accumulate_fwd(weights: Tensor, values: Optional[Tensor], packed_info: Optio
     if out is None:
         out = torch.empty((n_rays, dim), dtype=weights.dtype, device=dev)
     n = weights.numel()
-    if n_rays > 0 and dim > 0:
+    bits = None
+    if n > 0 and 2 <= dim <= 4 and packed_info is not None and ray_indices is not None:
+        # dense layout: warp tiles (csrc/render_bits.cu); measured at 36.4M samples: D = 3 0.22 ms vs
+        # 0.33 ms on the flat CTA tiles, D = 1 0.106 vs 0.098 ms (kept on the flat tiles)
+        bits = head_bits(packed_info, n)
+    if bits is not None and n_rays > 0:
+        with torch.cuda.device(dev):
+            ws, ws_bytes, epoch = _C.workspace(dev, 8 * n)
+            rc = _C.lib().nfb_accumulate_bits_fwd(
+                _p(weights), _p(values), dim, _p(ray_indices), _p(bits), n_rays, n, out.data_ptr(),
+                int(add_into), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+        _C.check(rc, "accumulate_bits_fwd")
+    elif n_rays > 0 and dim > 0:
         with torch.cuda.device(dev):
             ws, ws_bytes, epoch = _C.workspace(dev, max(n, 1))
             rc = _C.lib().nfb_accumulate_fwd(

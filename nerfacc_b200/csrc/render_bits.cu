@@ -547,6 +547,130 @@ __global__ void __launch_bounds__(kThreads, MINB) render_bits_bwd_stream_kernel(
     else render_bwd_stream<DENSITY, false, AHEAD>(p, wt);
 }
 
+// ---------------------------------------------------------------------------------------------
+// accumulate_along_rays (volrend.py:483-547) on the same streaming warp tiles: out[r, :] = sum of
+// weights[i] * values[i, :] over the samples of ray r (values == NULL: sum of weights), D <= 4.
+struct AccBitsArgs {
+    const float* __restrict__ weights;
+    const float* __restrict__ values;  // [n, D] or NULL
+    const int64_t* __restrict__ ray_indices;
+    const uint32_t* __restrict__ bits;
+    long long n, n_tiles;
+    unsigned long long* status;
+    uint32_t epoch;
+    bool vec_ok, add_into;
+    float* __restrict__ out;  // [n_rays, D]
+};
+constexpr int kAccSlots = 4;
+
+template <int D, bool HAS_V, bool FAST>
+__device__ __forceinline__ void accumulate_stream(const AccBitsArgs& p, const WarpTile<false>& wt) {
+    const int lane = wt.lane;
+    const VecIO<FAST, false> io{wt};
+    float wc[D];
+#pragma unroll
+    for (int ch = 0; ch < D; ++ch) wc[ch] = 0.0f;
+    if (wt.need_x) {
+#pragma unroll
+        for (int ch = 0; ch < D; ++ch) wc[ch] = wait_final(p.status + (wt.t - 1) * kAccSlots + ch, p.epoch);
+    }
+    wt.prefetch_l2(p.weights, 4);
+    if (HAS_V) wt.prefetch_l2(p.values, 4 * D);
+#pragma unroll
+    for (int k = 0; k < kWtNV; ++k) {
+        const long long gg = wt.g(k);
+        float w[4], val[4][D];
+        io.load(p.weights, k, w);
+        if (HAS_V) {
+            // D consecutive floats per item, 4 items per lane: D 128-bit loads
+            float t[4 * D];
+#pragma unroll
+            for (int j = 0; j < 4 * D; ++j) t[j] = 0.0f;
+            const float* b = p.values + D * gg;
+            const bool need = k < kWtVec || (wt.over && 4 * lane < wt.p_nx);
+            const bool whole = wt.vec_ok && gg >= 0 && gg + 3 < wt.n && need;
+#pragma unroll
+            for (int j = 0; j < D; ++j) ldg_l1_4_if(whole, b + 4 * j, t[4 * j], t[4 * j + 1], t[4 * j + 2], t[4 * j + 3]);
+            if (!FAST) {
+#pragma unroll
+                for (int j = 0; j < 4 * D; ++j) {
+                    const long long gi = gg + j / D;
+                    ldg_stream_if(!whole && need && gi >= 0 && gi < wt.n, b + j, t[j]);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int ch = 0; ch < D; ++ch) val[c][ch] = t[D * c + ch];
+        }
+        uint32_t em;
+        if (k < kWtVec) {
+            em = end_nibble(p.bits, gg, p.n) & wt.mask(k);
+        } else {
+            const int d = wt.p_nx - 1 - 4 * lane;  // the overhang's one end: item p_nx - 1
+            em = (wt.over && d >= 0 && d < 4) ? (1u << d) : 0u;
+        }
+        const int cf = __ffs(em) - 1;
+        long long rid = 0;
+        if (em) rid = __ldg(p.ray_indices + gg + cf);
+        VecHeads H;
+        H.init(k < kWtVec ? head_nibble<false>(p.bits, gg, p.n) : 0u, lane);
+        const bool of = cf == 0 ? H.o0 : (cf == 1 ? H.o1 : (cf == 2 ? H.o2 : H.o3));
+        float sel[D];
+#pragma unroll
+        for (int ch = 0; ch < D; ++ch) {
+            float u0 = w[0], u1 = w[1], u2 = w[2], u3 = w[3], e;
+            if (HAS_V) {
+                u0 = __fmul_rn(u0, val[0][ch]); u1 = __fmul_rn(u1, val[1][ch]);
+                u2 = __fmul_rn(u2, val[2][ch]); u3 = __fmul_rn(u3, val[3][ch]);
+            }
+            vec_segscan<SumOp>(u0, u1, u2, u3, e, wc[ch], H, lane);
+            const float uf = cf == 0 ? u0 : (cf == 1 ? u1 : (cf == 2 ? u2 : u3));
+            sel[ch] = of ? __fadd_rn(e, uf) : uf;
+        }
+        if (em) {
+            float* __restrict__ o = p.out + D * rid;
+#pragma unroll
+            for (int ch = 0; ch < D; ++ch) o[ch] = p.add_into ? __fadd_rn(o[ch], sel[ch]) : sel[ch];
+            uint32_t more = em & (em - 1u);
+            while (more) {  // rays that start and end inside my four items
+                const int c = __ffs(more) - 1;
+                more &= more - 1u;
+                float a[D];
+#pragma unroll
+                for (int ch = 0; ch < D; ++ch) a[ch] = 0.0f;
+#pragma unroll
+                for (int j = 1; j < 4; ++j) {
+                    const bool hj = j == 1 ? H.h1 : (j == 2 ? H.h2 : H.h3);
+                    if (j <= c) {
+#pragma unroll
+                        for (int ch = 0; ch < D; ++ch) {
+                            if (hj) a[ch] = 0.0f;
+                            a[ch] = __fadd_rn(a[ch], HAS_V ? __fmul_rn(w[j], val[j][ch]) : w[j]);
+                        }
+                    }
+                }
+                float* __restrict__ o2 = p.out + D * __ldg(p.ray_indices + gg + c);
+#pragma unroll
+                for (int ch = 0; ch < D; ++ch) o2[ch] = p.add_into ? __fadd_rn(o2[ch], a[ch]) : a[ch];
+            }
+        }
+        if (k == kWtVec - 1 && wt.has_next && wt.p_nx == 128 && lane == 0) {
+#pragma unroll
+            for (int ch = 0; ch < D; ++ch)
+                st_relaxed_u64(p.status + wt.t * kAccSlots + ch, pack_status(wc[ch], p.epoch, 2u));
+        }
+    }
+}
+
+template <int D, bool HAS_V>
+__global__ void __launch_bounds__(kThreads, 3) accumulate_bits_kernel(const AccBitsArgs p) {
+    WarpTile<false> wt;
+    if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
+    if (!wt.slow) accumulate_stream<D, HAS_V, true>(p, wt);
+    else accumulate_stream<D, HAS_V, false>(p, wt);
+}
+
 static int prep_ws_rb(void* ws, size_t ws_bytes, size_t need, uint32_t& epoch, cudaStream_t s) {
     if (ws == nullptr || ws_bytes < need) {
         set_error("workspace too small: need %zu bytes, got %zu", need, ws_bytes);
@@ -658,6 +782,43 @@ NFB_API int nfb_render_bits_bwd(int from_density, const float* g_colors, const f
     else render_bits_bwd_stream_kernel<false, 3, false><<<grid, kThreads, 0, s>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("render_bits_bwd");
+    return NFB_OK;
+}
+
+/* accumulate_along_rays for a dense canonical layout given as head bits + ray_indices, dim <= 4. */
+NFB_API int nfb_accumulate_bits_fwd(const float* weights, const float* values, int64_t dim,
+                                    const int64_t* ray_indices, const uint32_t* head_bits,
+                                    int64_t n_rays, int64_t n, float* out, int add_into,
+                                    void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                    nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0 && n_rays >= 0 && dim >= 1 && dim <= 4, "bad sizes (dim must be 1..4)");
+    NFB_CHECK_ARG(values != nullptr || dim == 1, "dim must be 1 when values is NULL");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (n_rays == 0) return NFB_OK;
+    NFB_CHECK_ARG(out != nullptr, "null out");
+    if (!add_into && cudaMemsetAsync(out, 0, sizeof(float) * n_rays * dim, s) != cudaSuccess) {
+        set_error("accumulate_bits_fwd: clearing the output failed");
+        return NFB_ERR_CUDA;
+    }
+    if (n == 0) return NFB_OK;
+    NFB_CHECK_ARG(weights && ray_indices && head_bits, "null pointer");
+    int rc = prep_ws_rb(workspace, workspace_bytes, nfb_render_bits_workspace_bytes(n), epoch, s);
+    if (rc != NFB_OK) return rc;
+    AccBitsArgs a{};
+    a.weights = weights; a.values = values; a.ray_indices = ray_indices; a.bits = head_bits;
+    a.n = n; a.n_tiles = num_warp_tiles(n);
+    a.status = static_cast<unsigned long long*>(workspace); a.epoch = epoch;
+    a.vec_ok = all_aligned16_rb({weights, values});
+    a.add_into = add_into != 0; a.out = out;
+    const unsigned grid = (unsigned)ceil_div<long long>(a.n_tiles, kWarps);
+    if (values == nullptr) accumulate_bits_kernel<1, false><<<grid, kThreads, 0, s>>>(a);
+    else if (dim == 1) accumulate_bits_kernel<1, true><<<grid, kThreads, 0, s>>>(a);
+    else if (dim == 2) accumulate_bits_kernel<2, true><<<grid, kThreads, 0, s>>>(a);
+    else if (dim == 3) accumulate_bits_kernel<3, true><<<grid, kThreads, 0, s>>>(a);
+    else accumulate_bits_kernel<4, true><<<grid, kThreads, 0, s>>>(a);
+    count_launch();
+    NFB_CHECK_LAUNCH("accumulate_bits_fwd");
     return NFB_OK;
 }
 

@@ -191,6 +191,11 @@ def test_accumulate_fwd_bwd(device, dim, known_layout):
     assert_close(w.grad.cpu().numpy(), gw0, 1e-5, 1e-5, "g_weights")
     if vals is not None:
         assert_close(v.grad.cpu().numpy(), gv0, 1e-5, 1e-6, "g_values")
+    # in-place variant on the same layout: outputs += ray sums (rows of empty rays keep their value)
+    acc = torch.full((R, ref.shape[1]), 0.25, device=device)
+    nf.accumulate_along_rays_(w.detach(), None if v is None else v.detach(), rit, acc)
+    assert_close(acc.cpu().numpy(), ref + 0.25, 1e-5, 2e-6 * max(scale, 1.0), "accumulate_")
+    assert (acc.cpu().numpy()[counts == 0] == 0.25).all()
 
 
 def test_accumulate_kat_and_inplace(device):
