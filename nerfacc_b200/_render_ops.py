@@ -156,7 +156,8 @@ def accumulate_fwd(weights: Tensor, values: Optional[Tensor], packed_info: Optio
         out = torch.empty((n_rays, dim), dtype=weights.dtype, device=dev)
     n = weights.numel()
     bits = None
-    if n > 0 and 2 <= dim <= 4 and packed_info is not None and ray_indices is not None:
+    if (n > 0 and 2 <= dim <= 4 and packed_info is not None and ray_indices is not None
+            and _per_ray_kernels(n, n_rays)):
         # dense layout: warp tiles (csrc/render_bits.cu); measured at 36.4M samples: D = 3 0.22 ms vs
         # 0.33 ms on the flat CTA tiles, D = 1 0.106 vs 0.098 ms (kept on the flat tiles)
         bits = head_bits(packed_info, n)
@@ -239,6 +240,10 @@ def _render_mode(n: int, n_rays: int, packed_info: Tensor) -> str:
     mode = _RENDER_MODE
     if mode not in ("bits", "rays", "flat"):
         mode = "bits"
+    if mode == "bits" and _RENDER_MODE != "bits" and not _per_ray_kernels(n, n_rays):
+        # rays of > 512 samples on average: a streaming tile that continues a ray waits for the
+        # tile before it, a chain as long as the ray; the flat tiles' look-back has no such chain
+        mode = "flat"
     if mode == "bits" and (n == 0 or n_rays == 0 or head_bits(packed_info, n) is None):
         mode = "rays" if _RENDER_MODE != "flat" else "flat"
     if mode == "rays" and _RENDER_MODE != "rays" and not _per_ray_kernels(n, n_rays):

@@ -2,58 +2,53 @@
 // turns per-ray counts into packed_info starts (shared with the traversal).
 //
 // Reference: nerfacc/pack.py:43-46 = index_add_ of ones (one int64 atomic per sample) +
-// cumsum + stack (4 kernels, 3 temporaries).  Here: one histogram pass that issues one
-// atomic per *run* of equal indices, and one single-pass look-back scan over the rays that
-// writes (start, count) interleaved in place.
+// cumsum + stack (4 kernels, 3 temporaries).  Here: one pass that compares neighbours and issues
+// two atomics per *run* of equal indices (run end minus run start), and one single-pass
+// look-back scan over the rays that writes (start, count) interleaved in place.
 #include "seg_tile.cuh"
 
 namespace nfb {
 
 // counts[r] += length of every run of r in ray_indices; counts live at packed_info[2r+1].
+// A run [a, b) of equal indices contributes b - a: the thread holding its first element adds -a,
+// the one holding its last adds b (two 64-bit atomics per run, none per sample; any number of
+// runs per ray).  Every thread takes four consecutive indices as two 128-bit loads and gets its
+// neighbours' edge elements by shuffle; only the first and last lane of a warp read one more.
+constexpr int kHistPerThread = 4;
 __global__ void __launch_bounds__(kThreads)
 pack_hist_kernel(const int64_t* __restrict__ ray_indices, long long n, long long n_rays,
-                 long long n_tiles, int64_t* __restrict__ packed_info) {
-    __shared__ TileSmem sm;
-    const TileGeom<false> g(n, n_tiles);
-    float ones[kVec][4];
-    long long rid[kVec][4];
-    uint32_t f[kVec], tail[kVec];
+                 int64_t* __restrict__ packed_info, bool vec_ok) {
+    const int lane = lane_id();
+    const long long per_block = (long long)kThreads * kHistPerThread;
+    for (long long base = (long long)blockIdx.x * per_block; base < n; base += (long long)gridDim.x * per_block) {
+        const long long i0 = base + (long long)threadIdx.x * kHistPerThread;
+        long long v[kHistPerThread];
+        if (vec_ok && i0 + kHistPerThread <= n) {
+            const longlong2 a = __ldg(reinterpret_cast<const longlong2*>(ray_indices + i0));
+            const longlong2 b = __ldg(reinterpret_cast<const longlong2*>(ray_indices + i0 + 2));
+            v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+        } else {
 #pragma unroll
-    for (int k = 0; k < kVec; ++k) {
-        const long long gi = g.base + g.voff(k);
-        long long prev = (gi > g.base && gi - 1 < n) ? __ldg(ray_indices + gi - 1) : -1;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            rid[k][c] = (gi + c < n) ? __ldg(ray_indices + gi + c) : -1;
-            ones[k][c] = (gi + c < n) ? 1.0f : 0.0f;
+            for (int c = 0; c < kHistPerThread; ++c) v[c] = (i0 + c < n) ? __ldg(ray_indices + i0 + c) : -1;
         }
-        const bool last_in_tile = (g.voff(k) + 4 == kTile);
-        const long long after = (!last_in_tile && gi + 4 < n) ? __ldg(ray_indices + gi + 4) : -2;
-        f[k] = 0; tail[k] = 0;
+        long long prev = __shfl_up_sync(kFull, v[kHistPerThread - 1], 1);
+        long long next = __shfl_down_sync(kFull, v[0], 1);
+        if (lane == 0) prev = (i0 > 0 && i0 - 1 < n) ? __ldg(ray_indices + i0 - 1) : -1;
+        if (lane == 31) next = (i0 + kHistPerThread < n) ? __ldg(ray_indices + i0 + kHistPerThread) : -1;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const long long nx = (c < 3) ? ((gi + c + 1 < n) ? rid[k][(c + 1) & 3] : -2) : after;
-            if (gi + c < n) {
-                if (rid[k][c] != prev) f[k] |= (1u << (8 * c));
-                if (nx != rid[k][c]) tail[k] |= (1u << c);
-            }
-            prev = rid[k][c];
+        for (int c = 0; c < kHistPerThread; ++c) {
+            const long long i = i0 + c;
+            if (i >= n) break;
+            const long long r = v[c];
+            if (r < 0 || r >= n_rays) continue;
+            const long long before = c == 0 ? prev : v[c - 1];
+            const long long after = (c == kHistPerThread - 1) ? next : ((i + 1 < n) ? v[c + 1] : -1);
+            long long add = 0;
+            if (before != r) add -= i;
+            if (after != r) add += i + 1;
+            if (before != r || after != r)
+                atomicAdd(reinterpret_cast<unsigned long long*>(packed_info + 2 * r + 1), (unsigned long long)add);
         }
-    }
-    float E[kVec];
-    tile_segscan<SumOp, false>(ones, f, E, nullptr, 0, 0u, sm);  // run lengths <= 4096: exact in fp32
-#pragma unroll
-    for (int k = 0; k < kVec; ++k) {
-        float I[4];
-        finish_inclusive<SumOp>(ones[k], f[k], E[k], I);
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-            if ((tail[k] >> c) & 1u) {
-                const long long r = rid[k][c];
-                if (r >= 0 && r < n_rays)
-                    atomicAdd(reinterpret_cast<unsigned long long*>(packed_info + 2 * r + 1),
-                              (unsigned long long)(I[c] + 0.5f));
-            }
     }
 }
 
@@ -150,8 +145,11 @@ NFB_API int nfb_pack_info(const int64_t* ray_indices, int64_t n, int64_t n_rays,
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     cudaMemsetAsync(packed_info, 0, sizeof(int64_t) * 2 * n_rays, s);
     if (n > 0) {
-        const long long nt = num_tiles(n);
-        pack_hist_kernel<<<(unsigned)nt, kThreads, 0, s>>>(ray_indices, n, n_rays, nt, packed_info);
+        long long nb = ceil_div<long long>(n, (long long)kThreads * kHistPerThread);
+        const long long cap = (long long)sm_count() * 16;
+        if (nb > cap) nb = cap;
+        pack_hist_kernel<<<(unsigned)nb, kThreads, 0, s>>>(ray_indices, n, n_rays, packed_info,
+                                                           aligned16(ray_indices));
         count_launch();
         NFB_CHECK_LAUNCH("pack_hist");
     }
