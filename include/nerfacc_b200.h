@@ -398,6 +398,15 @@ NFB_API int nfb_accumulate_bits_fwd(const float* weights, const float* values, i
                                     void* workspace, size_t workspace_bytes, uint32_t epoch,
                                     nfb_stream_t stream);
 
+/* depth[r] = depth_sum[r] / max(opacity[r], FLT_EPSILON) in place (volrend.py:147-150), and the
+ * gradient of that quotient: g_depth_sum = g_depth / den, g_opacity_sum = g_opacity (NULL = 0)
+ * - g_depth * depth / den where opacity >= eps — one launch each instead of the reference's
+ * elementwise torch ops and autograd nodes on [n_rays] tensors. */
+NFB_API int nfb_depth_normalize_fwd(const float* opacity, float* depth, int64_t n_rays, nfb_stream_t stream);
+NFB_API int nfb_depth_normalize_bwd(const float* g_opacity, const float* g_depth, const float* opacity,
+                                    const float* depth, int64_t n_rays, float* g_opacity_sum,
+                                    float* g_depth_sum, nfb_stream_t stream);
+
 /* ------------------------------------------------------------------------------------
  * Inverse-CDF resampling and per-ray search (nerfacc/cuda/csrc/pdf.cu).
  */

@@ -93,6 +93,8 @@ _PROTOS = {
                             c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_size, c_u32, c_ptr],
     "nfb_accumulate_bits_fwd": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int, c_ptr, c_size, c_u32,
                                 c_ptr],
+    "nfb_depth_normalize_fwd": [c_ptr, c_ptr, c_i64, c_ptr],
+    "nfb_depth_normalize_bwd": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "nfb_pack_info": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_ray_aabb_intersect": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_f32, c_f32, c_ptr, c_ptr,
                                c_ptr, c_ptr],

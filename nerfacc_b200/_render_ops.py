@@ -263,7 +263,7 @@ class RenderComposite(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, field, rgbs, t_starts, t_ends, packed_info, ray_indices, n_rays: int,
-                from_density: bool):
+                from_density: bool, norm_depth: bool = False):
         field, rgbs = field.contiguous(), rgbs.contiguous()
         t_starts, t_ends = t_starts.contiguous(), t_ends.contiguous()
         dev = _C.require_cuda(field, rgbs, t_starts, t_ends, packed_info, ray_indices)
@@ -321,7 +321,15 @@ class RenderComposite(torch.autograd.Function):
         ctx.set_materialize_grads(False)
         ctx.from_density = from_density
         ctx.n_rays = n_rays
-        ctx.save_for_backward(field, rgbs, t_starts, t_ends, trans, packed_info, ray_indices)
+        if norm_depth and n_rays > 0:
+            # depth = sum(w t_mid) / max(opacity, eps) (volrend.py:147-150): one launch over the rays
+            with torch.cuda.device(dev):
+                rc = _C.lib().nfb_depth_normalize_fwd(opacity.data_ptr(), depth.data_ptr(), n_rays,
+                                                      _C.stream_ptr(dev))
+            _C.check(rc, "depth_normalize_fwd")
+        ctx.norm_depth = bool(norm_depth)
+        ctx.save_for_backward(field, rgbs, t_starts, t_ends, trans, packed_info, ray_indices,
+                              *([opacity, depth] if norm_depth else []))
         if alphas is None:
             alphas = field.new_empty(0)
             ctx.mark_non_differentiable(alphas)
@@ -329,12 +337,23 @@ class RenderComposite(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_colors, g_opacity, g_depth, g_weights, g_trans, g_alphas):
-        field, rgbs, t_starts, t_ends, trans, packed_info, ray_indices = ctx.saved_tensors
+        field, rgbs, t_starts, t_ends, trans, packed_info, ray_indices = ctx.saved_tensors[:7]
+        opacity, depth = ctx.saved_tensors[7:] if ctx.norm_depth else (None, None)
         dev = field.device
         n = field.numel()
         need_field, need_rgb = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         g_field = torch.empty_like(field)
         g_rgbs = torch.empty_like(rgbs) if need_rgb else None
+        if n > 0 and ctx.norm_depth and g_depth is not None:
+            # gradient through the quotient: replaces (g_opacity, g_depth) by the gradients of the sums
+            g_o0 = torch.empty_like(opacity)
+            g_d0 = torch.empty_like(depth)
+            with torch.cuda.device(dev):
+                rc = _C.lib().nfb_depth_normalize_bwd(_p(_cg(g_opacity)), _p(_cg(g_depth)), _p(opacity),
+                                                      _p(depth), ctx.n_rays, g_o0.data_ptr(), g_d0.data_ptr(),
+                                                      _C.stream_ptr(dev))
+            _C.check(rc, "depth_normalize_bwd")
+            g_opacity, g_depth = g_o0, g_d0
         if n > 0:
             fd = ctx.from_density
             with torch.cuda.device(dev):
@@ -363,4 +382,4 @@ class RenderComposite(torch.autograd.Function):
                         _p(rgbs), _p(trans), _p(ray_indices), _p(packed_info), ctx.n_rays, n,
                         g_field.data_ptr(), _p(g_rgbs), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
             _C.check(rc, "composite_bwd")
-        return (g_field if need_field else None), g_rgbs, None, None, None, None, None, None
+        return (g_field if need_field else None), g_rgbs, None, None, None, None, None, None, None

@@ -671,6 +671,28 @@ __global__ void __launch_bounds__(kThreads, 3) accumulate_bits_kernel(const AccB
     else accumulate_stream<D, HAS_V, false>(p, wt);
 }
 
+// depth = sum(w t_mid) / max(sum(w), eps) per ray (volrend.py:147-150) and its gradient, as one
+// kernel each way over the [n_rays] rows instead of a dozen torch elementwise launches.
+constexpr float kDepthEps = 1.1920928955078125e-07f;  // torch.finfo(torch.float32).eps
+__global__ void depth_normalize_fwd_kernel(const float* __restrict__ opacity, float* __restrict__ depth, long long n) {
+    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x)
+        depth[r] = __fdiv_rn(depth[r], fmaxf(__ldg(opacity + r), kDepthEps));
+}
+// g_d0 = g_depth / den; g_o0 = g_opacity - g_depth * depth / den where opacity >= eps (clamp_min)
+__global__ void depth_normalize_bwd_kernel(const float* __restrict__ g_opacity, const float* __restrict__ g_depth,
+                                           const float* __restrict__ opacity, const float* __restrict__ depth,
+                                           long long n, float* __restrict__ g_o0, float* __restrict__ g_d0) {
+    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+        const float o0 = __ldg(opacity + r);
+        const float den = fmaxf(o0, kDepthEps);
+        const float gdn = __fdiv_rn(__ldg(g_depth + r), den);
+        float go = g_opacity ? __ldg(g_opacity + r) : 0.0f;
+        if (o0 >= kDepthEps) go = __fsub_rn(go, __fmul_rn(gdn, __ldg(depth + r)));
+        g_o0[r] = go;
+        g_d0[r] = gdn;
+    }
+}
+
 static int prep_ws_rb(void* ws, size_t ws_bytes, size_t need, uint32_t& epoch, cudaStream_t s) {
     if (ws == nullptr || ws_bytes < need) {
         set_error("workspace too small: need %zu bytes, got %zu", need, ws_bytes);
@@ -819,6 +841,35 @@ NFB_API int nfb_accumulate_bits_fwd(const float* weights, const float* values, i
     else accumulate_bits_kernel<4, true><<<grid, kThreads, 0, s>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("accumulate_bits_fwd");
+    return NFB_OK;
+}
+
+NFB_API int nfb_depth_normalize_fwd(const float* opacity, float* depth, int64_t n_rays, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_rays >= 0, "negative size");
+    if (n_rays == 0) return NFB_OK;
+    NFB_CHECK_ARG(opacity && depth, "null pointer");
+    long long b = ceil_div<long long>(n_rays, 256);
+    if (b > (long long)sm_count() * 16) b = (long long)sm_count() * 16;
+    depth_normalize_fwd_kernel<<<(unsigned)b, 256, 0, static_cast<cudaStream_t>(stream)>>>(opacity, depth, n_rays);
+    count_launch();
+    NFB_CHECK_LAUNCH("depth_normalize_fwd");
+    return NFB_OK;
+}
+
+NFB_API int nfb_depth_normalize_bwd(const float* g_opacity, const float* g_depth, const float* opacity,
+                                    const float* depth, int64_t n_rays, float* g_opacity_sum,
+                                    float* g_depth_sum, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_rays >= 0, "negative size");
+    if (n_rays == 0) return NFB_OK;
+    NFB_CHECK_ARG(g_depth && opacity && depth && g_opacity_sum && g_depth_sum, "null pointer");
+    long long b = ceil_div<long long>(n_rays, 256);
+    if (b > (long long)sm_count() * 16) b = (long long)sm_count() * 16;
+    depth_normalize_bwd_kernel<<<(unsigned)b, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        g_opacity, g_depth, opacity, depth, n_rays, g_opacity_sum, g_depth_sum);
+    count_launch();
+    NFB_CHECK_LAUNCH("depth_normalize_bwd");
     return NFB_OK;
 }
 

@@ -91,14 +91,18 @@ def rendering(
     if flat and _composite_fused_ok(t_starts, t_ends, ray_indices, n_rays, rgbs, field):
         # one weights kernel + one composite kernel forward, one kernel backward
         pi = pack_info(ray_indices, n_rays)
+        # depth / max(opacity, eps) and its gradient are one launch each inside the Function
+        # (no [n_rays] torch ops and autograd nodes around the two big kernels)
+        fused_norm = True
         colors, opacities, depths, weights, trans, alphas = _ops.RenderComposite.apply(
             field, rgbs, t_starts.detach(), t_ends.detach(), pi, ray_indices.contiguous(), int(n_rays),
-            use_density)
+            use_density, fused_norm)
         if use_density:
             extras = {"weights": weights, "alphas": alphas, "trans": trans, "sigmas": field, "rgbs": rgbs}
         else:
             extras = {"weights": weights, "trans": trans, "rgbs": rgbs, "alphas": field}
-        depths = depths / opacities.clamp_min(torch.finfo(rgbs.dtype).eps)
+        if not fused_norm:
+            depths = depths / opacities.clamp_min(torch.finfo(rgbs.dtype).eps)
         if render_bkgd is not None:
             colors = colors + render_bkgd * (1.0 - opacities)
         return colors, opacities, depths, extras
