@@ -172,12 +172,14 @@ NFB_HD uint32_t f_bits(float a) { uint32_t r; memcpy(&r, &a, 4); return r; }
 NFB_HD float bits_f(uint32_t a) { float r; memcpy(&r, &a, 4); return r; }
 #endif
 
-template <class Piece>
+// HALF = false: the same with the stop test `t >= target` (the DDA's own recurrence tdist += delta,
+// consumed up to a time; see jump_ahead).
+template <bool HALF = true, class Piece>
 NFB_HD float advance(float t, const float dt, const float target, const int cap, int& steps,
                      Piece&& piece) {
     if (!(dt > 0.0f) || target != target) return t;
     while (steps < cap) {
-        if (rn_fma(dt, 0.5f, t) >= target) break;
+        if ((HALF ? rn_fma(dt, 0.5f, t) : t) >= target) break;
         const float t1 = rn_add(t, dt);
         if (!(t1 > t)) break;  // stuck at this magnitude (or NaN / inf)
         const float q = rn_sub(t1, t);  // exact: t1 is a grid point reached from t
@@ -194,11 +196,11 @@ NFB_HD float advance(float t, const float dt, const float target, const int cap,
                 int kmax = (0x1000000 - ti) / qi;  // >= 1 because t1 <= top
                 if (kmax > cap - steps) kmax = cap - steps;
                 auto t_at = [&](int k) { return rn_mul(i2f_rn(ti + k * qi), u); };
-                auto done = [&](int k) { return rn_fma(dt, 0.5f, t_at(k)) >= target; };
+                auto done = [&](int k) { return (HALF ? rn_fma(dt, 0.5f, t_at(k)) : t_at(k)) >= target; };
                 int k = kmax;
                 if (kmax > 1 && done(kmax)) {
                     // smallest k in [1, kmax] with done(k): estimate, then fix up (monotone)
-                    const float gap = rn_sub(target, rn_fma(dt, 0.5f, t));
+                    const float gap = rn_sub(target, HALF ? rn_fma(dt, 0.5f, t) : t);
                     const float kf = ceilf(rn_div(gap, q));
                     k = (kf >= (float)kmax) ? kmax : ((kf <= 1.0f) ? 1 : (int)kf);
                     while (k > 1 && done(k - 1)) --k;
@@ -372,6 +374,65 @@ __device__ __forceinline__ void setup_dda(const float (&o)[3], const float (&d)[
             }
         }
     }
+}
+
+// The cells a fresh segment crosses before the ray reaches the box of the occupied cells are
+// empty, but the walk needs the state it would have after them — and tdist[k] += delta[k] is the
+// same float recurrence as t += dt, so advance<false>() consumes, in closed form per binade, every
+// crossing of axis k with a time before t_in (the ray's entry into the occupied box grown by one
+// cell: the margin dwarfs the slab test's rounding).  All axes stop at the same time, so the state
+// reached is one the serial walk passes through (it takes crossings in time order).  t_first
+// becomes the exit time of the last cell skipped: the t of the empty span that stands for them.
+__device__ __forceinline__ void jump_ahead(const float (&o)[3], const float (&d)[3], const GridSpec& G, int level,
+                                           float tmin, float tmax, Dda& S, float& t_first) {
+    if (G.bounds == nullptr) return;
+    const float inf = __int_as_float(0x7f800000);
+    const float* __restrict__ bb = G.aabbs + 6 * level;
+    float t_in = -inf, t_out = inf;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float vox = (bb[3 + k] - bb[k]) / (float)G.res[k];
+        const float plo = bb[k] + (float)(__ldg(G.bounds + 6 * level + k) - 1) * vox;
+        const float phi = bb[k] + (float)(__ldg(G.bounds + 6 * level + 3 + k) + 2) * vox;
+        if (d[k] == 0.0f) {
+            if (o[k] < plo || o[k] > phi) t_out = -inf;  // never inside
+            continue;
+        }
+        const float a = (plo - o[k]) / d[k], b = (phi - o[k]) / d[k];
+        t_in = fmaxf(t_in, fminf(a, b));
+        t_out = fminf(t_out, fmaxf(a, b));
+    }
+    if (t_in >= t_out || t_out <= tmin || t_in >= tmax) {
+        // The ray does not meet the (grown) box inside this segment: every cell of the segment is
+        // empty.  Let the walk leave after its first step (an early leave at a pulled-in stop,
+        // which stands in for the cells not walked with one empty span).
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (S.stepi[k] != 0 && S.stop[k] != S.cur[k] + S.stepi[k]) { S.stop[k] = S.cur[k] + S.stepi[k]; S.cm |= 1 << k; }
+        return;
+    }
+    if (!(t_in > tmin)) return;  // starts inside the box
+    int n[3];
+    float tn[3], last = -inf;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        n[k] = 0;
+        tn[k] = S.tdist[k];
+        if (S.stepi[k] == 0) continue;
+        float lastk = -inf;
+        tn[k] = advance<false>(S.tdist[k], S.delta[k], t_in, 0x7fffffff, n[k],
+                               [&](float t0, float q, int kk) { lastk = __fmaf_rn((float)(kk - 1), q, t0); });
+        const int room = S.stop[k] > S.cur[k] ? S.stop[k] - S.cur[k] : S.cur[k] - S.stop[k];
+        if (n[k] >= room) return;  // would step out of the segment: leave it to the walk
+        last = fmaxf(last, lastk);
+    }
+    if (!(last > -inf)) return;  // nothing to skip
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        S.cur[k] += n[k] * S.stepi[k];
+        S.tdist[k] = tn[k];
+    }
+    t_first = fminf(last, tmax);
 }
 
 __device__ __forceinline__ void load_events(const float (&o)[3], const float (&d)[3], long long r,
@@ -569,7 +630,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         const long long cand = !ok ? 0 : (ray_list ? (long long)__ldg(ray_list + base + lane) : (long long)base + lane);
         if (ok && !P.accept(cand)) { P.skipped(cand); ok = false; }
         Dda S = {};
-        float tmin = 0.0f, tmax = 0.0f;
+        float tmin = 0.0f, tmax = 0.0f, t_first = 0.0f;
         int level = 0, si = 0;
         bool found = false;
         if (ok) {
@@ -581,7 +642,11 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             RayEvents pev;
             load_events(o, d, cand, t_sorted, t_indices, hits, G, pev);
             found = find_segment(pev, m, si, near, far, tmin, tmax, level);
-            if (found) setup_dda(o, d, G, level, tmin, tmax, S, clip);
+            if (found) {
+                setup_dda(o, d, G, level, tmin, tmax, S, clip);
+                t_first = tmin;
+                if (clip) jump_ahead(o, d, G, level, tmin, tmax, S, t_first);
+            }
         }
         const unsigned okm = __ballot_sync(kFull, ok);
         if (ok) {
@@ -591,7 +656,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                         ((uint32_t)(S.stepi[0] + 1) << 16) | ((uint32_t)(S.stepi[1] + 1) << 18) |
                         ((uint32_t)(S.stepi[2] + 1) << 20) | ((uint32_t)S.cm << 22);
             if (found) {
-                e[2 * 32] = __float_as_uint(tmin);
+                e[2 * 32] = __float_as_uint(t_first);  // end of the (empty) stretch before the first cell walked
                 e[3 * 32] = __float_as_uint(tmax);
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
