@@ -67,6 +67,19 @@ int main(int argc, char** argv) {
             return 1;
         }
         total_steps += s_ref;
+        // the variant that stops at t >= target (the DDA's tdist += delta consumed up to a time)
+        int s2_ref = 0, s2_new = 0;
+        float t2 = t;
+        while (s2_ref < cap && !(t2 >= target)) { volatile float t1 = t2 + dt; if (!(t1 > t2)) break; t2 = t1; ++s2_ref; }
+        float last = -1.0f, last_ref = -1.0f;
+        { float tt = t; for (int j = 0; j < s2_ref; ++j) { last_ref = tt; volatile float t1 = tt + dt; tt = t1; } }
+        const float r2 = nfb::advance<false>(t, dt, target, cap, s2_new,
+                                             [&](float t0, float q, int k) { last = std::fmaf((float)(k - 1), q, t0); });
+        if (!(r2 == t2 && s2_ref == s2_new && (s2_ref == 0 || last == last_ref))) {
+            printf("MISMATCH (t >= target) case %ld: t=%.9g dt=%.9g target=%.9g cap=%d -> serial (t=%.9g, n=%d, last=%.9g) "
+                   "advance (t=%.9g, n=%d, last=%.9g)\n", c, t, dt, target, cap, t2, s2_ref, last_ref, r2, s2_new, last);
+            return 1;
+        }
     }
     printf("ok %ld %lld\n", cases, total_steps);
     return 0;
