@@ -383,9 +383,10 @@ __device__ __forceinline__ void setup_dda(const float (&o)[3], const float (&d)[
 // cell: the margin dwarfs the slab test's rounding).  All axes stop at the same time, so the state
 // reached is one the serial walk passes through (it takes crossings in time order).  t_first
 // becomes the exit time of the last cell skipped: the t of the empty span that stands for them.
-__device__ __forceinline__ void jump_ahead(const float (&o)[3], const float (&d)[3], const GridSpec& G, int level,
+// Returns true when the segment cannot meet an occupied cell at all.
+__device__ __forceinline__ bool jump_ahead(const float (&o)[3], const float (&d)[3], const GridSpec& G, int level,
                                            float tmin, float tmax, Dda& S, float& t_first) {
-    if (G.bounds == nullptr) return;
+    if (G.bounds == nullptr) return false;
     const float inf = __int_as_float(0x7f800000);
     const float* __restrict__ bb = G.aabbs + 6 * level;
     float t_in = -inf, t_out = inf;
@@ -409,9 +410,9 @@ __device__ __forceinline__ void jump_ahead(const float (&o)[3], const float (&d)
 #pragma unroll
         for (int k = 0; k < 3; ++k)
             if (S.stepi[k] != 0 && S.stop[k] != S.cur[k] + S.stepi[k]) { S.stop[k] = S.cur[k] + S.stepi[k]; S.cm |= 1 << k; }
-        return;
+        return true;
     }
-    if (!(t_in > tmin)) return;  // starts inside the box
+    if (!(t_in > tmin)) return false;  // starts inside the box
     int n[3];
     float tn[3], last = -inf;
 #pragma unroll
@@ -423,16 +424,17 @@ __device__ __forceinline__ void jump_ahead(const float (&o)[3], const float (&d)
         tn[k] = advance<false>(S.tdist[k], S.delta[k], t_in, 0x7fffffff, n[k],
                                [&](float t0, float q, int kk) { lastk = __fmaf_rn((float)(kk - 1), q, t0); });
         const int room = S.stop[k] > S.cur[k] ? S.stop[k] - S.cur[k] : S.cur[k] - S.stop[k];
-        if (n[k] >= room) return;  // would step out of the segment: leave it to the walk
+        if (n[k] >= room) return false;  // would step out of the segment: leave it to the walk
         last = fmaxf(last, lastk);
     }
-    if (!(last > -inf)) return;  // nothing to skip
+    if (!(last > -inf)) return false;  // nothing to skip
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         S.cur[k] += n[k] * S.stepi[k];
         S.tdist[k] = tn[k];
     }
     t_first = fminf(last, tmax);
+    return false;
 }
 
 __device__ __forceinline__ void load_events(const float (&o)[3], const float (&d)[3], long long r,
@@ -632,7 +634,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         Dda S = {};
         float tmin = 0.0f, tmax = 0.0f, t_first = 0.0f;
         int level = 0, si = 0;
-        bool found = false;
+        bool found = false, miss = false;
         if (ok) {
             float o[3], d[3];
 #pragma unroll
@@ -645,7 +647,14 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             if (found) {
                 setup_dda(o, d, G, level, tmin, tmax, S, clip);
                 t_first = tmin;
-                if (clip) jump_ahead(o, d, G, level, tmin, tmax, S, t_first);
+                if (clip) miss = jump_ahead(o, d, G, level, tmin, tmax, S, t_first);
+            }
+            // A ray that cannot yield anything (no segment, or — one level — one that misses the
+            // occupied box) is retired here: no marker in the event queue, no cell walked.
+            if (!found || (miss && m == 1)) {
+                typename Policy::Sink s0 = P.begin(cand);
+                P.end(cand, s0, 0, 0, near);
+                ok = false;
             }
         }
         const unsigned okm = __ballot_sync(kFull, ok);
