@@ -423,7 +423,7 @@ def run_ours(args) -> None:
         roofline = {"kernel": dom, "bound": "hbm", "achieved": kd["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": kd["frac"], "traffic": None, "peak_source": peak_src,
                     "note": ("the dominant kernel is the DDA march: an instruction-issue-bound serial walk per ray "
-                             "(ncu: issue slots ~70 % busy, DRAM <1 %; profiles/r01_h_ncu_step_summary.txt), so its "
+                             "(ncu: issue slots ~65 % busy, DRAM <1 %; profiles/r01_j_ncu_step_summary.txt), so its "
                              "HBM fraction is small by nature; the step's streaming kernels are in `kernels` and "
                              "`hbm_kernels`"),
                     "algorithmic_bytes_per_launch": kd["bytes"], "avg_launch_ms": kd["avg_ms"]}
