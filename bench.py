@@ -262,8 +262,12 @@ def run_ours(args) -> None:
     if world > 1:
         import torch.distributed as dist
 
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+        # Keep stdout to the one JSON line: at debug level VERSION (the default some images set in
+        # /etc/nccl.conf) NCCL printf()s its banner to stdout; at any explicit level its log goes to
+        # the debug file, which we point at stderr unless the caller chose one.
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     n_rays = args.rays
