@@ -252,13 +252,17 @@ def _render_mode(n: int, n_rays: int, packed_info: Tensor) -> str:
 
 
 class RenderComposite(torch.autograd.Function):
-    """rendering() of volrend.py:14-158 for flattened CUDA inputs: one forward and one backward
-    kernel (nfb_render_rays_fwd / nfb_render_rays_bwd, a group of lanes per ray) or, when rays
-    are very long on average, the flat tile kernels — weights forward (nfb_render_weight_fwd),
-    composite forward (nfb_composite_fwd), one backward (nfb_composite_bwd).
+    """rendering() of volrend.py:14-158 for flattened CUDA inputs, one forward and one backward
+    kernel.  Which pair depends on what is known about the layout (`_render_mode`): the streaming
+    warp-tile kernels for dense canonical layouts (nfb_render_bits_fwd / _bwd), a group of lanes
+    per ray for arbitrary chunks (nfb_render_rays_fwd / _bwd), or, for rays of more than 512
+    samples on average, the flat CTA tiles — weights forward (nfb_render_weight_fwd), composite
+    forward (nfb_composite_fwd), one backward (nfb_composite_bwd).
 
-    Returns (colors_sum [R,3], opacity [R,1], depth_sum [R,1], weights, trans, alphas); the
-    depth normalisation and the background blend stay torch ops on [R, .] tensors in volrend.py.
+    Returns (colors_sum [R,3], opacity [R,1], depth [R,1], weights, trans, alphas).  With
+    `norm_depth` depth is sum(w t_mid) / max(opacity, eps) (volrend.py:147-150), formed and
+    differentiated by one launch over the rays each way (nfb_depth_normalize_fwd / _bwd); the
+    background blend stays a torch op on [R, .] tensors in volrend.py.
     """
 
     @staticmethod
