@@ -129,7 +129,7 @@ __device__ __forceinline__ uint32_t end_nibble(const uint32_t* __restrict__ bits
 
 // ---------------------------------------------------------------------------------------------
 // A tile is walked vector by vector (128 items) with the running sums carried in registers, so
-// nothing per-item outlives its vector: few registers (3 CTAs/SM forward), straight-line code
+// nothing per-item outlives its vector: few registers (4 CTAs/SM forward, 3 backward), straight-line code
 // per vector, and the head logic of a vector computed once for all the sums that use it.  A tile
 // with no ray boundary in its first 128 items continues a long ray: it first waits for the
 // running sums its predecessor publishes when it is done (a chain as long as the ray is in
@@ -765,8 +765,8 @@ NFB_API int nfb_render_bits_fwd(int from_density, const float* alphas, const flo
     a.colors = colors; a.opacity = opacity; a.depth = depth;
     a.vec_ok = all_aligned16_rb({alphas, t_starts, t_ends, sigmas, rgbs, weights, trans, alphas_out});
     const unsigned grid = (unsigned)ceil_div<long long>(a.n_tiles, kWarps);
-    if (from_density) render_bits_fwd_stream_kernel<true, 3, false><<<grid, kThreads, 0, s>>>(a);
-    else render_bits_fwd_stream_kernel<false, 3, false><<<grid, kThreads, 0, s>>>(a);
+    if (from_density) render_bits_fwd_stream_kernel<true, 4, false><<<grid, kThreads, 0, s>>>(a);
+    else render_bits_fwd_stream_kernel<false, 4, false><<<grid, kThreads, 0, s>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("render_bits_fwd");
     return NFB_OK;
