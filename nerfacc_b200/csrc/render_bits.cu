@@ -664,7 +664,7 @@ __device__ __forceinline__ void accumulate_stream(const AccBitsArgs& p, const Wa
 }
 
 template <int D, bool HAS_V>
-__global__ void __launch_bounds__(kThreads, 3) accumulate_bits_kernel(const AccBitsArgs p) {
+__global__ void __launch_bounds__(kThreads, 4) accumulate_bits_kernel(const AccBitsArgs p) {
     WarpTile<false> wt;
     if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
     if (!wt.slow) accumulate_stream<D, HAS_V, true>(p, wt);

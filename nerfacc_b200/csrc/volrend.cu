@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(kThreads, 3) weight_fwd_bits_kernel(const Weig
 }
 
 template <bool DENSITY>
-__global__ void __launch_bounds__(kThreads, 2) weight_bwd_bits_kernel(const WeightBwdArgs p) {
+__global__ void __launch_bounds__(kThreads, 3) weight_bwd_bits_kernel(const WeightBwdArgs p) {
     WarpTile<true> wt;
     if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
     float v[kWtNV][4];    // s = (g_T + g_w*a) * T, reverse-exclusive-summed
