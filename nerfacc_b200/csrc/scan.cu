@@ -60,7 +60,7 @@ scan_flat_kernel(const float* __restrict__ in, const float* __restrict__ aux_y,
 // ---------------------------------------------------------------- scans from head bits
 // Same results as scan_flat_kernel, on warp tiles (warp_tile.cuh).
 template <class Op, bool REV, bool EXCL, int MODE>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 6)
 scan_bits_kernel(const float* __restrict__ in, const float* __restrict__ aux_y,
                  const float* __restrict__ aux_x, float* __restrict__ out,
                  const uint32_t* __restrict__ bits, long long n, long long n_wt,
