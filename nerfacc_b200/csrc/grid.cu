@@ -300,16 +300,22 @@ traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info
             // its first one lies in by binary search; samples of rays whose runs are pooled or
             // re-marched lie in no listed run and are left to those passes.
             const long long first = base0 & ~3ll;
-            for (long long i0 = first + 4 * lane; i0 < base0 + span; i0 += 128) {
+            int kbase = 0;  // last run starting at or before the chunk's first sample (warp-uniform)
+            for (long long c0 = first; c0 < base0 + span; c0 += 128) {  // (warp-uniform trip count)
+                const long long i0 = c0 + 4 * lane;
                 const int rel = (int)(i0 - base0);  // >= -3
                 const int e0 = rel < 0 ? 0 : rel;
-                int lo = -1, hi = total;  // last run with start <= e0 (or -1)
-                while (hi - lo > 1) {
-                    const int mid = (lo + hi) >> 1;
-                    if (s_start[w][mid] <= e0) lo = mid;
-                    else hi = mid;
+                // runs are sorted by start: move kbase up to the chunk, 32 candidates at a time;
+                // each lane then walks on from there (a chunk of 128 samples meets a handful of runs)
+                const int cs = (int)(c0 - base0) < 0 ? 0 : (int)(c0 - base0);
+                while (true) {
+                    const int kk = kbase + 1 + lane;
+                    const unsigned m = __ballot_sync(kFull, kk < total && s_start[w][kk] <= cs);
+                    kbase += __popc(m);
+                    if (m != kFull) break;
                 }
-                int k = lo;
+                int k = s_start[w][kbase] <= e0 ? kbase : -1;
+                if (i0 >= base0 + span) continue;
                 long long ri[4];
                 float ts[4], te[4];
                 unsigned ok = 0u;
