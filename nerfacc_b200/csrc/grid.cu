@@ -758,7 +758,7 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
         const Run* runs = static_cast<const Run*>(run_buf);
         n_runs = reinterpret_cast<const int*>(runs + rays->n_rays * kRunSlots);
         const long long groups = (rays->n_rays + 31) / 32;
-        traverse_expand_kernel<<<grid_for(groups, kExpandWarps, 8), kExpandWarps * 32, 0, s>>>(
+        traverse_expand_kernel<<<grid_for(groups, kExpandWarps, 32), kExpandWarps * 32, 0, s>>>(
             rays->n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends,
             aligned16(ray_indices) && aligned16(t_starts) && aligned16(t_ends));
         count_launch();
