@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(kPdfWarps * 32) searchsorted_kernel(const Sear
 
 static inline unsigned pdf_blocks(long long n_rays) {
     long long b = ceil_div<long long>(n_rays, kPdfWarps);
-    const long long cap = (long long)sm_count() * 8;
+    const long long cap = (long long)sm_count() * 32;
     if (b > cap) b = cap;
     if (b < 1) b = 1;
     return (unsigned)b;
@@ -308,7 +308,9 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
             t.bin_slopes = (n_in - 1 <= 32) && (2 * (n_in - 1) <= n_out);
             const size_t smem = (size_t)(per_ray * rt + fixed) * 4;
             long long blocks = ceil_div<long long>(n_rays, rt);
-            const long long cap = (long long)sm_count() * 8;
+            // one CTA per tile of rays (measured: a persistent grid of 8 CTAs per SM leaves a tail
+            // and keeps the load and compute phases of neighbouring tiles from overlapping)
+            const long long cap = (long long)sm_count() * 4096;
             if (blocks > cap) blocks = cap;
             importance_sampling_tile_kernel<<<(unsigned)blocks, kPdfWarps * 32, smem, st>>>(t);
             count_launch();
