@@ -343,3 +343,33 @@ def test_rendering_fused_composite_vs_oracle(device, mode, path, monkeypatch):
     # (bits_odd has 1-2 sample rays of tiny opacity: depth = d0 / o0 makes the per-ray gradient rows
     # themselves — torch on the GPU vs numpy here — differ by a few 1e-4 relative after cancellation)
     assert_close(f_t.grad.cpu().numpy(), g_f, 1e-4, (2e-5 if path == "bits_odd" else 2e-6) * scale, "g_field")
+
+
+def test_depth_normalize_matches_torch(device):
+    """nfb_depth_normalize_fwd / _bwd against torch's own depth / opacity.clamp_min(eps) and its
+    autograd (volrend.py:147-150), incl. rays of zero and sub-eps opacity."""
+    from nerfacc_b200 import _C
+
+    R = 10007
+    g = torch.Generator(device=device); g.manual_seed(3)
+    op = torch.rand(R, 1, device=device, generator=g)
+    op[::13] = 0.0
+    op[5::17] = 3e-8
+    d0 = torch.rand(R, 1, device=device, generator=g) * 4
+    g_op = torch.randn(R, 1, device=device, generator=g)
+    g_dp = torch.randn(R, 1, device=device, generator=g)
+    eps = torch.finfo(torch.float32).eps
+    o_t, d_t = op.clone().requires_grad_(True), d0.clone().requires_grad_(True)
+    ref = d_t / o_t.clamp_min(eps)
+    torch.autograd.backward([ref, o_t * 1.0], [g_dp, g_op])
+    depth = d0.clone()
+    lib = _C.lib()
+    with torch.cuda.device(device):
+        _C.check(lib.nfb_depth_normalize_fwd(op.data_ptr(), depth.data_ptr(), R, _C.stream_ptr(device)), "fwd")
+        g_o0, g_d0 = torch.empty_like(op), torch.empty_like(op)
+        _C.check(lib.nfb_depth_normalize_bwd(g_op.data_ptr(), g_dp.data_ptr(), op.data_ptr(), depth.data_ptr(), R,
+                                             g_o0.data_ptr(), g_d0.data_ptr(), _C.stream_ptr(device)), "bwd")
+    assert torch.equal(depth, ref.detach())
+    assert_close(g_d0.cpu().numpy(), d_t.grad.cpu().numpy(), 1e-6, 0.0, "g_depth_sum")
+    scale = float(o_t.grad.abs().max())
+    assert_close(g_o0.cpu().numpy(), o_t.grad.cpu().numpy(), 1e-5, 1e-7 * scale, "g_opacity_sum")
