@@ -195,6 +195,9 @@ def run_reference(args) -> None:
         return
     n_rays = args.cpu_rays
     r = time_cpu(n_rays, args.steps, args.warmup)
+    import bench_configs as BC
+
+    cfg1 = BC.cpu_cfg1()
     sample = (f"{n_rays} rays/step of the same scene ({r['samples_per_step']} samples/step), "
               f"{args.steps} steps after {args.warmup} warm-up, {r['cores']} OpenMP threads")
     line = {
@@ -203,7 +206,7 @@ def run_reference(args) -> None:
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": {"workload": workload_name(1 << 20), "cpu_sample_rays": n_rays},
         "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-                         "sample": sample},
+                         "sample": sample, "cfg1": cfg1},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -244,9 +247,41 @@ def aggregate_over_ranks(ms_local: float, units_local: int, dist, device):
     return float(t.item()), int(u.item())
 
 
+def pin_rank_to_local_cores(local_rank: int, world: int) -> dict:
+    """N > 1: give every rank its own slice of the cores NVML calls local to its GPU, BEFORE any
+    pinned host buffer is allocated (first touch then places it on that NUMA node).  torchrun
+    leaves all ranks floating over all cores, so 8 ranks migrate and their pinned memory lands
+    wherever the allocating thread happened to run."""
+    info = {"cpus": None}
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        n_dev = pynvml.nvmlDeviceGetCount()
+        words = (os.cpu_count() + 63) // 64
+
+        def mask_of(i):
+            m = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(i), words)
+            return tuple(int(x) for x in m)
+
+        mine = mask_of(local_rank)
+        allowed = sorted(os.sched_getaffinity(0))
+        local = [c for c in allowed if (mine[c // 64] >> (c % 64)) & 1] or allowed
+        peers = [i for i in range(min(world, n_dev)) if mask_of(i) == mine]
+        k, j = len(peers), peers.index(local_rank) if local_rank in peers else 0
+        per = max(len(local) // max(k, 1), 1)
+        cpus = local[j * per:(j + 1) * per] or local
+        os.sched_setaffinity(0, set(cpus))
+        info = {"cpus": f"{cpus[0]}-{cpus[-1]}", "n": len(cpus), "gpu_local_cpus": len(local), "ranks_sharing": k}
+    except Exception as e:  # no NVML / restricted container: leave the scheduler alone
+        info["error"] = repr(e)[:120]
+    return info
+
+
 def run_ours(args) -> None:
     import torch
 
+    import bench_configs as BC
     import nerfacc_b200 as nf
     from nerfacc_b200 import _C
 
@@ -256,6 +291,7 @@ def run_ours(args) -> None:
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); "
                          "use --impl reference for the CPU port")
+    affinity = pin_rank_to_local_cores(local_rank, world) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     dist = None
@@ -270,14 +306,44 @@ def run_ours(args) -> None:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+
     n_rays = args.rays
     bins = make_grid()
     o_np, d_np = make_rays(n_rays, 1234 + rank)
     est = nf.OccGridEstimator(AABB.tolist(), resolution=RES, levels=1).to(dev)
     est.binaries = torch.from_numpy(bins).to(dev)
+    est.occs = est.binaries.flatten().float()  # the grid a converged trainer would hold
+    est.train()
+    if world > 1:
+        est.shard_updates(None, seed=7)  # opt in: evaluations split over ranks, occs MAX-all-reduced
     o_host = torch.from_numpy(o_np).pin_memory()
     d_host = torch.from_numpy(d_np).pin_memory()
     o_dev, d_dev = o_host.to(dev), d_host.to(dev)
+
+    # occ_eval_fn of the in-loop update_every_n_steps (examples/train_ngp_nerf_occ.py:163-173 calls
+    # it with the field's density * step): constant per cell = the scene the grid was made from,
+    # 0 within 1e-3 of a cell face so that rounding in position -> cell can never light a neighbour.
+    # The update therefore reproduces `binaries` exactly and S stays the same every step.
+    shell_flat = est.binaries.flatten()
+    a_lo = torch.tensor(AABB[:3], device=dev)
+    a_sz = torch.tensor(AABB[3:] - AABB[:3], device=dev)
+
+    def occ_eval_fn(x):
+        g = (x - a_lo) / a_sz * RES
+        idx = g.floor().clamp_(0, RES - 1)
+        frac = g - idx
+        inside = ((frac > 1e-3) & (frac < 1.0 - 1e-3)).all(-1)
+        idx = idx.long()
+        cell = (idx[:, 0] * RES + idx[:, 1]) * RES + idx[:, 2]
+        return (shell_flat[cell] & inside).float()[:, None]
 
     ri, ts, te = est.sampling(o_dev, d_dev, render_step_size=STEP_SIZE)
     S = int(ri.shape[0])
@@ -289,11 +355,35 @@ def run_ours(args) -> None:
     g_d = torch.rand((n_rays, 1), device=dev, generator=gen)
     del ri, ts, te
 
+    # ---- outside the timed region: parity of this very step at its full size
+    parity = None
+    if rank == 0 and not args.no_parity:
+        parity = BC.preflight_parity(nf, est, o_dev, d_dev, STEP_SIZE, sigmas, rgbs, g_c, g_o, g_d)
+        torch.cuda.empty_cache()
+        if parity.get("status") == "FAILED":
+            print(json.dumps({"parity": parity}), file=sys.stderr, flush=True)
+            raise SystemExit("bench.py: the step's outputs differ from the reference CUDA kernels")
+    # ---- N > 1: the path's one collective (BASELINE cfg4), checked bit for bit on NCCL
+    update = None
+    if world > 1:
+        update = BC.cfg4_sharded_update_check(nf, dev, dist, rank, world)
+        torch.cuda.empty_cache()
+        if update["parity"] != "bit-exact":
+            raise SystemExit(f"bench.py: sharded update_every_n_steps differs from the un-sharded update: {update}")
+
     def field(t_starts, t_ends, ray_indices):
         assert t_starts.shape[0] == S
         return rgbs, sigmas
 
+    state = {"step": 0}
+    UPDATE_EVERY = 16
+
     def step(o, d):
+        # one training step as examples/train_ngp_nerf_occ.py:160-200 orders it: grid update (every
+        # 16th step; with N > 1 it carries the MAX all-reduce), march, render, backward
+        if not args.no_update:
+            est.update_every_n_steps(state["step"], occ_eval_fn, occ_thre=1e-2, n=UPDATE_EVERY)
+        state["step"] += 1
         sigmas.grad = None
         rgbs.grad = None
         ri, ts, te = est.sampling(o, d, render_step_size=STEP_SIZE)
@@ -323,16 +413,23 @@ def run_ours(args) -> None:
             s_cuts.append(s_cuts[-1] + int(ri_i.shape[0]))
             del ri_i
     assert s_cuts[-1] == S, "chunked marching must give the same samples"
-    for i in range(n_chunks):
-        sig_c.append(sigmas.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
-        rgb_c.append(rgbs.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
+    if n_chunks == 1:
+        sig_c, rgb_c = [sigmas], [rgbs]
+    else:
+        for i in range(n_chunks):
+            sig_c.append(sigmas.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
+            rgb_c.append(rgbs.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
 
     def step_e2e():
         # Steps are not drained one by one (a training loop is not either): the timed region ends
-        # with a device-wide synchronize, every step's copies in and out lie inside it.
+        # after the main stream has waited for both copy streams, every step's copies in and out
+        # lie inside it.
         main = torch.cuda.current_stream(dev)
         p = e2e_state["k"] & 1
         e2e_state["k"] += 1
+        if not args.no_update:
+            est.update_every_n_steps(state["step"], occ_eval_fn, occ_thre=1e-2, n=UPDATE_EVERY)
+        state["step"] += 1
         if buf_free[p] is not None:
             s_in.wait_event(buf_free[p])
         ready = []
@@ -371,50 +468,95 @@ def run_ours(args) -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, k):
+    def timed(fn, k, first_step, join=()):
+        """k calls of fn, device-timed between two events on the main stream; `join`: streams the
+        main stream waits for before the closing event, so their work lies inside the interval."""
         barrier()
+        state["step"] = first_step
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(k):
             fn()
+        main = torch.cuda.current_stream(dev)
+        for st in join:
+            main.wait_stream(st)
         e1.record()
         barrier()
-        return aggregate_over_ranks(e0.elapsed_time(e1), 0, dist, dev)[0]
+        return e0.elapsed_time(e1)
 
+    # Steps are numbered like a trainer's: the timed region starts at step 256 (the first
+    # steady-state update of the occupancy grid; updates at 256, 272, ...: K/16 rounded up).
+    FIRST = 256
+    state["step"] = FIRST - max(args.warmup, 3)
     for _ in range(max(args.warmup, 3)):
         step(o_dev, d_dev)
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
-    _C.prof_enable(True)
     launches0 = _C.launch_count()
-    ms = timed(lambda: step(o_dev, d_dev), args.steps)
+    ms_local = timed(lambda: step(o_dev, d_dev), args.steps, FIRST)
     launches = _C.launch_count() - launches0
+    ms = aggregate_over_ranks(ms_local, 0, dist, dev)[0]
+    # second pass, not part of `value`: the same steps with CUDA events around every C-ABI call
+    _C.prof_enable(True)
+    ms_prof = timed(lambda: step(o_dev, d_dev), args.steps, FIRST)
     prof = _C.prof_collect()
     _C.prof_enable(False)
     for _ in range(2):
         step_e2e()
-    ms_e2e = timed(step_e2e, args.steps)
+    ms_e2e_local = timed(step_e2e, args.steps, FIRST, join=(s_out, s_in))
+    ms_e2e = aggregate_over_ranks(ms_e2e_local, 0, dist, dev)[0]
     clk = clocks.stop() if rank == 0 else None
+
+    # the update alone (steady state), for the record
+    upd_ms = None
+    if not args.no_update:
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for j in range(4):
+            est.update_every_n_steps(512 + 16 * j, occ_eval_fn, occ_thre=1e-2, n=UPDATE_EVERY)
+        e1.record()
+        torch.cuda.synchronize()
+        upd_ms = aggregate_over_ranks(e0.elapsed_time(e1) / 4, 0, dist, dev)[0]
+        assert int(est.sampling(o_dev, d_dev, render_step_size=STEP_SIZE)[0].shape[0]) == S
+
+    # per-rank copy times under contention (all ranks copy at once), to name the e2e limiter
+    per_rank = None
+    if dist is not None:
+        def copy_ms(fn, reps=5):
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b) / reps
+
+        h2d = copy_ms(lambda: (o_buf[0][0].copy_(o_host[cuts[0]:cuts[1]], non_blocking=True),
+                               d_buf[0][0].copy_(d_host[cuts[0]:cuts[1]], non_blocking=True)))
+        c_dev, o1_dev = torch.empty((n_rays, 3), device=dev), torch.empty((n_rays, 1), device=dev)
+        d2h = copy_ms(lambda: (host_c.copy_(c_dev, non_blocking=True), host_o.copy_(o1_dev, non_blocking=True),
+                               host_d.copy_(o1_dev, non_blocking=True)))
+        mine = torch.tensor([ms_local / args.steps, ms_e2e_local / args.steps, h2d, d2h], device=dev,
+                            dtype=torch.float64)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [{"rank": r, "device_ms_per_step": float(t[0]), "e2e_ms_per_step": float(t[1]),
+                     "h2d_ms": float(t[2]), "d2h_ms": float(t[3])} for r, t in enumerate(allr)]
 
     S_all = aggregate_over_ranks(0.0, S, dist, dev)[1]
     value = S_all * args.steps / (ms * 1e-3) / 1e9
     e2e_value = S_all * args.steps / (ms_e2e * 1e-3) / 1e9
 
-    # per-entry-point live timings -> roofline of the dominant kernel
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    # per-entry-point live timings (second pass) -> roofline of the dominant kernel
     B = (bins.size + 7) // 8
     kernels = {}
     for name, (cnt, tot_ms) in prof.items():
         avg = tot_ms / max(cnt, 1)
-        ent = {"launches_per_step": cnt / args.steps, "avg_ms": avg, "share_of_step": tot_ms / ms}
+        ent = {"launches_per_step": cnt / args.steps, "avg_ms": avg, "share_of_step": tot_ms / ms_prof}
         if name in ALGO_BYTES:
             by = ALGO_BYTES[name](S, n_rays, B)
             ent.update(bytes=by, gbs=by / (avg * 1e-3) / 1e9, frac=by / (avg * 1e-3) / 1e9 / peak)
@@ -426,16 +568,30 @@ def run_ours(args) -> None:
         kd = kernels[dom]
         roofline = {"kernel": dom, "bound": "hbm", "achieved": kd["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": kd["frac"], "traffic": None, "peak_source": peak_src,
-                    "note": ("the dominant kernel is the DDA march: an instruction-issue-bound serial walk per ray "
-                             "(ncu: issue slots ~65 % busy, DRAM <1 %; profiles/r01_j_ncu_step_summary.txt), so its "
-                             "HBM fraction is small by nature; the step's streaming kernels are in `kernels` and "
-                             "`hbm_kernels`"),
-                    "algorithmic_bytes_per_launch": kd["bytes"], "avg_launch_ms": kd["avg_ms"]}
+                    "algorithmic_bytes_per_launch": kd["bytes"], "avg_launch_ms": kd["avg_ms"],
+                    "timed": "second pass of the same K steps with CUDA events around each C-ABI call "
+                             f"({ms_prof / args.steps:.3f} ms/step with the events, {ms / args.steps:.3f} without)"}
+        if dom == "traverse_count":
+            roofline["note"] = ("the dominant kernel is the DDA march: an instruction-issue-bound serial walk per "
+                                "ray whose own bytes are the rays in and 16 B/ray out, so its HBM fraction is small "
+                                "by nature; `traversal` scores count + fill against the sampling output stream as "
+                                "SURVEY 8(d) does, `step_roofline` the whole step against 120 B/sample")
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 roofline["traffic"] = json.load(f).get(dom)
         except Exception:
             pass
+    traversal = None
+    if "traverse_count" in kernels and "traverse_fill_sampling" in kernels:
+        t_ms = kernels["traverse_count"]["avg_ms"] + kernels["traverse_fill_sampling"]["avg_ms"]
+        by = 16 * S + 48 * n_rays + B
+        traversal = {"kernels": ["traverse_count", "traverse_fill_sampling"], "bytes": by, "ms": t_ms,
+                     "achieved": by / (t_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": by / (t_ms * 1e-3) / 1e9 / peak}
+    step_roofline = {"bytes_per_step": 120 * S, "ms_per_step": ms / args.steps,
+                     "achieved": 120 * S / (ms / args.steps * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": 120 * S / (ms / args.steps * 1e-3) / 1e9 / peak,
+                     "note": "SURVEY 8(d): 16 S march + 44 S forward + 60 S backward"}
 
     # time-weighted HBM fraction of the step's streaming (HBM-bound) kernels, the march aside
     stream_names = [k for k in kernels if "bytes" in kernels[k] and k != "traverse_count"]
@@ -450,12 +606,28 @@ def run_ours(args) -> None:
         if dist is not None:
             dist.destroy_process_group()
         return
+    # ---- the other BASELINE configs, each next to the reference's own CUDA kernels (N = 1 only)
+    configs = None
+    if world == 1 and not args.no_configs:
+        del sigmas, rgbs, g_c, g_o, g_d, sig_c, rgb_c, o_buf, d_buf
+        torch.cuda.empty_cache()
+        R = BC.refcuda()
+        configs = {"method": "CUDA events, 3 warm-ups, median of 5 groups of 5 back-to-back calls; "
+                             "ref_cuda_ms = the unmodified reference extension (oracle/_ref) on the same tensors",
+                   "ref_cuda": R is not None}
+        for name, fn in (("cfg3", BC.bench_cfg3), ("cfg4", BC.bench_cfg4), ("cfg5", BC.bench_cfg5)):
+            try:
+                configs[name] = fn(nf, dev, peak, R)
+            except Exception as e:  # a side leg must not cost the headline line
+                configs[name] = {"error": repr(e)[:300]}
+            torch.cuda.empty_cache()
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        r = time_cpu(args.cpu_rays, 3, 1)
+        r = time_cpu(args.cpu_rays, args.cpu_steps, 1)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                "sample": f"{args.cpu_rays} rays/step of the same scene ({r['samples_per_step']} samples/step), "
-                         f"3 steps after 1 warm-up, {r['seconds']:.1f} s"}
+                         f"{args.cpu_steps} steps after 1 warm-up, {r['seconds']:.1f} s",
+               "cfg1": BC.cpu_cfg1()}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -463,15 +635,25 @@ def run_ours(args) -> None:
         "config": {"workload": workload_name(n_rays), "rays_per_gpu": n_rays, "samples_per_gpu": S,
                    "samples_per_ray": S / n_rays, "l2": "inputs larger than L2 (sample stream "
                    f"{S * 16 / 1e6:.0f} MB march output, {S * 44 / 1e6:.0f} MB render inputs/outputs)",
-                   "parallelism": f"rays sharded x{world}, grid replicated, no data-path collective"},
+                   "parallelism": (f"rays sharded x{world}, grid replicated; update_every_n_steps(n=16) in the loop"
+                                   + (", its occ_eval_fn evaluations sharded and occs MAX-all-reduced over NCCL"
+                                      if world > 1 else "")),
+                   "update_in_loop": (None if args.no_update else
+                                      {"every": UPDATE_EVERY, "first_timed_step": FIRST, "steady_state_ms": upd_ms,
+                                       "updates_in_timed_region": len([k for k in range(FIRST, FIRST + args.steps)
+                                                                       if k % UPDATE_EVERY == 0])})},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": 2 * n_rays * 12 * world, "d2h_bytes_per_step": n_rays * 20 * world,
                 "pipeline": f"{n_chunks} ray blocks/step through OccGridEstimator.sampling + rendering + backward; "
                             "pinned-host rays in, colours/opacity/depth out to pinned host, every step; "
                             "H2D / compute / D2H on three streams, the next step's rays copied in while this "
-                            "step computes (two device ray buffers), results copied out while the backward runs"},
+                            "step computes (two device ray buffers), results copied out while the backward runs; "
+                            "the closing event waits for both copy streams",
+                "per_rank": per_rank, "cpu_affinity": affinity},
         "gpu_launches": launches,
-        "roofline": roofline, "hbm_kernels": hbm_kernels, "kernels": kernels, "cpu_baseline": cpu, "clocks": clk,
+        "roofline": roofline, "traversal": traversal, "step_roofline": step_roofline, "hbm_kernels": hbm_kernels,
+        "kernels": kernels, "parity": parity, "update": update, "configs": configs, "cpu_baseline": cpu,
+        "clocks": clk,
     }
     print(json.dumps(line), flush=True)
     if dist is not None:
@@ -486,7 +668,11 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU")
     ap.add_argument("--cpu-rays", type=int, default=1 << 20, help="rays per step of the CPU sample")
+    ap.add_argument("--cpu-steps", type=int, default=8, help="timed steps of the CPU sample (about 2 s each)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the pre-flight parity check")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg3/cfg4/cfg5 side legs")
+    ap.add_argument("--no-update", action="store_true", help="leave update_every_n_steps out of the step")
     ap.add_argument("--e2e-chunks", type=int, default=1,
                     help="ray blocks per step of the end-to-end leg (copies overlap compute across blocks)")
     args = ap.parse_args()

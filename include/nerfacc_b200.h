@@ -337,6 +337,24 @@ NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
                                 int64_t* out_ray_indices, float* out_t_starts, float* out_t_ends,
                                 int64_t* total, void* workspace, size_t workspace_bytes,
                                 nfb_stream_t stream);
+/* The whole "skip invisible space" step of OccGridEstimator.sampling
+ * (nerfacc/estimators/occ_grid.py:186-220: render_visibility_from_{alpha,density} -> bool mask ->
+ * ray_indices[mask], t_starts[mask], t_ends[mask]; nerfacc/volrend.py:365-480) in ONE pass over the
+ * samples: T by the segmented scan of nfb_render_weight_fwd, vis = T >= early_stop_eps
+ * [& alpha >= alpha_thre if alpha_thre > 0], survivors ranked in the tile, global offset by
+ * decoupled look-back, (ray_indices, t_starts, t_ends) written compacted in order; *total
+ * (device-visible) = how many.  `packed_info` must be canonical and dense over the n samples
+ * (what sampling / traverse_grids / pack_info produce).  Optional outputs: out_packed_info
+ * [n_rays,2] = pack_info of the survivors (what nerfacc/pack.py:38-46 would compute from
+ * out_ray_indices); vis [n] = the mask itself.  workspace: nfb_workspace_bytes(n). */
+NFB_API int nfb_visibility_compact(int from_density, const float* alphas, const float* t_starts,
+                                   const float* t_ends, const float* sigmas, const float* prefix_trans,
+                                   const int64_t* packed_info, int64_t n_rays, int64_t n,
+                                   const int64_t* ray_indices, float early_stop_eps, float alpha_thre,
+                                   int64_t* out_ray_indices, float* out_t_starts, float* out_t_ends,
+                                   int64_t* out_packed_info, uint8_t* vis, int64_t* total,
+                                   void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                   nfb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * nerfacc.rendering() for packed rays in one forward and one backward kernel (a group of

@@ -113,6 +113,8 @@ _PROTOS = {
     "nfb_compact_workspace_bytes": [c_i64],
     "nfb_compact_samples": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                             c_size, c_ptr],
+    "nfb_visibility_compact": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_f32, c_f32,
+                               c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_u32, c_ptr],
     "nfb_importance_sampling": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr,
                                 c_ptr, c_ptr, c_ptr, c_ptr],
     "nfb_searchsorted": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],

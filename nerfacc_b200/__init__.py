@@ -19,3 +19,30 @@ from .volrend import (
     render_weight_from_density,
     rendering,
 )
+
+# the 22 public names of the reference (nerfacc/__init__.py:23-46): `from nerfacc import *` works
+# the same when this package is imported under the alias `nerfacc`
+__all__ = [
+    "__version__",
+    "inclusive_prod",
+    "exclusive_prod",
+    "inclusive_sum",
+    "exclusive_sum",
+    "pack_info",
+    "render_visibility_from_alpha",
+    "render_visibility_from_density",
+    "render_weight_from_alpha",
+    "render_weight_from_density",
+    "render_transmittance_from_alpha",
+    "render_transmittance_from_density",
+    "accumulate_along_rays",
+    "rendering",
+    "importance_sampling",
+    "searchsorted",
+    "RayIntervals",
+    "RaySamples",
+    "ray_aabb_intersect",
+    "traverse_grids",
+    "OccGridEstimator",
+    "PropNetEstimator",
+]

@@ -71,6 +71,21 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if nvcc is None:
         raise RuntimeError("nvcc not found: cannot build libnerfacc_b200.so")
     os.makedirs(OBJ_DIR, exist_ok=True)
+    # N torchrun ranks may get here together with a stale library: one builds, the rest wait and
+    # find it up to date; the .so appears under its final name only when complete (os.replace)
+    import fcntl
+
+    with open(os.path.join(OBJ_DIR, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and up_to_date():
+                return LIB
+            return _build_locked(nvcc, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(nvcc: str, verbose: bool) -> str:
     srcs = sources()
 
     def compile_one(src: str) -> str:
@@ -87,12 +102,17 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(compile_one, srcs))
-    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-lcudart_static", "-Xcompiler", "-fPIC"]
+    tmp = LIB + f".tmp{os.getpid()}"
+    cmd = [nvcc, "-shared", "-o", tmp, *objs, "-lcudart_static", "-Xcompiler", "-fPIC"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    with open(STAMP, "w") as f:
+    if os.path.exists(STAMP):
+        os.remove(STAMP)  # never a stamp that vouches for a library it does not belong to
+    os.replace(tmp, LIB)
+    with open(STAMP + ".tmp", "w") as f:
         f.write(digest())
+    os.replace(STAMP + ".tmp", STAMP)
     return LIB
 
 

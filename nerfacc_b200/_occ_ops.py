@@ -13,12 +13,13 @@ from ._grid_ops import _pinned_totals
 from .pack import pack_info
 
 
-def dist_info() -> Tuple[int, int]:
-    """(world_size, rank) of the default process group, (1, 0) when not distributed."""
+def dist_info(group=None) -> Tuple[int, int]:
+    """(world_size, rank) within `group` (None = the default process group); (1, 0) when
+    torch.distributed is not initialised."""
     import torch.distributed as dist
 
     if dist.is_available() and dist.is_initialized():
-        return dist.get_world_size(), dist.get_rank()
+        return dist.get_world_size(group), dist.get_rank(group)
     return 1, 0
 
 
@@ -29,12 +30,12 @@ def shard_range(n: int, world: int, rank: int) -> Tuple[int, int]:
     return lo, min(lo + per, n)
 
 
-def all_reduce_max(occs: Tensor) -> None:
+def all_reduce_max(occs: Tensor, group=None) -> None:
     """The only collective on the path: every rank decayed the same cells and
     max-ed in its own shard of evaluations; MAX across ranks completes the scatter-max."""
     import torch.distributed as dist
 
-    dist.all_reduce(occs, op=dist.ReduceOp.MAX)
+    dist.all_reduce(occs, op=dist.ReduceOp.MAX, group=group)
 
 
 def cell_points(cells: Tensor, u: Tensor, resolution: Tensor, aabb: Tensor) -> Tensor:
@@ -105,3 +106,37 @@ def compact_samples(masks: Tensor, ray_indices: Tensor, t_starts: Tensor, t_ends
         torch.cuda.current_stream(dev).synchronize()
     k = int(totals[0])
     return o_ray[:k], o_ts[:k], o_te[:k]
+
+
+def visibility_compact(from_density: bool, values: Tensor, t_starts: Tensor, t_ends: Tensor,
+                       packed_info: Tensor, ray_indices: Tensor, early_stop_eps: float, alpha_thre: float,
+                       want_mask: bool = False):
+    """render_visibility_from_{density,alpha} + the three boolean selects of occ_grid.py:186-220
+    + pack_info of the survivors, as one kernel and one host sync.  `values` = sigmas (density
+    mode) or alphas; `packed_info` must be canonical and dense over the samples.
+    Returns (ray_indices', t_starts', t_ends', packed_info', mask or None)."""
+    n = values.numel()
+    n_rays = packed_info.shape[0]
+    dev = _C.require_cuda(values, t_starts, t_ends, packed_info, ray_indices)
+    if n == 0:
+        return ray_indices, t_starts, t_ends, packed_info, (torch.zeros(0, dtype=torch.bool, device=dev) if want_mask else None)
+    f32 = lambda t: t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+    values, t_starts, t_ends = f32(values), f32(t_starts), f32(t_ends)
+    ray_indices = ray_indices.contiguous()
+    assert ray_indices.dtype == torch.long and ray_indices.shape == values.shape == t_starts.shape == t_ends.shape
+    o_ray, o_ts, o_te = torch.empty_like(ray_indices), torch.empty_like(t_starts), torch.empty_like(t_ends)
+    o_pi = torch.empty_like(packed_info)
+    mask = torch.empty(values.shape, dtype=torch.bool, device=dev) if want_mask else None
+    totals = _pinned_totals(dev)
+    with torch.cuda.device(dev):
+        ws, ws_bytes, epoch = _C.workspace(dev, n)
+        rc = _C.lib().nfb_visibility_compact(
+            int(from_density), None if from_density else values.data_ptr(), t_starts.data_ptr(),
+            t_ends.data_ptr(), values.data_ptr() if from_density else None, None, packed_info.data_ptr(),
+            n_rays, n, ray_indices.data_ptr(), float(early_stop_eps), float(alpha_thre), o_ray.data_ptr(),
+            o_ts.data_ptr(), o_te.data_ptr(), o_pi.data_ptr(), None if mask is None else mask.data_ptr(),
+            totals.data_ptr(), ws.data_ptr(), ws_bytes, epoch, _C.stream_ptr(dev))
+        _C.check(rc, "visibility_compact")
+        torch.cuda.current_stream(dev).synchronize()
+    k = int(totals[0])
+    return o_ray[:k], o_ts[:k], o_te[:k], o_pi, mask

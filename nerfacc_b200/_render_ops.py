@@ -322,6 +322,9 @@ class RenderComposite(torch.autograd.Function):
                 _C.check(rc, "composite_fwd")
         ctx.per_ray = per_ray
         ctx.mode = mode
+        # the head bits travel with the node: the identity-keyed cache misses when saved-tensor
+        # hooks (save_on_cpu, checkpoint wrappers) hand the backward a different packed_info object
+        ctx.bits = bits if mode == "bits" else None
         ctx.set_materialize_grads(False)
         ctx.from_density = from_density
         ctx.n_rays = n_rays
@@ -362,7 +365,7 @@ class RenderComposite(torch.autograd.Function):
             fd = ctx.from_density
             with torch.cuda.device(dev):
                 if ctx.mode == "bits":
-                    bits = head_bits(packed_info, n)
+                    bits = ctx.bits
                     ws, ws_bytes, epoch = _C.workspace(dev, n)
                     rc = _C.lib().nfb_render_bits_bwd(
                         int(fd), _p(_cg(g_colors)), _p(_cg(g_opacity)), _p(_cg(g_depth)), _p(_cg(g_weights)),

@@ -111,6 +111,203 @@ __global__ void __launch_bounds__(kThreads) weight_fwd_kernel(const WeightFwdArg
     }
 }
 
+// ---------------------------------------------------------------- visibility -> compaction
+// One pass for what OccGridEstimator.sampling does after the user's sigma_fn / alpha_fn
+// (nerfacc/estimators/occ_grid.py:186-220: render_visibility_* -> a bool mask -> three boolean
+// selects -> later a pack_info over the survivors): the tile computes T with the same segmented
+// scan as weight_fwd_kernel, thresholds, ranks the survivors inside the tile with ballots, gets
+// its global offset by a second decoupled look-back (integer counts, status slot 1), and writes
+// (ray_indices, t_starts, t_ends) compacted.  The survivors' packed_info comes from the same
+// ranks: new_start[r] = rank of the item at old_start[r] (also right for empty rays, whose start
+// is the next ray's); pi_counts_kernel then turns neighbouring starts into counts.
+struct VisCompactArgs {
+    WeightFwdArgs w;
+    const int64_t* ray_indices;
+    const float* t_starts;  // (== w.t_starts in density mode)
+    const float* t_ends;
+    int64_t* o_ray;
+    float* o_ts;
+    float* o_te;
+    int64_t* o_packed_info;  // optional [n_rays, 2]
+    long long* total;        // device-visible survivor count
+};
+
+__device__ __forceinline__ unsigned long long pack_count(uint32_t v, uint32_t epoch, uint32_t state) {
+    return ((unsigned long long)((epoch << 2) | state) << 32) | (unsigned long long)v;
+}
+
+// Survivors before `tile`: walk back to the nearest tile that has published its inclusive prefix.
+__device__ __forceinline__ long long lookback_count(unsigned long long* st, int slot, long long tile,
+                                                    uint32_t epoch) {
+    long long acc = 0;
+    long long k = tile - 1;
+    while (true) {
+        const unsigned long long w = ld_relaxed_u64(st + k * kStatusPerTile + slot);
+        const uint32_t meta = (uint32_t)(w >> 32);
+        if ((meta >> 2) != epoch || (meta & 3u) == 0u) { __nanosleep(40); continue; }
+        acc += (long long)(uint32_t)w;
+        if ((meta & 3u) == 2u) break;
+        --k;  // tile 0 always publishes state 2
+    }
+    return acc;
+}
+
+template <bool DENSITY>
+__global__ void __launch_bounds__(kThreads) vis_compact_kernel(const VisCompactArgs q) {
+    const WeightFwdArgs& p = q.w;
+    __shared__ TileSmem sm;
+    __shared__ uint32_t s_mask[kWarps][kVec][4];  // survivors of (warp, vector, component) by lane
+    __shared__ int s_vbase[kWarps][kVec];         // survivors of the tile before vector (w, k)
+    __shared__ int s_wtot[kWarps];
+    __shared__ long long s_tile_base;
+    const TileGeom<false> g(p.n, p.n_tiles);
+    const int lane = lane_id(), w = warp_id();
+    float v[kVec][4], al[kVec][4];
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        if (DENSITY) {
+            float ts[4], te[4], s[4];
+            g.load(p.t_starts, p.vec_ok, k, 0.0f, ts);
+            g.load(p.t_ends, p.vec_ok, k, 0.0f, te);
+            g.load(p.sigmas, p.vec_ok, k, 0.0f, s);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                v[k][c] = __fmul_rn(s[c], __fsub_rn(te[c], ts[c]));
+                al[k][c] = __fsub_rn(1.0f, expf(-v[k][c]));
+            }
+        } else {
+            g.load(p.alphas, p.vec_ok, k, 0.0f, al[k]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) v[k][c] = __fsub_rn(1.0f, al[k][c]);
+        }
+    }
+    scatter_heads<false>(p.seg, g.base, p.n, sm.flags, sm.range);
+    uint32_t f[kVec];
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) f[k] = vec_flags(sm.flags, k);
+    float E[kVec];
+    if (DENSITY) tile_segscan<SumOp>(v, f, E, p.status, 0, p.epoch, sm);
+    else tile_segscan<ProdOp>(v, f, E, p.status, 0, p.epoch, sm);
+
+    const unsigned lt = (1u << lane) - 1u;
+    uint32_t keep[kVec];
+    int within[kVec], vtot[kVec], wtot = 0;
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        float T[4];
+        if (DENSITY) {
+            finish_exclusive<SumOp>(v[k], f[k], E[k], T);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) T[c] = expf(-T[c]);
+        } else {
+            finish_exclusive<ProdOp>(v[k], f[k], E[k], T);
+        }
+        if (p.prefix) {
+            float pf[4];
+            g.load(p.prefix, p.vec_ok, k, 1.0f, pf);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) T[c] = __fmul_rn(T[c], pf[c]);
+        }
+        const long long gi = g.base + g.voff(k);
+        keep[k] = 0u;
+        within[k] = 0;
+        vtot[k] = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {  // volrend.py:414-417, 476-479
+            bool ok = T[c] >= p.early_stop_eps && gi + c < p.n;
+            if (p.alpha_thre > 0.0f) ok = ok && (al[k][c] >= p.alpha_thre);
+            const unsigned m = __ballot_sync(kFull, ok);
+            if (lane == 0) s_mask[w][k][c] = m;
+            keep[k] |= ok ? (1u << c) : 0u;
+            within[k] += __popc(m & lt);
+            vtot[k] += __popc(m);
+        }
+        wtot += vtot[k];
+        if (p.vis) {
+            uint8_t m4[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) m4[c] = (keep[k] >> c) & 1u;
+            if (p.vec_ok && gi + 3 < p.n) {
+                *reinterpret_cast<uchar4*>(p.vis + gi) = make_uchar4(m4[0], m4[1], m4[2], m4[3]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (gi + c < p.n) p.vis[gi + c] = m4[c];
+            }
+        }
+    }
+    if (lane == 0) s_wtot[w] = wtot;
+    __syncthreads();
+    int before = 0, agg = 0;
+#pragma unroll
+    for (int j = 0; j < kWarps; ++j) { if (j == w) before = agg; agg += s_wtot[j]; }
+    if (lane == 0) {
+        int run = before;
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) { s_vbase[w][k] = run; run += vtot[k]; }
+    }
+    if (threadIdx.x == 0) {
+        const long long tile = blockIdx.x;
+        unsigned long long* mine = p.status + tile * kStatusPerTile + 1;
+        long long X = 0;
+        if (tile == 0) {
+            st_relaxed_u64(mine, pack_count((uint32_t)agg, p.epoch, 2u));
+        } else {
+            st_relaxed_u64(mine, pack_count((uint32_t)agg, p.epoch, 1u));
+            X = lookback_count(p.status, 1, tile, p.epoch);
+            st_relaxed_u64(mine, pack_count((uint32_t)(X + agg), p.epoch, 2u));
+        }
+        s_tile_base = X;
+        if (tile == (long long)gridDim.x - 1 && q.total) *q.total = X + agg;
+    }
+    __syncthreads();
+    const long long tile_base = s_tile_base;
+    int vb = before;
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) {
+        long long pos = tile_base + vb + within[k];
+        vb += vtot[k];
+        const long long gi = g.base + g.voff(k);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if ((keep[k] >> c) & 1u) {
+                q.o_ray[pos] = __ldg(q.ray_indices + gi + c);
+                q.o_ts[pos] = __ldg(q.t_starts + gi + c);
+                q.o_te[pos] = __ldg(q.t_ends + gi + c);
+                ++pos;
+            }
+        }
+    }
+    if (q.o_packed_info) {
+        const long long r_lo = sm.range[0], r_hi = sm.range[1];
+        for (long long r = r_lo + threadIdx.x; r < r_hi; r += kThreads) {
+            const int P = (int)(load_chunk(p.seg.packed_info, r).start - g.base);  // in [0, kTile)
+            const int pw = P >> 9, pk = (P >> 7) & 3, pl = (P >> 2) & 31, pc = P & 3;
+            const unsigned below = (1u << pl) - 1u;
+            int rank = s_vbase[pw][pk];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const unsigned m = s_mask[pw][pk][c];
+                rank += __popc(m & below) + ((c < pc) ? (int)((m >> pl) & 1u) : 0);
+            }
+            q.o_packed_info[2 * r] = tile_base + rank;
+        }
+        if (blockIdx.x == gridDim.x - 1)  // rays that start at or past the end of the array (empty)
+            for (long long r = r_hi + threadIdx.x; r < p.seg.n_rays; r += kThreads)
+                q.o_packed_info[2 * r] = tile_base + agg;
+    }
+}
+
+// counts of the survivors' packed_info from neighbouring starts (the last ray: up to the total)
+__global__ void pi_counts_kernel(int64_t* __restrict__ pi, long long n_rays, const long long* __restrict__ total) {
+    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < n_rays;
+         r += (long long)gridDim.x * blockDim.x) {
+        const long long a = pi[2 * r];
+        const long long b = (r + 1 < n_rays) ? pi[2 * (r + 1)] : *total;
+        pi[2 * r + 1] = b - a;
+    }
+}
+
 struct WeightBwdArgs {
     const float* g_weights;  // any of the three upstream grads may be null (= zero)
     const float* g_trans;
@@ -476,6 +673,54 @@ NFB_API int nfb_render_weight_bits_bwd(int from_density, const float* g_weights,
     else weight_bwd_bits_kernel<false><<<grid, kThreads, 0, s>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("render_weight_bits_bwd");
+    return NFB_OK;
+}
+
+/* OccGridEstimator.sampling's "skip invisible space" step (occ_grid.py:186-220) in one pass. */
+NFB_API int nfb_visibility_compact(int from_density, const float* alphas, const float* t_starts,
+                                   const float* t_ends, const float* sigmas, const float* prefix_trans,
+                                   const int64_t* packed_info, int64_t n_rays, int64_t n,
+                                   const int64_t* ray_indices, float early_stop_eps, float alpha_thre,
+                                   int64_t* out_ray_indices, float* out_t_starts, float* out_t_ends,
+                                   int64_t* out_packed_info, uint8_t* vis, int64_t* total,
+                                   void* workspace, size_t workspace_bytes, uint32_t epoch,
+                                   nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0 && n_rays >= 0, "negative size");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    NFB_CHECK_ARG(total != nullptr, "null total");
+    if (n == 0) {
+        cudaMemsetAsync(total, 0, sizeof(int64_t), s);
+        if (out_packed_info && n_rays > 0) cudaMemsetAsync(out_packed_info, 0, sizeof(int64_t) * 2 * n_rays, s);
+        return NFB_OK;
+    }
+    NFB_CHECK_ARG(packed_info != nullptr && aligned16(packed_info), "packed_info (canonical, dense) is required, 16-byte aligned");
+    NFB_CHECK_ARG(ray_indices && t_starts && t_ends && out_ray_indices && out_t_starts && out_t_ends, "null pointer");
+    if (from_density) NFB_CHECK_ARG(sigmas != nullptr, "density mode needs sigmas");
+    else NFB_CHECK_ARG(alphas != nullptr, "alpha mode needs alphas");
+    int rc = prep_ws(workspace, workspace_bytes, n, epoch, s);
+    if (rc != NFB_OK) return rc;
+    VisCompactArgs a{};
+    a.w.alphas = alphas; a.w.t_starts = t_starts; a.w.t_ends = t_ends; a.w.sigmas = sigmas; a.w.prefix = prefix_trans;
+    a.w.vis = vis; a.w.early_stop_eps = early_stop_eps; a.w.alpha_thre = alpha_thre;
+    a.w.seg = SegSpec{packed_info, n_rays, 0};
+    a.w.n = n; a.w.n_tiles = num_tiles(n);
+    a.w.status = static_cast<unsigned long long*>(workspace); a.w.epoch = epoch;
+    a.w.vec_ok = all_aligned16({alphas, t_starts, t_ends, sigmas, prefix_trans}) &&
+                 (vis == nullptr || (reinterpret_cast<uintptr_t>(vis) & 3u) == 0);
+    a.ray_indices = ray_indices; a.t_starts = t_starts; a.t_ends = t_ends;
+    a.o_ray = out_ray_indices; a.o_ts = out_t_starts; a.o_te = out_t_ends;
+    a.o_packed_info = out_packed_info; a.total = reinterpret_cast<long long*>(total);
+    if (from_density) vis_compact_kernel<true><<<(unsigned)a.w.n_tiles, kThreads, 0, s>>>(a);
+    else vis_compact_kernel<false><<<(unsigned)a.w.n_tiles, kThreads, 0, s>>>(a);
+    count_launch();
+    if (out_packed_info && n_rays > 0) {
+        long long b = ceil_div<long long>(n_rays, 256);
+        if (b > (long long)sm_count() * 8) b = (long long)sm_count() * 8;
+        pi_counts_kernel<<<(unsigned)b, 256, 0, s>>>(out_packed_info, n_rays, a.total);
+        count_launch();
+    }
+    NFB_CHECK_LAUNCH("visibility_compact");
     return NFB_OK;
 }
 

@@ -7,9 +7,11 @@ helpers.  What differs is underneath:
     sample total; the reference has eight or more), gets (ray_indices, t_starts, t_ends)
     straight from the fill pass, and evaluates visibility with the fused kernel;
   * the EMA update uses scatter-max semantics — what the reference's author intended
-    (occ_grid.py:399-402) — so it is deterministic with duplicate cell ids, and across
-    ranks: with torch.distributed initialised, cells are evaluated in shards and `occs` is
-    MAX-all-reduced (NCCL) before binarisation, giving every rank the single-GPU result;
+    (occ_grid.py:399-402) — so it is deterministic with duplicate cell ids.  By default every
+    rank updates its own grid from the global RNG, as the reference does.  After
+    `shard_updates(process_group)` (opt-in) the ranks of that group split the `occ_eval_fn`
+    evaluations and `occs` is MAX-all-reduced (NCCL) before binarisation, giving every rank the
+    single-GPU result — the path's one collective (SURVEY.md §8e);
   * the (48 + 16) MiB int64 `grid_coords` / `grid_indices` tables of the reference are
     derived on demand instead of being resident buffers.
 """
@@ -22,7 +24,6 @@ from .. import _occ_ops
 from .._grid_ops import Marcher
 from .._packing import mark_canonical, remember_packed_info
 from ..grid import _enlarge_aabb
-from ..volrend import render_visibility_from_alpha, render_visibility_from_density
 from .base import AbstractEstimator
 
 
@@ -82,7 +83,34 @@ class OccGridEstimator(AbstractEstimator):
             "binaries", torch.zeros([levels] + resolution.tolist(), dtype=torch.bool)
         )
         self._occ_mean_cache: Optional[Tuple[int, int, float]] = None
-        self._update_seed = 0
+        # sharded updates (opt-in, see shard_updates): (process group | None, world, rank, seed)
+        self._shard: Optional[Tuple[object, int, int, int]] = None
+        self._update_count = 0
+
+    def shard_updates(self, process_group=None, seed: int = 0, enabled: bool = True,
+                      _world_rank: Optional[Tuple[int, int]] = None) -> "OccGridEstimator":
+        """Opt in to (or out of) splitting `_update` across the ranks of `process_group` (None =
+        the default group of torch.distributed, which must be initialised).
+
+        No counterpart in the reference, whose ranks each update their own grid.  When enabled,
+        every `_update` is a COLLECTIVE: all ranks of the group must call it in lockstep with the
+        same `step` and an `occ_eval_fn` of the same model, else the all-reduce deadlocks or mixes
+        grids.  The cells and jitter offsets of update number k are drawn from a private generator
+        seeded with (seed, k) — identical on every rank, independent of torch.manual_seed — each
+        rank evaluates `occ_eval_fn` on its 1/world slice of them, applies the decay to all of
+        them, and `occs` is MAX-all-reduced: the result is bit-identical to the same update done
+        by one rank (SURVEY.md §8e exactness rule).  Default (never called): rank-local updates
+        from the global RNG, no collective."""
+        if not enabled:
+            self._shard = None
+            return self
+        if _world_rank is not None:  # tests / parity checks: the same draws on a single rank
+            world, rank = _world_rank
+        else:
+            world, rank = _occ_ops.dist_info(process_group)
+        self._shard = (process_group, int(world), int(rank), int(seed))
+        self._update_count = 0
+        return self
 
     # -- derived tables (resident int64 buffers in the reference, occ_grid.py:76-83) ----------
     @property
@@ -157,28 +185,23 @@ class OccGridEstimator(AbstractEstimator):
         ):
             alpha_thre = min(alpha_thre, self._occs_mean())
             if sigma_fn is not None:
-                sigmas = (sigma_fn(t_starts, t_ends, ray_indices) if n_samples != 0
+                values = (sigma_fn(t_starts, t_ends, ray_indices) if n_samples != 0
                           else torch.empty((0,), device=t_starts.device))
                 assert (
-                    sigmas.shape == t_starts.shape
-                ), "sigmas must have shape of (N,)! Got {}".format(sigmas.shape)
-                masks = render_visibility_from_density(
-                    t_starts=t_starts, t_ends=t_ends, sigmas=sigmas, packed_info=packed_info,
-                    early_stop_eps=early_stop_eps, alpha_thre=alpha_thre,
-                )
+                    values.shape == t_starts.shape
+                ), "sigmas must have shape of (N,)! Got {}".format(values.shape)
             else:
-                alphas = (alpha_fn(t_starts, t_ends, ray_indices) if n_samples != 0
+                values = (alpha_fn(t_starts, t_ends, ray_indices) if n_samples != 0
                           else torch.empty((0,), device=t_starts.device))
                 assert (
-                    alphas.shape == t_starts.shape
-                ), "alphas must have shape of (N,)! Got {}".format(alphas.shape)
-                masks = render_visibility_from_alpha(
-                    alphas=alphas, packed_info=packed_info,
-                    early_stop_eps=early_stop_eps, alpha_thre=alpha_thre,
-                )
-            ray_indices, t_starts, t_ends = _occ_ops.compact_samples(
-                masks, ray_indices, t_starts, t_ends, marcher.n_rays
-            )
+                    values.shape == t_starts.shape
+                ), "alphas must have shape of (N,)! Got {}".format(values.shape)
+            # visibility, the three selects and the survivors' packed_info in one kernel
+            ray_indices, t_starts, t_ends, packed_info, _ = _occ_ops.visibility_compact(
+                sigma_fn is not None, values, t_starts, t_ends, packed_info, ray_indices,
+                early_stop_eps, alpha_thre)
+            mark_canonical(packed_info, total=ray_indices.shape[0])
+            remember_packed_info(ray_indices, packed_info, marcher.n_rays)
         return ray_indices, t_starts, t_ends
 
     def _occs_mean(self) -> float:
@@ -308,13 +331,13 @@ class OccGridEstimator(AbstractEstimator):
         warmup_steps: int = 256,
     ) -> None:
         """Update the occ field in the EMA way (reference occ_grid.py:367-404)."""
-        world, rank = _occ_ops.dist_info()
-        gen = None
-        if world > 1:
+        world, rank, gen, group = 1, 0, None, None
+        if self._shard is not None:
+            group, world, rank, seed = self._shard
             # every rank must draw the same cells and offsets: a private generator seeded alike
             gen = torch.Generator(device=self.device)
-            gen.manual_seed(0x5EED0000 + self._update_seed)
-            self._update_seed += 1
+            gen.manual_seed(((0x5EED0000 + seed) << 20) + self._update_count)
+            self._update_count += 1
         if step < warmup_steps:
             lvl_indices = self._get_all_cells()
         else:
@@ -329,7 +352,7 @@ class OccGridEstimator(AbstractEstimator):
             occ = occ_eval_fn(x).squeeze(-1) if hi > lo else x.new_empty((0,))
             _occ_ops.ema_update(self.occs, cell_ids, occ, lo, hi, ema_decay)
         if world > 1:
-            _occ_ops.all_reduce_max(self.occs)
+            _occ_ops.all_reduce_max(self.occs, group)
         self._occ_mean_cache = None  # the kernels wrote `occs` through its data pointer
         self.binaries = _occ_ops.binarize(self.occs, occ_thre).view(self.binaries.shape)
 

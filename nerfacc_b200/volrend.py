@@ -15,7 +15,7 @@ import torch
 from torch import Tensor
 
 from . import _render_ops as _ops
-from ._packing import as_packed_info, recall_packed_info
+from ._packing import as_packed_info, dense_total, recall_packed_info
 from .pack import pack_info
 from .scan import exclusive_prod, exclusive_sum
 
@@ -326,9 +326,11 @@ def accumulate_along_rays(
         return torch.sum(src, dim=-2)
     assert n_rays is not None, "n_rays must be provided"
     assert weights.dim() == 1, "weights must be flattened"
+    assert ray_indices.shape == weights.shape, (
+        f"ray_indices {tuple(ray_indices.shape)} and weights {tuple(weights.shape)} must have the same shape")
     if _accumulate_fused_ok(weights, values, ray_indices):
         ri = ray_indices.contiguous()
-        pi = recall_packed_info(ray_indices, n_rays)
+        pi = _recall_for(ray_indices, n_rays, weights.numel())
         return _ops.Accumulate.apply(weights, values, pi, ri, int(n_rays))
     src = weights[..., None] if values is None else weights[..., None] * values
     outputs = torch.zeros((n_rays, src.shape[-1]), device=src.device, dtype=src.dtype)
@@ -358,15 +360,25 @@ def accumulate_along_rays_(
     assert (
         outputs.dim() == 2 and outputs.shape[-1] == dim
     ), "outputs must be of shape (n_rays, D)"
+    assert ray_indices.shape == weights.shape, (
+        f"ray_indices {tuple(ray_indices.shape)} and weights {tuple(weights.shape)} must have the same shape")
     if (_accumulate_fused_ok(weights, values, ray_indices) and outputs.is_contiguous()
             and outputs.dtype == torch.float32 and _no_grad_needed(weights, values, outputs)):
-        pi = recall_packed_info(ray_indices, outputs.shape[0])
+        pi = _recall_for(ray_indices, outputs.shape[0], weights.numel())
         _ops.accumulate_fwd(weights.detach().contiguous(),
                             None if values is None else values.detach().contiguous(), pi,
                             ray_indices.contiguous(), outputs.shape[0], out=outputs)
         return
     src = weights[..., None] if values is None else weights[..., None] * values
     outputs.index_add_(0, ray_indices, src)
+
+
+def _recall_for(ray_indices: Tensor, n_rays: int, n: int) -> Optional[Tensor]:
+    """The packed_info remembered for `ray_indices`, only if it describes exactly n samples."""
+    pi = recall_packed_info(ray_indices, n_rays)
+    if pi is not None and dense_total(pi) != int(n):
+        return None
+    return pi
 
 
 def _composite_fused_ok(t_starts, t_ends, ray_indices, n_rays, rgbs, field) -> bool:

@@ -36,4 +36,4 @@ def test_two_rank_update_and_aggregation(tmp_path):
         logs.append(o.decode(errors="replace"))
     assert all(p.returncode == 0 for p in procs), "\n".join(logs)
     r = json.loads(out.read_text())
-    assert r == {"update": True, "parts": True, "ms": 11.0, "units": 3000, "distinct": True, "world": 2}
+    assert r == {"update": True, "estimator": True, "parts": True, "ms": 11.0, "units": 3000, "distinct": True, "world": 2}
