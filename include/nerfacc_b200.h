@@ -355,6 +355,21 @@ NFB_API int nfb_visibility_compact(int from_density, const float* alphas, const 
                                    int64_t* out_packed_info, uint8_t* vis, int64_t* total,
                                    void* workspace, size_t workspace_bytes, uint32_t epoch,
                                    nfb_stream_t stream);
+/* nfb_compact_samples without a workspace argument, for callers that cannot allocate (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
+ * REFERENCE.  The look-back status words live in a
+ * file-scope `static __device__` array of the library (256 KiB, held by every GPU that loads the
+ * library until exit), so one call handles at most NFB_COMPACT_STATIC_MAX_SAMPLES samples; a larger
+ * n returns NFB_ERR_INVALID_ARGUMENT.  Calls no cudaMalloc / cudaFree / allocating routine; the
+ * array's device address is looked up with cudaGetSymbolAddress once per device, at the first call
+ * made with that device current (make that call outside capture).  Every call shares the array and
+ * clears the part it uses on `stream` first: calls that overlap on the GPU (different streams, or
+ * graphs replayed concurrently) race — serialise them.  Outputs are identical to nfb_compact_samples. */
+#define NFB_COMPACT_STATIC_MAX_SAMPLES (1ll << 26)
+NFB_API int nfb_compact_samples_static(const uint8_t* mask, const int64_t* ray_indices,
+                                       const float* t_starts, const float* t_ends, int64_t n,
+                                       int64_t* out_ray_indices, float* out_t_starts,
+                                       float* out_t_ends, int64_t* total, nfb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * nerfacc.rendering() for packed rays in one forward and one backward kernel (a group of

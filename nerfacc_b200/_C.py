@@ -115,6 +115,7 @@ _PROTOS = {
                             c_size, c_ptr],
     "nfb_visibility_compact": [c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_f32, c_f32,
                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_u32, c_ptr],
+    "nfb_compact_samples_static": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "nfb_importance_sampling": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr,
                                 c_ptr, c_ptr, c_ptr, c_ptr],
     "nfb_searchsorted": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],

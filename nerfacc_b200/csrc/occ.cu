@@ -12,6 +12,8 @@
 //                         grid — two launches, no host sync, no temporaries;
 //  * compact_kernel       single-pass stream compaction (decoupled look-back) of
 //                         (ray_indices, t_starts, t_ends) by the visibility mask.
+#include <atomic>
+
 #include "seg_tile.cuh"
 
 namespace nfb {
@@ -167,6 +169,36 @@ compact_kernel(const uint8_t* __restrict__ mask, const int64_t* __restrict__ ray
     }
 }
 
+// ---- allocation-free compaction ------------------------------------------------------------
+// nfb_compact_samples_static keeps the look-back status words of compact_kernel in this
+// file-scope array instead of a caller-provided workspace, for callers that cannot allocate
+// (CUDA-graph capture, serving loops).  Every GPU that loads the library holds the 256 KiB until
+// exit.  `g_compact_status` is a host-side stand-in in host code, never a device address: the
+// launch below passes what cudaGetSymbolAddress returned for the current device.
+constexpr long long kStaticCompactMaxN = NFB_COMPACT_STATIC_MAX_SAMPLES;  // samples per call
+constexpr long long kStaticCompactTiles = kStaticCompactMaxN / kCompTile;
+static __device__ __align__(256) unsigned long long g_compact_status[kStaticCompactTiles];
+
+constexpr int kMaxDevices = 64;
+static std::atomic<unsigned long long*> g_compact_status_addr[kMaxDevices];
+
+// Device address of g_compact_status on the CURRENT device; looked up once per device.
+static cudaError_t compact_status_address(unsigned long long** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    unsigned long long* p = g_compact_status_addr[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_compact_status);
+        if (e != cudaSuccess) return e;
+        if (p == nullptr) return cudaErrorInvalidSymbol;
+        g_compact_status_addr[dev].store(p, std::memory_order_release);  // racing threads store the same value
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
 static inline unsigned blocks_for(long long n, int block = 256, int per_sm = 16) {
     long long b = ceil_div<long long>(n, block);
     const long long cap = (long long)sm_count() * per_sm;
@@ -253,6 +285,36 @@ NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
                                                     static_cast<unsigned long long*>(workspace));
     count_launch();
     NFB_CHECK_LAUNCH("compact_samples");
+    return NFB_OK;
+}
+
+NFB_API int nfb_compact_samples_static(const uint8_t* mask, const int64_t* ray_indices,
+                                       const float* t_starts, const float* t_ends, int64_t n,
+                                       int64_t* out_ray_indices, float* out_t_starts,
+                                       float* out_t_ends, int64_t* total, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0, "negative size");
+    NFB_CHECK_ARG(n <= kStaticCompactMaxN,
+                  "compact_samples_static: n = %lld exceeds the built-in scratch (at most %lld samples per call); "
+                  "use nfb_compact_samples with a caller-provided workspace",
+                  (long long)n, (long long)kStaticCompactMaxN);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (n == 0) { if (total) cudaMemsetAsync(total, 0, sizeof(int64_t), s); return NFB_OK; }
+    NFB_CHECK_ARG(mask && ray_indices && t_starts && t_ends && out_ray_indices && out_t_starts && out_t_ends, "null pointer");
+    unsigned long long* status = nullptr;
+    const cudaError_t e = compact_status_address(&status);
+    if (e != cudaSuccess) {
+        set_error("compact_samples_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        return NFB_ERR_CUDA;
+    }
+    const long long nt = ceil_div<long long>(n, kCompTile);
+    // the array keeps the previous call's states: the tiles this call uses must start at zero
+    cudaMemsetAsync(status, 0, (size_t)nt * sizeof(unsigned long long), s);
+    compact_kernel<<<(unsigned)nt, kThreads, 0, s>>>(mask, ray_indices, t_starts, t_ends, n, out_ray_indices,
+                                                    out_t_starts, out_t_ends, reinterpret_cast<long long*>(total),
+                                                    status);
+    count_launch();
+    NFB_CHECK_LAUNCH("compact_samples_static");
     return NFB_OK;
 }
 
