@@ -487,7 +487,9 @@ def run_ours(args) -> None:
     # Steps are numbered like a trainer's: the timed region starts at step 256 (the first
     # steady-state update of the occupancy grid; updates at 256, 272, ...: K/16 rounded up).
     FIRST = 256
-    state["step"] = FIRST - max(args.warmup, 3)
+    # warm-up runs the same step numbers the timed region starts with, so it contains a
+    # steady-state update (the first one pays torch's one-off kernel loads and allocations)
+    state["step"] = FIRST
     for _ in range(max(args.warmup, 3)):
         step(o_dev, d_dev)
     clocks = ClockSampler(local_rank)

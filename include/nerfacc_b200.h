@@ -330,6 +330,14 @@ NFB_API size_t nfb_occ_binarize_workspace_bytes(void);
 NFB_API int nfb_occ_binarize(const float* occs, int64_t n_cells, float occ_thre, uint8_t* binaries,
                              float* thre_out, void* workspace, size_t workspace_bytes,
                              nfb_stream_t stream);
+/* OccGridEstimator.mark_invisible_cells (nerfacc/estimators/occ_grid.py:263-332): occs[c] = 0 for
+ * the cells (occs[c] >= 0 on entry) whose corner-lattice point projects into at least one camera's
+ * image at depth >= near_plane and into none at 0 <= depth < near_plane, else -1.
+ * cams: [n_cams, 21] floats per camera = world->camera rotation (9, row-major), translation (3),
+ * intrinsics K (9, row-major); occs: [levels * rx*ry*rz]; res_host: HOST pointer to 3 ints. */
+NFB_API int nfb_mark_invisible_cells(const float* cams, int64_t n_cams, const int32_t* res_host,
+                                     int32_t levels, const float* aabbs, float width, float height,
+                                     float near_plane, float* occs, nfb_stream_t stream);
 /* Keep the samples with mask[i] != 0, order preserved; *total (device-visible) = how many. */
 NFB_API size_t nfb_compact_workspace_bytes(int64_t n);
 NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
@@ -463,6 +471,51 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
                                     const int64_t* edge_info, const int64_t* sample_info,
                                     const float* bias, float* out_edges, float* out_centres,
                                     nfb_stream_t stream);
+/* The first lines of every sigma_fn / rgb_sigma_fn in the reference's examples
+ * (examples/utils.py:82-112), the callers' side of the callbacks:
+ *   positions[i,:] = rays_o[ray_indices[i],:] + rays_d[ray_indices[i],:] * (t_starts[i] + t_ends[i]) / 2
+ *   dirs[i,:]      = rays_d[ray_indices[i],:]                       (optional: dirs may be NULL)
+ * in one pass, bit-identical to the torch expression.  ray_indices must lie in [0, n_rays). */
+NFB_API int nfb_sample_positions(const float* rays_o, const float* rays_d, const int64_t* ray_indices,
+                                 const float* t_starts, const float* t_ends, int64_t n, int64_t n_rays,
+                                 float* positions, float* dirs, nfb_stream_t stream);
+
+/* Batched nfb_importance_sampling that writes the interval edges twice: in the normalised
+ * coordinate s (out_edges [n_rays, n_out+1], as above) and mapped to ray distance t
+ * (out_t_edges, same shape) the way PropNetEstimator._transform_stot does
+ * (nerfacc/estimators/prop_net.py:215-229), op for op:
+ *   stot_mode 1 "uniform": t = s*c1 + (1-s)*c0      with c0 = t_min,   c1 = t_max
+ *   stot_mode 2 "lindisp": t = 1 / (s*c1 + (1-s)*c0) with c0 = 1/t_min, c1 = 1/t_max (rounded to fp32). */
+NFB_API int nfb_importance_sampling_stot(const float* vals, const float* cdfs, int64_t n_rays,
+                                         int64_t n_in, int64_t n_out, const float* bias,
+                                         float* out_edges, float* out_t_edges, int stot_mode, float c0,
+                                         float c1, nfb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * PropNetEstimator's batched-row glue (nerfacc/estimators/prop_net.py:96-114, 232-256).
+ */
+/* cdfs [n_rays, n+1] = 1 - cat([T, 0]) with T_i = exp(-sum_{j<i} sigmas_j * (t_vals_{j+1} - t_vals_j))
+ * (render_transmittance_from_density on t_starts = t_vals[:, :-1], t_ends = t_vals[:, 1:],
+ * nerfacc/volrend.py:209-264, then prop_net.py:112-114); 1 <= n <= 512. */
+NFB_API int nfb_cdf_from_density_fwd(const float* t_vals, const float* sigmas, int64_t n_rays, int64_t n,
+                                     float* cdfs, nfb_stream_t stream);
+/* g_sigmas [n_rays, n] from g_cdfs [n_rays, n+1] (what autograd derives from the composite above). */
+NFB_API int nfb_cdf_from_density_bwd(const float* t_vals, const float* sigmas, const float* g_cdfs,
+                                     int64_t n_rays, int64_t n, float* g_sigmas, nfb_stream_t stream);
+/* _pdf_loss for batched rows (prop_net.py:232-256): query edges/cdfs [n_rays, n_q], key edges/cdfs
+ * [n_rays, n_k]; loss [n_rays, n_q-1] = clip(w - w_outer, 0)^2 / (w + eps), w = the query bin's mass,
+ * w_outer = cdfs_key[ids_right of the bin's right edge] - cdfs_key[ids_left of its left edge]
+ * (ids as nfb_searchsorted). */
+NFB_API int nfb_pdf_loss_fwd(const float* q_vals, const float* q_cdfs, int64_t n_q, const float* k_vals,
+                             const float* k_cdfs, int64_t n_k, int64_t n_rays, float eps, float* loss,
+                             nfb_stream_t stream);
+/* g_k_cdfs [n_rays, n_k]: gradient of the loss rows w.r.t. cdfs_key given g_loss [n_rays, n_q-1]
+ * (the reference: gather backward = scatter_add with atomics; here every key edge sums its
+ * contiguous range of query bins, deterministic). */
+NFB_API int nfb_pdf_loss_bwd(const float* q_vals, const float* q_cdfs, int64_t n_q, const float* k_vals,
+                             const float* k_cdfs, int64_t n_k, int64_t n_rays, float eps,
+                             const float* g_loss, float* g_k_cdfs, nfb_stream_t stream);
+
 /* searchsorted: replaces csrc/pdf.cu:245-286 + 458-503.  For every query value the pair of
  * neighbouring key positions (ids_left, ids_right) with key[left] <= v < key[right], clamped to
  * the row.  Batched query (q_info == NULL): ids are relative to the key row; packed query:

@@ -110,6 +110,7 @@ _PROTOS = {
     "nfb_occ_ema_update": [c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_i64, c_f32, c_ptr, c_ptr],
     "nfb_occ_binarize_workspace_bytes": [],
     "nfb_occ_binarize": [c_ptr, c_i64, c_f32, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
+    "nfb_mark_invisible_cells": [c_ptr, c_i64, c_ptr, C.c_int32, c_ptr, c_f32, c_f32, c_f32, c_ptr, c_ptr],
     "nfb_compact_workspace_bytes": [c_i64],
     "nfb_compact_samples": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                             c_size, c_ptr],
@@ -118,6 +119,13 @@ _PROTOS = {
     "nfb_compact_samples_static": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "nfb_importance_sampling": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr,
                                 c_ptr, c_ptr, c_ptr, c_ptr],
+    "nfb_sample_positions": [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
+    "nfb_importance_sampling_stot": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_int, c_f32, c_f32,
+                                     c_ptr],
+    "nfb_cdf_from_density_fwd": [c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr],
+    "nfb_cdf_from_density_bwd": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr],
+    "nfb_pdf_loss_fwd": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_ptr, c_ptr],
+    "nfb_pdf_loss_bwd": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_f32, c_ptr, c_ptr, c_ptr],
     "nfb_searchsorted": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "nfb_traverse_fill": [_sp(Rays), _sp(Grid), _sp(March), c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                           c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],

@@ -140,3 +140,18 @@ def visibility_compact(from_density: bool, values: Tensor, t_starts: Tensor, t_e
         torch.cuda.current_stream(dev).synchronize()
     k = int(totals[0])
     return o_ray[:k], o_ts[:k], o_te[:k], o_pi, mask
+
+
+def mark_invisible_cells(occs: Tensor, cams: Tensor, resolution: Tensor, levels: int, aabbs: Tensor,
+                         width: float, height: float, near_plane: float) -> None:
+    """In place (occ_grid.py:263-332): occs = 0 for visible cells, -1 for the rest; cells already
+    at -1 are left alone.  cams: [n_cams, 21] = (w2c_R | w2c_T | K) per camera."""
+    dev = _C.require_cuda(occs, cams, aabbs)
+    assert occs.is_contiguous() and occs.dtype == torch.float32 and cams.shape[-1] == 21
+    res_host = (C.c_int32 * 3)(*[int(v) for v in resolution.tolist()])
+    aabbs = aabbs.float().contiguous()
+    with torch.cuda.device(dev):
+        rc = _C.lib().nfb_mark_invisible_cells(cams.data_ptr(), cams.shape[0], res_host, int(levels),
+                                               aabbs.data_ptr(), float(width), float(height), float(near_plane),
+                                               occs.data_ptr(), _C.stream_ptr(dev))
+    _C.check(rc, "mark_invisible_cells")

@@ -169,6 +169,64 @@ compact_kernel(const uint8_t* __restrict__ mask, const int64_t* __restrict__ ray
     }
 }
 
+// ---- mark_invisible_cells (occ_grid.py:263-332) ------------------------------------------------
+// One thread per cell, all cameras in a loop (camera rows staged in shared memory, 21 floats
+// each: world->camera rotation, translation, intrinsics).  The reference runs ~12 torch kernels
+// and two batched matmuls per chunk of 32^3 cells; the arithmetic here is the same sequence of
+// fp32 operations (x = ijk / (res - 1); world = lo + x * ext; cam = R . world + T with the dot
+// product as an FMA chain, the way a K = 3 matmul accumulates; pix = K . cam; u, v by IEEE division).
+constexpr int kCamChunk = 256;
+__global__ void __launch_bounds__(256)
+mark_invisible_kernel(const float* __restrict__ cams /*[n_cams,21]*/, int n_cams, int rx, int ry, int rz,
+                      int levels, const float* __restrict__ aabbs, float width, float height, float near,
+                      float* __restrict__ occs) {
+    __shared__ float s_cam[kCamChunk * 21];
+    const long long per_lvl = (long long)rx * ry * rz;
+    const long long n = per_lvl * levels;
+    // grid-stride in lockstep so that every thread of the CTA reaches the barriers
+    for (long long base = (long long)blockIdx.x * blockDim.x; base < n; base += (long long)gridDim.x * blockDim.x) {
+        const long long i = base + threadIdx.x;
+        const bool live = i < n && occs[i] >= 0.0f;  // cells already invisible are left alone
+        float w[3] = {0.0f, 0.0f, 0.0f};
+        if (live) {
+            const int lvl = (int)(i / per_lvl);
+            const long long c = i - (long long)lvl * per_lvl;
+            const int ijk[3] = {(int)(c / ((long long)ry * rz)), (int)((c / rz) % ry), (int)(c % rz)};
+            const int res[3] = {rx, ry, rz};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float x = __fdiv_rn((float)ijk[k], (float)(res[k] - 1));
+                const float lo = aabbs[6 * lvl + k], hi = aabbs[6 * lvl + 3 + k];
+                w[k] = __fadd_rn(lo, __fmul_rn(x, __fsub_rn(hi, lo)));
+            }
+        }
+        int seen = 0;
+        bool too_near = false;
+        for (int c0 = 0; c0 < n_cams; c0 += kCamChunk) {
+            const int nc = min(kCamChunk, n_cams - c0);
+            __syncthreads();
+            for (int j = threadIdx.x; j < nc * 21; j += blockDim.x) s_cam[j] = __ldg(cams + (long long)c0 * 21 + j);
+            __syncthreads();
+            if (!live) continue;
+            for (int j = 0; j < nc; ++j) {
+                const float* __restrict__ m = s_cam + j * 21;
+                float cam[3], pix[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    cam[k] = __fadd_rn(__fmaf_rn(m[3 * k + 2], w[2], __fmaf_rn(m[3 * k + 1], w[1], __fmul_rn(m[3 * k], w[0]))), m[9 + k]);
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    pix[k] = __fmaf_rn(m[12 + 3 * k + 2], cam[2], __fmaf_rn(m[12 + 3 * k + 1], cam[1], __fmul_rn(m[12 + 3 * k], cam[0])));
+                const float u = __fdiv_rn(pix[0], pix[2]), v = __fdiv_rn(pix[1], pix[2]);
+                const bool in_image = pix[2] >= 0.0f && u >= 0.0f && u < width && v >= 0.0f && v < height;
+                seen += (in_image && pix[2] >= near) ? 1 : 0;
+                too_near = too_near || (in_image && pix[2] < near);
+            }
+        }
+        if (live) occs[i] = (seen > 0 && !too_near) ? 0.0f : -1.0f;
+    }
+}
+
 // ---- allocation-free compaction ------------------------------------------------------------
 // nfb_compact_samples_static keeps the look-back status words of compact_kernel in this
 // file-scope array instead of a caller-provided workspace, for callers that cannot allocate
@@ -315,6 +373,23 @@ NFB_API int nfb_compact_samples_static(const uint8_t* mask, const int64_t* ray_i
                                                     status);
     count_launch();
     NFB_CHECK_LAUNCH("compact_samples_static");
+    return NFB_OK;
+}
+
+NFB_API int nfb_mark_invisible_cells(const float* cams, int64_t n_cams, const int32_t* res_host, int32_t levels,
+                                     const float* aabbs, float width, float height, float near_plane,
+                                     float* occs, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_cams >= 0 && levels >= 0, "negative size");
+    NFB_CHECK_ARG(res_host != nullptr, "null resolution");
+    const long long n = (long long)res_host[0] * res_host[1] * res_host[2] * levels;
+    if (n == 0) return NFB_OK;
+    NFB_CHECK_ARG(n_cams < (1ll << 31), "too many cameras");
+    NFB_CHECK_ARG((cams || n_cams == 0) && aabbs && occs, "null pointer");
+    mark_invisible_kernel<<<blocks_for(n, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        cams, (int)n_cams, res_host[0], res_host[1], res_host[2], levels, aabbs, width, height, near_plane, occs);
+    count_launch();
+    NFB_CHECK_LAUNCH("mark_invisible_cells");
     return NFB_OK;
 }
 

@@ -131,10 +131,21 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_kernel(con
 struct PdfTileArgs {
     const float* vals; const float* cdfs; const float* bias;
     float* out_edges; float* out_centres;  // either may be nullptr
+    // optional: the edges mapped from s in [0,1] to ray distance t as well (PropNetEstimator's
+    // _transform_stot, prop_net.py:215-229): 1 uniform: s*c1 + (1-s)*c0 with (c0, c1) = (t_min, t_max);
+    // 2 lindisp: 1 / (s*c1 + (1-s)*c0) with (c0, c1) = (1/t_min, 1/t_max)
+    float* out_t_edges;
+    int stot;
+    float stot_c0, stot_c1;
     long long n_rays;
     int n_in, n_out, rt;
     bool bin_slopes;
 };
+
+__device__ __forceinline__ float stot_apply(int mode, float s, float c0, float c1) {
+    const float a = __fadd_rn(__fmul_rn(s, c1), __fmul_rn(__fsub_rn(1.0f, s), c0));
+    return mode == 2 ? __fdiv_rn(1.0f, a) : a;
+}
 
 __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kernel(const PdfTileArgs p) {
     extern __shared__ float s_pdf[];
@@ -155,6 +166,7 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
             const float* cdf = s_cdf + (size_t)j * n_in;
             const float* val = s_val + (size_t)j * n_in;
             float* __restrict__ ge = p.out_edges ? p.out_edges + (r0 + j) * (n_out + 1) : nullptr;
+            float* __restrict__ gt = p.out_t_edges ? p.out_t_edges + (r0 + j) * (n_out + 1) : nullptr;
             float* __restrict__ gs = p.out_centres ? p.out_centres + (r0 + j) * n_out : nullptr;
             const float u_floor = cdf[0], u_ceil = cdf[last];
             const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
@@ -200,16 +212,25 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
                 const float t_next = __shfl_down_sync(kFull, t, 1);
                 carry_prev = __shfl_sync(kFull, t, 31);
                 if (valid && ge) {
+                    float e, e_last = 0.0f;
+                    bool has_last = false;
                     if (sid == 0) {
                         const float half = __fmul_rn(__fsub_rn(n_out > 1 ? t_next : t, t), 0.5f);
-                        ge[0] = fmaxf(__fsub_rn(t, half), t_min);
-                        if (n_out == 1) ge[1] = fminf(__fadd_rn(t, half), t_max);
+                        e = fmaxf(__fsub_rn(t, half), t_min);
+                        if (n_out == 1) { e_last = fminf(__fadd_rn(t, half), t_max); has_last = true; }
                     } else {
-                        ge[sid] = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                        e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
                         if (sid == n_out - 1) {
                             const float half = __fmul_rn(__fsub_rn(t, t_prev), 0.5f);
-                            ge[sid + 1] = fminf(__fadd_rn(t, half), t_max);
+                            e_last = fminf(__fadd_rn(t, half), t_max);
+                            has_last = true;
                         }
+                    }
+                    ge[sid] = e;
+                    if (has_last) ge[sid + 1] = e_last;
+                    if (gt) {
+                        gt[sid] = stot_apply(p.stot, e, p.stot_c0, p.stot_c1);
+                        if (has_last) gt[sid + 1] = stot_apply(p.stot, e_last, p.stot_c0, p.stot_c1);
                     }
                 }
             }
@@ -280,11 +301,12 @@ static inline int pdf_smem_floats(long long want) {
 
 extern "C" {
 
-NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const int64_t* in_info,
+static int importance_sampling_impl(const float* vals, const float* cdfs, const int64_t* in_info,
                                     int64_t n_rays, int64_t n_in, int64_t max_in,
                                     const int64_t* n_out_per_ray, int64_t n_out, int64_t max_out,
                                     const int64_t* edge_info, const int64_t* sample_info,
                                     const float* bias, float* out_edges, float* out_centres,
+                                    float* out_t_edges, int stot, float stot_c0, float stot_c1,
                                     nfb_stream_t stream) {
     using namespace nfb;
     NFB_CHECK_ARG(n_rays >= 0, "negative size");
@@ -304,6 +326,7 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
         if ((per_ray * rt + fixed) * 4 <= 48 * 1024 && n_in < (1 << 20) && n_out < (1 << 20)) {
             PdfTileArgs t{};
             t.vals = vals; t.cdfs = cdfs; t.bias = bias; t.out_edges = out_edges; t.out_centres = out_centres;
+            t.out_t_edges = out_t_edges; t.stot = stot; t.stot_c0 = stot_c0; t.stot_c1 = stot_c1;
             t.n_rays = n_rays; t.n_in = (int)n_in; t.n_out = (int)n_out; t.rt = rt;
             t.bin_slopes = (n_in - 1 <= 32) && (2 * (n_in - 1) <= n_out);
             const size_t smem = (size_t)(per_ray * rt + fixed) * 4;
@@ -318,6 +341,7 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
             return NFB_OK;
         }
     }
+    NFB_CHECK_ARG(out_t_edges == nullptr, "the s -> t output needs batched rows that fit the tile kernel");
     PdfArgs a{};
     a.vals = vals; a.cdfs = cdfs; a.in_info = in_info; a.n_in = n_in;
     a.n_out_per_ray = n_out_per_ray; a.n_out = n_out; a.edge_info = edge_info; a.sample_info = sample_info;
@@ -334,6 +358,28 @@ NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const 
     count_launch();
     NFB_CHECK_LAUNCH("importance_sampling");
     return NFB_OK;
+}
+
+NFB_API int nfb_importance_sampling(const float* vals, const float* cdfs, const int64_t* in_info,
+                                    int64_t n_rays, int64_t n_in, int64_t max_in,
+                                    const int64_t* n_out_per_ray, int64_t n_out, int64_t max_out,
+                                    const int64_t* edge_info, const int64_t* sample_info,
+                                    const float* bias, float* out_edges, float* out_centres,
+                                    nfb_stream_t stream) {
+    return importance_sampling_impl(vals, cdfs, in_info, n_rays, n_in, max_in, n_out_per_ray, n_out, max_out,
+                                    edge_info, sample_info, bias, out_edges, out_centres, nullptr, 0, 0.0f, 0.0f,
+                                    stream);
+}
+
+NFB_API int nfb_importance_sampling_stot(const float* vals, const float* cdfs, int64_t n_rays, int64_t n_in,
+                                         int64_t n_out, const float* bias, float* out_edges,
+                                         float* out_t_edges, int stot_mode, float c0, float c1,
+                                         nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(stot_mode == 1 || stot_mode == 2, "stot_mode: 1 uniform, 2 lindisp");
+    NFB_CHECK_ARG(out_edges && out_t_edges, "null pointer");
+    return importance_sampling_impl(vals, cdfs, nullptr, n_rays, n_in, n_in, nullptr, n_out, n_out, nullptr,
+                                    nullptr, bias, out_edges, nullptr, out_t_edges, stot_mode, c0, c1, stream);
 }
 
 NFB_API int nfb_searchsorted(const float* query, const int64_t* q_info, int64_t n_q,

@@ -279,24 +279,14 @@ class OccGridEstimator(AbstractEstimator):
         assert K.shape[0] == c2w.shape[0] or K.shape[0] == 1
 
         n_cams = c2w.shape[0]
-        rot = c2w[:, :3, :3].transpose(2, 1)  # world -> camera rotation, (n_cams, 3, 3)
-        trans = -rot @ c2w[:, :3, 3:]  # (n_cams, 3, 1)
-        coords_all = self.grid_coords
-        for lvl, cells in enumerate(self._get_all_cells()):
-            lo, hi = self.aabbs[lvl, :3], self.aabbs[lvl, 3:]
-            for i in range(0, len(cells), chunk):
-                ids = cells[i : i + chunk]
-                # cell corner lattice in [0, 1]^3 -> world -> camera -> pixel
-                unit = coords_all[ids] / (self.resolution - 1)
-                world = (lo + unit * (hi - lo)).T
-                cam = rot @ world + trans  # (n_cams, 3, chunk)
-                pix = K @ cam
-                depth = pix[:, 2]
-                u, v = pix[:, 0] / depth, pix[:, 1] / depth
-                in_image = (depth >= 0) & (u >= 0) & (u < width) & (v >= 0) & (v < height)
-                seen = ((depth >= near_plane) & in_image).sum(0) / n_cams > 0
-                too_close = ((depth < near_plane) & in_image).any(0)
-                self.occs[lvl * self.cells_per_lvl + ids] = torch.where(seen & ~too_close, 0.0, -1.0)
+        w2c_R = c2w[:, :3, :3].transpose(2, 1)  # (n_cams, 3, 3)
+        w2c_T = -w2c_R @ c2w[:, :3, 3:]  # (n_cams, 3, 1)
+        # one launch over cells x cameras (the reference: ~12 kernels + 2 matmuls per 32^3 chunk)
+        cams = torch.cat([w2c_R.reshape(n_cams, 9), w2c_T.reshape(n_cams, 3),
+                          K.expand(n_cams, 3, 3).reshape(n_cams, 9)], dim=-1).float().contiguous()
+        _occ_ops.mark_invisible_cells(self.occs, cams.to(self.device), self.resolution, self.levels,
+                                      self.aabbs, width, height, near_plane)
+        self._occ_mean_cache = None
 
     @torch.no_grad()
     def _get_all_cells(self) -> List[Tensor]:

@@ -3,9 +3,13 @@ nerfacc/estimators/prop_net.py:22-193 (same constructor, `sampling`, `compute_lo
 `update_every_n_steps`, `prop_cache` protocol) plus its helpers `_transform_stot`, `_pdf_loss`,
 `get_proposal_requires_grad_fn` (prop_net.py:195-259).
 
-Device work per level: one `nfb_importance_sampling` launch (centres are not needed, only the
-edges are written), the user's proposal network, and one fused `nfb_render_weight_fwd` launch
-for the batched transmittance; the loss does one `nfb_searchsorted` launch per cached level.
+Device work per level: one `nfb_importance_sampling_stot` launch (the edges in s and, mapped
+through `_transform_stot`, in t; the centres are not needed and not written), the user's proposal
+network, and one `nfb_cdf_from_density` launch (interval lengths, exclusive sum, exp, `1 - cat([T, 0])`
+in one pass; its backward is one launch too).  The loss is one `nfb_pdf_loss` launch per cached
+level each way (searchsorted, envelope mass, penalty; the gradient row of `cdfs_key` without atomics).
+Rows that the fused kernels do not take (packed intervals, tensor-valued near/far, rows of more
+than 512 samples) run the reference's sequence of ops on the general kernels.
 """
 from typing import Callable, List, Optional, Tuple
 
@@ -17,6 +21,7 @@ except ImportError:  # pragma: no cover
 import torch
 from torch import Tensor
 
+from .. import _prop_ops
 from ..data_specs import RayIntervals
 from ..pdf import importance_sampling, searchsorted
 from ..volrend import render_transmittance_from_density
@@ -78,20 +83,30 @@ class PropNetEstimator(AbstractEstimator):
         cdfs = torch.tensor([0.0, 1.0], device=dev).repeat(n_rays, 1)
         intervals = RayIntervals(vals=cdfs)
 
+        stot = (sampling_type, near_plane, far_plane)
+        if sampling_type not in ("uniform", "lindisp"):
+            raise ValueError(f"Unknown transform_type: {sampling_type}")
         for level_fn, level_samples in zip(prop_sigma_fns, prop_samples):
-            intervals, _ = importance_sampling(intervals, cdfs, level_samples, stratified, _samples=False)
-            t_vals = _transform_stot(sampling_type, intervals.vals, near_plane, far_plane)
+            intervals, _, t_vals = importance_sampling(intervals, cdfs, level_samples, stratified,
+                                                       _samples=False, _stot=stot)
+            if t_vals is None:
+                t_vals = _transform_stot(sampling_type, intervals.vals, near_plane, far_plane)
             t_starts, t_ends = t_vals[..., :-1], t_vals[..., 1:]
             with torch.set_grad_enabled(requires_grad):
                 sigmas = level_fn(t_starts, t_ends)
                 assert sigmas.shape == t_starts.shape
-                trans, _ = render_transmittance_from_density(t_starts, t_ends, sigmas)
-                cdfs = _cdf_from_trans(trans)
+                if _prop_ops.cdf_rows_ok(t_vals, sigmas):
+                    cdfs = _prop_ops.CdfFromDensity.apply(t_vals, sigmas)
+                else:
+                    trans, _ = render_transmittance_from_density(t_starts, t_ends, sigmas)
+                    cdfs = _cdf_from_trans(trans)
                 if requires_grad:
                     self.prop_cache.append((intervals, cdfs))
 
-        intervals, _ = importance_sampling(intervals, cdfs, num_samples, stratified, _samples=False)
-        t_vals = _transform_stot(sampling_type, intervals.vals, near_plane, far_plane)
+        intervals, _, t_vals = importance_sampling(intervals, cdfs, num_samples, stratified,
+                                                   _samples=False, _stot=stot)
+        if t_vals is None:
+            t_vals = _transform_stot(sampling_type, intervals.vals, near_plane, far_plane)
         if requires_grad:
             self.prop_cache.append((intervals, None))
         return t_vals[..., :-1], t_vals[..., 1:]
@@ -180,6 +195,10 @@ def _pdf_loss(
 ) -> Tensor:
     """Mip-NeRF 360 proposal loss: each query interval's mass must not exceed the mass of the
     key intervals that envelope it (prop_net.py:232-257)."""
+    if (segments_query.vals.dim() == 2 and segments_key.vals.dim() == 2
+            and _prop_ops.pdf_loss_rows_ok(segments_query.vals, cdfs_query, segments_key.vals, cdfs_key)):
+        # one launch: search, envelope mass and penalty (and one launch for the gradient)
+        return _prop_ops.PdfLoss.apply(segments_query.vals, cdfs_query, segments_key.vals, cdfs_key, eps)
     ids_left, ids_right = searchsorted(segments_key, segments_query)
     if segments_query.vals.dim() > 1:
         w = cdfs_query[..., 1:] - cdfs_query[..., :-1]

@@ -53,3 +53,36 @@ def pack_info(ray_indices: Tensor, n_rays: Optional[int] = None) -> Tensor:
     mark_canonical(packed_info, total=ri.numel())
     remember_packed_info(ray_indices, packed_info, n_rays)
     return packed_info
+
+
+@torch.no_grad()
+def sample_positions(rays_o: Tensor, rays_d: Tensor, ray_indices: Tensor, t_starts: Tensor, t_ends: Tensor,
+                     return_dirs: bool = False):
+    """Sample mid-points along the rays, as every `sigma_fn` / `rgb_sigma_fn` computes them first
+    (reference examples/utils.py:82-112):
+
+    >>> positions = rays_o[ray_indices] + rays_d[ray_indices] * (t_starts + t_ends)[:, None] / 2.0
+    >>> t_dirs = rays_d[ray_indices]      # with return_dirs=True
+
+    One pass over the samples (8 + 8 B read, 12 or 24 B written per sample) instead of two gathers
+    and three elementwise kernels; bit-identical to the expression above.  Not differentiable
+    (rays and sample distances carry no gradient on this path).  Additive API: not part of nerfacc.
+
+    Returns `positions` (n_samples, 3), or `(positions, t_dirs)`.
+    """
+    dev = _C.require_cuda(rays_o, rays_d, ray_indices, t_starts, t_ends)
+    f32 = lambda t: t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+    rays_o, rays_d, t_starts, t_ends = f32(rays_o), f32(rays_d), f32(t_starts), f32(t_ends)
+    assert rays_o.dim() == 2 and rays_o.shape[-1] == 3 and rays_o.shape == rays_d.shape, "rays must be (n_rays, 3)"
+    assert ray_indices.dim() == 1 and ray_indices.shape == t_starts.shape == t_ends.shape, "samples must be flattened"
+    ri = ray_indices.long().contiguous()
+    n = ri.shape[0]
+    positions = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    dirs = torch.empty((n, 3), dtype=torch.float32, device=dev) if return_dirs else None
+    if n > 0:
+        with torch.cuda.device(dev):
+            rc = _C.lib().nfb_sample_positions(rays_o.data_ptr(), rays_d.data_ptr(), ri.data_ptr(),
+                                               t_starts.data_ptr(), t_ends.data_ptr(), n, rays_o.shape[0],
+                                               positions.data_ptr(), _C.ptr(dirs), _C.stream_ptr(dev))
+        _C.check(rc, "sample_positions")
+    return (positions, dirs) if return_dirs else positions

@@ -79,6 +79,7 @@ def importance_sampling(
     *,
     _bias: Optional[Tensor] = None,
     _samples: bool = True,
+    _stot: Optional[Tuple[str, float, float]] = None,
 ) -> Tuple[RayIntervals, RaySamples]:
     """Inverse-transform resampling of every ray (reference nerfacc/pdf.py:66-139).
 
@@ -125,6 +126,22 @@ def importance_sampling(
         want_samples = _samples or vals.dim() == 1
         centres = torch.empty(lead + (n_out,), dtype=torch.float32, device=dev) if want_samples else None
         edges = torch.empty(lead + (n_out + 1,), dtype=torch.float32, device=dev)
+        if _stot is not None:
+            # PropNetEstimator: the edges in s and, from the same kernel, mapped to ray distance
+            # (third return value); None when this shape has no fused path
+            t_edges = None
+            kind, t_min, t_max = _stot
+            fused = (vals.dim() > 1 and in_info is None and not want_samples and kind in ("uniform", "lindisp")
+                     and isinstance(t_min, (int, float)) and isinstance(t_max, (int, float)) and n_in <= 1024)
+            if fused and n_rays > 0 and n_out > 0:
+                c0, c1 = (float(t_min), float(t_max)) if kind == "uniform" else (1 / t_min, 1 / t_max)
+                t_edges = torch.empty_like(edges)
+                with torch.cuda.device(dev):
+                    rc = _C.lib().nfb_importance_sampling_stot(
+                        vals.data_ptr(), cdfs.data_ptr(), n_rays, n_in, n_out, _C.ptr(bias), edges.data_ptr(),
+                        t_edges.data_ptr(), 1 if kind == "uniform" else 2, c0, c1, _C.stream_ptr(dev))
+                _C.check(rc, "importance_sampling_stot")
+                return RayIntervals(vals=edges), RaySamples(vals=None), t_edges
         if n_rays > 0 and n_out > 0:
             with torch.cuda.device(dev):
                 rc = _C.lib().nfb_importance_sampling(
@@ -132,6 +149,8 @@ def importance_sampling(
                     None, n_out, n_out, None, None, _C.ptr(bias),
                     edges.data_ptr(), _C.ptr(centres), _C.stream_ptr(dev))
             _C.check(rc, "importance_sampling")
+        if _stot is not None:
+            return RayIntervals(vals=edges), RaySamples(vals=centres), None
         return RayIntervals(vals=edges), RaySamples(vals=centres)
 
     # per-ray counts: flattened outputs.  The totals size the allocations (one host sync, as the

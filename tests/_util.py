@@ -34,3 +34,25 @@ def assert_close(actual, expected, rtol, atol, what=""):
         raise AssertionError(
             f"{what}: {int(bad.sum())}/{bad.size} mismatches; worst at {i}: got {actual.flat[i]!r} "
             f"expected {expected.flat[i]!r} (err {err.flat[i]:.3e}, tol {tol.flat[i]:.3e})")
+
+
+def record(name, values):
+    """Append measured figures (max errors of ours / of the reference kernels against float64, ...)
+    to gpurun_out/measured_errors.json — the source of the tolerance table in DESIGN.md section 2.
+    Never fails a test."""
+    import json
+    import os
+
+    try:
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        path = os.path.join(root, "gpurun_out", "measured_errors.json")
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        data = {}
+        if os.path.exists(path):
+            with open(path) as f:
+                data = json.load(f)
+        data[name] = values
+        with open(path, "w") as f:
+            json.dump(data, f, indent=1, sort_keys=True)
+    except Exception:
+        pass
