@@ -147,6 +147,13 @@ __device__ __forceinline__ float stot_apply(int mode, float s, float c0, float c
     return mode == 2 ? __fdiv_rn(1.0f, a) : a;
 }
 
+// BINS: 0 general (binary search + one IEEE division per sample), 1 a single input bin
+// (n_in == 2: PropNetEstimator's first level, the uniform CDF — no search, the bin's constants in
+// registers), 2 few bins (n_in - 1 <= 32, fewer than half as many as samples): search, slopes from a
+// per-ray table.  STOT: 0 off, 1 uniform, 2 lindisp.  The loop body is straight-line: the search
+// runs a fixed number of branch-free steps, all lanes store every iteration, and the first and last
+// edge (pdf.cu:178-196, 224-238) are patched by lane 0 after the loop.
+template <int STOT, bool CENTRES, int BINS>
 __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kernel(const PdfTileArgs p) {
     extern __shared__ float s_pdf[];
     const int lane = lane_id(), w = warp_id(), tid = threadIdx.x;
@@ -154,90 +161,123 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
     float* s_cdf = s_pdf;                              // [rt][n_in]
     float* s_val = s_cdf + (size_t)p.rt * n_in;        // [rt][n_in]
     float* s_bin = s_val + (size_t)p.rt * n_in + w * 64;  // per warp: [32] slope, [32] degenerate midpoint
+    int top = 1;  // largest power of two <= last (search steps)
+    while (2 * top <= last) top <<= 1;
     const long long n_tiles = (p.n_rays + p.rt - 1) / p.rt;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long r0 = tile * p.rt;
         const int rays = (int)((p.n_rays - r0 < p.rt) ? (p.n_rays - r0) : p.rt);
         const float* __restrict__ gc = p.cdfs + r0 * n_in;
         const float* __restrict__ gv = p.vals + r0 * n_in;
-        for (int i = tid; i < rays * n_in; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
+        const int total = rays * n_in;
+        if (((reinterpret_cast<uintptr_t>(gc) | reinterpret_cast<uintptr_t>(gv)) & 15u) == 0) {
+            const int n4 = total >> 2;
+            for (int i = tid; i < n4; i += kPdfWarps * 32) {
+                reinterpret_cast<float4*>(s_cdf)[i] = __ldg(reinterpret_cast<const float4*>(gc) + i);
+                reinterpret_cast<float4*>(s_val)[i] = __ldg(reinterpret_cast<const float4*>(gv) + i);
+            }
+            for (int i = 4 * n4 + tid; i < total; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
+        } else {
+            for (int i = tid; i < total; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
+        }
         __syncthreads();
         for (int j = w; j < rays; j += kPdfWarps) {
             const float* cdf = s_cdf + (size_t)j * n_in;
             const float* val = s_val + (size_t)j * n_in;
-            float* __restrict__ ge = p.out_edges ? p.out_edges + (r0 + j) * (n_out + 1) : nullptr;
-            float* __restrict__ gt = p.out_t_edges ? p.out_t_edges + (r0 + j) * (n_out + 1) : nullptr;
-            float* __restrict__ gs = p.out_centres ? p.out_centres + (r0 + j) * n_out : nullptr;
+            float* __restrict__ ge = p.out_edges + (r0 + j) * (n_out + 1);
+            float* __restrict__ gt = STOT ? p.out_t_edges + (r0 + j) * (n_out + 1) : nullptr;
+            float* __restrict__ gs = CENTRES ? p.out_centres + (r0 + j) * n_out : nullptr;
             const float u_floor = cdf[0], u_ceil = cdf[last];
             const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
             const float b = p.bias ? __ldg(p.bias + r0 + j) : 0.5f;
             const float t_min = val[0], t_max = val[last];
-            if (p.bin_slopes) {
+            float slope1 = 0.0f, mid1 = 0.0f;  // BINS == 1: the one bin
+            bool flat1 = false;
+            if (BINS == 1) {
+                const float du = __fsub_rn(u_ceil, u_floor);
+                flat1 = du < 1e-10f;  // pdf.cu:159-160
+                slope1 = __fdiv_rn(__fsub_rn(t_max, t_min), du);
+                mid1 = __fmul_rn(__fadd_rn(t_min, t_max), 0.5f);
+            } else if (BINS == 2) {
                 if (lane < last) {
                     const float du = __fsub_rn(cdf[lane + 1], cdf[lane]);
                     const bool flat = du < 1e-10f;
-                    // a flat bin (pdf.cu:159-160) keeps its midpoint in the second slot; other bins a NaN there
+                    // a flat bin keeps its midpoint in the second slot; other bins a NaN there
                     s_bin[lane] = __fdiv_rn(__fsub_rn(val[lane + 1], val[lane]), du);
                     s_bin[32 + lane] = flat ? __fmul_rn(__fadd_rn(val[lane], val[lane + 1]), 0.5f) : __int_as_float(0x7fc00000);
                 }
                 __syncwarp();
             }
             float carry_prev = 0.0f;  // centre of sample i0 - 1
+            float t0 = 0.0f, t1 = 0.0f, tl = 0.0f, tl2 = 0.0f;  // centres 0, 1, n_out-1, n_out-2
             for (int i0 = 0; i0 < n_out; i0 += 32) {
                 const int sid = i0 + lane;
-                const bool valid = sid < n_out;
-                float t = 0.0f;
-                if (valid) {
-                    const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
-                    const int q = upper_bound(cdf, 0, last, u);
-                    const int p0 = max(min(q - 1, last), 0), p1 = max(min(q, last), 0);
+                const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
+                float t;
+                if (BINS == 1) {
+                    // upper_bound over the single leading edge: p0 = 0, p1 = 1 when cdf[0] <= u, else both 0
+                    const bool in_bin = !(u_floor > u);
+                    t = flat1 ? mid1 : __fmaf_rn(__fsub_rn(u, u_floor), slope1, t_min);
+                    if (!in_bin) t = __fmul_rn(__fadd_rn(t_min, t_min), 0.5f);  // degenerate pair (0, 0): du = 0 < 1e-10
+                } else {
+                    // q = upper_bound(cdf[0..last), u) (pdf.cu:44-63): the count of leading entries <= u
+                    int q = 0;
+                    for (int st = top; st > 0; st >>= 1) {
+                        const int idx = q + st;
+                        const float c = cdf[min(idx, last) - 1];
+                        q = (idx <= last && !(c > u)) ? idx : q;
+                    }
+                    const int p0 = max(q - 1, 0), p1 = q;  // q <= last
                     const float u_lower = cdf[p0], t_lower = val[p0];
-                    if (p.bin_slopes && p1 == p0 + 1) {
+                    if (BINS == 2 && p1 == p0 + 1) {
                         const float mid = s_bin[32 + p0];
                         t = (mid == mid) ? mid : __fmaf_rn(__fsub_rn(u, u_lower), s_bin[p0], t_lower);
                     } else {
                         const float u_upper = cdf[p1], t_upper = val[p1];
-                        if (__fsub_rn(u_upper, u_lower) < 1e-10f) {
-                            t = __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f);
-                        } else {
-                            const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), __fsub_rn(u_upper, u_lower));
-                            t = __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
-                        }
+                        const float du = __fsub_rn(u_upper, u_lower);
+                        const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), du);
+                        t = (du < 1e-10f) ? __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f)
+                                          : __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
                     }
-                    if (gs) gs[sid] = t;
                 }
-                // compute_intervels_kernel, pdf.cu:169-241
+                const bool valid = sid < n_out;
+                if (CENTRES && valid) gs[sid] = t;
                 float t_prev = __shfl_up_sync(kFull, t, 1);
                 if (lane == 0) t_prev = carry_prev;
-                const float t_next = __shfl_down_sync(kFull, t, 1);
-                carry_prev = __shfl_sync(kFull, t, 31);
-                if (valid && ge) {
-                    float e, e_last = 0.0f;
-                    bool has_last = false;
-                    if (sid == 0) {
-                        const float half = __fmul_rn(__fsub_rn(n_out > 1 ? t_next : t, t), 0.5f);
-                        e = fmaxf(__fsub_rn(t, half), t_min);
-                        if (n_out == 1) { e_last = fminf(__fadd_rn(t, half), t_max); has_last = true; }
-                    } else {
-                        e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
-                        if (sid == n_out - 1) {
-                            const float half = __fmul_rn(__fsub_rn(t, t_prev), 0.5f);
-                            e_last = fminf(__fadd_rn(t, half), t_max);
-                            has_last = true;
-                        }
-                    }
-                    ge[sid] = e;
-                    if (has_last) ge[sid + 1] = e_last;
-                    if (gt) {
-                        gt[sid] = stot_apply(p.stot, e, p.stot_c0, p.stot_c1);
-                        if (has_last) gt[sid + 1] = stot_apply(p.stot, e_last, p.stot_c0, p.stot_c1);
-                    }
+                if (i0 == 0) { t0 = __shfl_sync(kFull, t, 0); t1 = __shfl_sync(kFull, t, 1); }
+                if (i0 + 32 >= n_out) {  // the last chunk: centres n_out-1 and n_out-2
+                    const int l = n_out - 1 - i0;
+                    tl = __shfl_sync(kFull, t, l);
+                    tl2 = (l > 0) ? __shfl_sync(kFull, t, l > 0 ? l - 1 : 0) : carry_prev;
                 }
+                carry_prev = __shfl_sync(kFull, t, 31);
+                // compute_intervels_kernel, pdf.cu:169-241: interior edges are midpoints of neighbouring centres
+                const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                if (valid) {
+                    ge[sid] = e;  // (edge 0 is patched below)
+                    if (STOT) gt[sid] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
+                }
+            }
+            if (lane == 0) {
+                const float half0 = __fmul_rn(__fsub_rn(n_out > 1 ? t1 : t0, t0), 0.5f);
+                const float e0 = fmaxf(__fsub_rn(t0, half0), t_min);
+                const float halfn = (n_out > 1) ? __fmul_rn(__fsub_rn(tl, tl2), 0.5f) : half0;
+                const float en = fminf(__fadd_rn(tl, halfn), t_max);
+                ge[0] = e0;
+                ge[n_out] = en;
+                if (STOT) { gt[0] = stot_apply(STOT, e0, p.stot_c0, p.stot_c1); gt[n_out] = stot_apply(STOT, en, p.stot_c0, p.stot_c1); }
             }
             __syncwarp();
         }
         __syncthreads();
     }
+}
+
+template <int STOT, bool CENTRES>
+static void launch_is_tile(const PdfTileArgs& t, int bins, unsigned blocks, size_t smem, cudaStream_t st) {
+    if (bins == 1) importance_sampling_tile_kernel<STOT, CENTRES, 1><<<blocks, kPdfWarps * 32, smem, st>>>(t);
+    else if (bins == 2) importance_sampling_tile_kernel<STOT, CENTRES, 2><<<blocks, kPdfWarps * 32, smem, st>>>(t);
+    else importance_sampling_tile_kernel<STOT, CENTRES, 0><<<blocks, kPdfWarps * 32, smem, st>>>(t);
 }
 
 struct SearchArgs {
@@ -323,7 +363,8 @@ static int importance_sampling_impl(const float* vals, const float* cdfs, const 
         const long long fixed = (long long)kPdfWarps * 64;
         int rt = 64;
         while (rt > 4 && (per_ray * rt + fixed) * 4 > 48 * 1024) rt >>= 1;
-        if ((per_ray * rt + fixed) * 4 <= 48 * 1024 && n_in < (1 << 20) && n_out < (1 << 20)) {
+        if ((per_ray * rt + fixed) * 4 <= 48 * 1024 && n_in < (1 << 20) && n_out < (1 << 20) && out_edges != nullptr &&
+            n_in >= 2) {
             PdfTileArgs t{};
             t.vals = vals; t.cdfs = cdfs; t.bias = bias; t.out_edges = out_edges; t.out_centres = out_centres;
             t.out_t_edges = out_t_edges; t.stot = stot; t.stot_c0 = stot_c0; t.stot_c1 = stot_c1;
@@ -335,7 +376,12 @@ static int importance_sampling_impl(const float* vals, const float* cdfs, const 
             // and keeps the load and compute phases of neighbouring tiles from overlapping)
             const long long cap = (long long)sm_count() * 4096;
             if (blocks > cap) blocks = cap;
-            importance_sampling_tile_kernel<<<(unsigned)blocks, kPdfWarps * 32, smem, st>>>(t);
+            const int bins = (n_in == 2) ? 1 : (t.bin_slopes ? 2 : 0);
+            const bool cen = out_centres != nullptr;
+            const unsigned nb = (unsigned)blocks;
+            if (stot == 2) { if (cen) launch_is_tile<2, true>(t, bins, nb, smem, st); else launch_is_tile<2, false>(t, bins, nb, smem, st); }
+            else if (stot == 1) { if (cen) launch_is_tile<1, true>(t, bins, nb, smem, st); else launch_is_tile<1, false>(t, bins, nb, smem, st); }
+            else { if (cen) launch_is_tile<0, true>(t, bins, nb, smem, st); else launch_is_tile<0, false>(t, bins, nb, smem, st); }
             count_launch();
             NFB_CHECK_LAUNCH("importance_sampling_tile");
             return NFB_OK;

@@ -162,6 +162,19 @@ __global__ void __launch_bounds__(kThreads) vis_compact_kernel(const VisCompactA
     __shared__ long long s_tile_base;
     const TileGeom<false> g(p.n, p.n_tiles);
     const int lane = lane_id(), w = warp_id();
+    // what the survivors' copies will read after the two look-backs: pull it into L2 now, so those
+    // late, dependent loads do not start a DRAM round trip (one 128-byte line per thread)
+    {
+        const long long left = p.n - g.base;
+        const long long items = left < kTile ? left : kTile;
+        const char* ri = reinterpret_cast<const char*>(q.ray_indices + g.base);
+        if ((long long)threadIdx.x * 128 < items * 8) asm volatile("prefetch.global.L2 [%0];" :: "l"(ri + threadIdx.x * 128));
+        if (!DENSITY && (long long)threadIdx.x * 128 < items * 8) {
+            const int half = threadIdx.x >> 1;  // 128 lines each for t_starts and t_ends
+            const char* tp = reinterpret_cast<const char*>(((threadIdx.x & 1) ? q.t_ends : q.t_starts) + g.base);
+            if ((long long)half * 128 < items * 4) asm volatile("prefetch.global.L2 [%0];" :: "l"(tp + half * 128));
+        }
+    }
     float v[kVec][4], al[kVec][4];
 #pragma unroll
     for (int k = 0; k < kVec; ++k) {
