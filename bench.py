@@ -617,7 +617,8 @@ def run_ours(args) -> None:
         configs = {"method": "CUDA events, 3 warm-ups, median of 5 groups of 5 back-to-back calls; "
                              "ref_cuda_ms = the unmodified reference extension (oracle/_ref) on the same tensors",
                    "ref_cuda": R is not None}
-        for name, fn in (("cfg3", BC.bench_cfg3), ("cfg4", BC.bench_cfg4), ("cfg5", BC.bench_cfg5)):
+        for name, fn in (("cfg3", BC.bench_cfg3), ("cfg4", BC.bench_cfg4), ("cfg5", BC.bench_cfg5),
+                         ("test_time_loop", lambda nf_, dev_, peak_, R_: BC.bench_chunked(nf_, dev_, peak_))):
             try:
                 configs[name] = fn(nf, dev, peak, R)
             except Exception as e:  # a side leg must not cost the headline line

@@ -605,6 +605,104 @@ def bench_cfg5(nf, dev, peak, R, n_rays=1 << 20):
     return res
 
 
+# ------------------------------------------------------------------ test-time loop
+def spelled_out_loop(pkg, est, o, d, fn, step, cone, early_stop_eps, alpha_thre, max_samples=1024):
+    """examples/utils.py:252-425 (render_image_with_occgrid_test) call for call, on package `pkg`
+    (this library, or the reference package on the reference kernels)."""
+    n = o.shape[0]
+    dev = o.device
+    opacity = torch.zeros((n, 1), device=dev)
+    depth = torch.zeros((n, 1), device=dev)
+    rgb = torch.zeros((n, 3), device=dev)
+    ray_mask = torch.ones(n, device=dev).bool()
+    min_samples = 1 if cone == 0 else 4
+    iter_samples = total_samples = 0
+    near_planes = torch.full_like(o[..., 0], fill_value=0.0)
+    far_planes = torch.full_like(o[..., 0], fill_value=1e10)
+    t_mins, t_maxs, hits = pkg.ray_aabb_intersect(o, d, est.aabbs)
+    m = est.binaries.size(0)
+    if m > 1:
+        t_sorted, t_indices = torch.sort(torch.cat([t_mins, t_maxs], -1), -1)
+    else:
+        t_sorted = torch.cat([t_mins, t_maxs], -1)
+        t_indices = torch.arange(0, m * 2, device=dev, dtype=torch.int64).expand(n, m * 2)
+    opc_thre = 1 - early_stop_eps
+    while iter_samples < max_samples:
+        n_alive = ray_mask.sum().item()
+        if n_alive == 0:
+            break
+        n_samples = max(min(n // n_alive, 64), min_samples)
+        iter_samples += n_samples
+        intervals, samples, termination_planes = pkg.traverse_grids(
+            o, d, est.binaries, est.aabbs, near_planes, far_planes, step, cone, n_samples, True, ray_mask,
+            t_sorted, t_indices, hits)
+        t_starts = intervals.vals[intervals.is_left]
+        t_ends = intervals.vals[intervals.is_right]
+        ray_indices = samples.ray_indices[samples.is_valid]
+        packed_info = samples.packed_info
+        rgbs, sigmas = fn(t_starts, t_ends, ray_indices)
+        weights, _, alphas = pkg.render_weight_from_density(
+            t_starts, t_ends, sigmas, ray_indices=ray_indices, n_rays=n,
+            prefix_trans=1 - opacity[ray_indices].squeeze(-1))
+        if alpha_thre > 0:
+            vis = alphas >= alpha_thre
+            ray_indices, rgbs, weights, t_starts, t_ends = (ray_indices[vis], rgbs[vis], weights[vis],
+                                                            t_starts[vis], t_ends[vis])
+        pkg.accumulate_along_rays_(weights, values=rgbs, ray_indices=ray_indices, outputs=rgb)
+        pkg.accumulate_along_rays_(weights, values=None, ray_indices=ray_indices, outputs=opacity)
+        pkg.accumulate_along_rays_(weights, values=(t_starts + t_ends)[..., None] / 2.0, ray_indices=ray_indices,
+                                   outputs=depth)
+        near_planes = termination_planes
+        ray_mask = torch.logical_and(opacity.view(-1) <= opc_thre, packed_info[:, 1] == n_samples)
+        total_samples += ray_indices.shape[0]
+    depth = depth / opacity.clamp_min(torch.finfo(torch.float32).eps)
+    return rgb, opacity, depth, total_samples
+
+
+def bench_chunked(nf, dev, peak, n_rays=1 << 18):
+    """The test-time loop on the cfg2 scene (thin shell, step 5e-3) with an analytic field
+    (sigma = 50 inside the shell): this library's fused loop, the same loop spelled with this
+    library's public API, and the reference package on the reference kernels."""
+    import bench as B
+
+    est = nf.OccGridEstimator(B.AABB.tolist(), resolution=B.RES, levels=1).to(dev)
+    est.binaries = torch.from_numpy(B.make_grid()).to(dev)
+    o_np, d_np = B.make_rays(n_rays, 77)
+    o, d = torch.from_numpy(o_np).to(dev), torch.from_numpy(d_np).to(dev)
+
+    def fn(t_starts, t_ends, ray_indices):
+        pos = nf.sample_positions(o, d, ray_indices, t_starts, t_ends)
+        rad = pos.norm(dim=-1)
+        return torch.sigmoid(pos * 3.0), 50.0 * ((rad >= 0.8) & (rad <= 0.9)).float()
+
+    kw = dict(step=B.STEP_SIZE, cone=0.0, early_stop_eps=1e-4, alpha_thre=0.0)
+    fused = lambda: nf.render_image_with_occgrid_test(1024, fn, est, o, d, render_step_size=B.STEP_SIZE,
+                                                      early_stop_eps=1e-4)
+    rgb, opac, depth, total = fused()
+    iters = []
+    nf.render_image_with_occgrid_test(1024, fn, est, o, d, render_step_size=B.STEP_SIZE, early_stop_eps=1e-4,
+                                      _on_chunk=lambda c: iters.append(c["k"]))
+    res = {"rays": n_rays, "samples_marched": int(total), "iterations": len(iters)}
+    t_f = timeit(fused, warm=1, groups=3, reps=1)
+    t_k, names = native_ms(fused, reps=1)
+    t_s = timeit(lambda: spelled_out_loop(nf, est, o, d, fn, **kw), warm=1, groups=3, reps=1)
+    res["fused_loop"] = {"ms": t_f, "kernel_ms": t_k, "native_calls": names, "host_syncs_per_iteration": 1}
+    res["public_api_loop"] = {"ms": t_s, "note": "examples/utils.py:252-425 spelled with this library's public API"}
+    ref = refpkg()
+    if ref is not None:
+        r_est = ref.OccGridEstimator(B.AABB.tolist(), resolution=B.RES, levels=1).to(dev)
+        r_est.binaries = est.binaries.clone()
+        t_r = timeit(lambda: spelled_out_loop(ref, r_est, o, d, fn, **kw), warm=1, groups=3, reps=1)
+        r2 = spelled_out_loop(ref, r_est, o, d, fn, **kw)
+        same = (opac - r2[1]).abs().view(-1) <= 1e-4
+        res["reference_loop"] = {"ms": t_r, "samples_marched": int(r2[3]),
+                                 "note": "the same loop on the reference package and kernels (baseline/_ref, oracle/_ref)"}
+        res["fused_loop"]["speedup_vs_reference_loop"] = t_r / t_f
+        res["fused_loop"]["rays_with_equal_opacity"] = float(same.float().mean())
+        res["fused_loop"]["max_rgb_diff_on_those"] = float((rgb - r2[0]).abs()[same].max())
+    return res
+
+
 # ------------------------------------------------------------------ cfg1 (CPU)
 def cpu_cfg1(steps=8, warmup=2):
     """BASELINE.json configs[0] on the host cores: the reference's batched PyTorch path —

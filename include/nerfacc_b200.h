@@ -310,6 +310,44 @@ NFB_API int nfb_traverse_fill(const nfb_rays_t* rays, const nfb_grid_t* grid,
                               void* scratch, size_t scratch_bytes, nfb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * The test-time rendering loop of the reference's callers (examples/utils.py:252-425,
+ * render_image_with_occgrid_test): per iteration the alive rays march up to k
+ * more samples from their termination planes (traverse_grids(over_allocate=True,
+ * traverse_steps_limit=k, rays_mask=alive, near_planes=termination_planes)), the radiance field is
+ * queried, the chunk is composited behind what the rays already hold (render_weight_from_density
+ * with prefix_trans = 1 - opacity, the alpha_thre filter, accumulate_along_rays_ x3) and rays that
+ * are opaque or did not fill their chunk retire.  Here the loop state — alive list, per-ray near
+ * planes, k — stays on the device: an iteration is nfb_chunk_march, the caller's field, and
+ * nfb_chunk_composite, with ONE host read (the chunk's sample total) in between.
+ *   state: nfb_chunk_state_bytes() device bytes;  plan_host: 2 int64 in pinned (device-visible)
+ *   memory, receives (rays alive, k) of the next chunk whenever a plan is made;
+ *   alive / alive_next: int32 [n_rays] double buffer (alive starts as 0..n_rays-1);
+ *   slot_of: int64 [n_rays], a ray's position in the alive list (starts as 0..n_rays-1);
+ *   sample_info: int64 [n_rays,2], the chunk's packed_info (zero counts for retired rays);
+ *   slot_t_starts/ends: float [n_rays * max(min_samples, 1)] marching slots;
+ *   ray_indices / t_starts / t_ends: the dense chunk the field sees, same capacity. */
+NFB_API size_t nfb_chunk_state_bytes(void);
+NFB_API int nfb_chunk_init(void* state, int64_t n_rays, int32_t min_samples, int64_t* plan_host,
+                           nfb_stream_t stream);
+/* rays->near_planes [n_rays] is read and overwritten in place with the termination planes of the
+ * rays marched; n_alive_max: an upper bound of the alive list's length (sizes the launch);
+ * totals[0] = samples of the chunk.  scratch: nfb_traverse_scratch_bytes(n_rays). */
+NFB_API int nfb_chunk_march(const nfb_rays_t* rays, const nfb_grid_t* grid, const nfb_march_t* march,
+                            const int32_t* alive, int64_t n_alive_max, const void* state,
+                            const int64_t* slot_of, int64_t* sample_info, float* slot_t_starts,
+                            float* slot_t_ends, int64_t* ray_indices, float* t_starts, float* t_ends,
+                            int64_t* totals, void* scratch, size_t scratch_bytes, nfb_stream_t stream);
+/* rgb [n_rays,3], opacity [n_rays], depth [n_rays] accumulate in place; a ray stays alive iff
+ * opacity <= opacity_thre (= 1 - early_stop_eps) and it marched its full k samples; then plans the
+ * next chunk: k = max(min(n_rays / alive, 64), min_samples). */
+NFB_API int nfb_chunk_composite(const int32_t* alive, int32_t* alive_next, int64_t n_alive_max, void* state,
+                                int64_t* sample_info, int64_t* slot_of, const float* t_starts,
+                                const float* t_ends, const float* sigmas, const float* rgbs, int64_t n_rays,
+                                float* rgb, float* opacity, float* depth, float alpha_thre,
+                                float opacity_thre, int32_t min_samples, int64_t* plan_host,
+                                nfb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * Occupancy-grid update (nerfacc/estimators/occ_grid.py:367-404) and visibility compaction
  * (occ_grid.py:216-220).
  */

@@ -106,6 +106,12 @@ _PROTOS = {
     "nfb_traverse_scratch_bytes": [c_i64],
     "nfb_traverse_fill_sampling": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                    c_i64, c_ptr, c_size, c_ptr],
+    "nfb_chunk_state_bytes": [],
+    "nfb_chunk_init": [c_ptr, c_i64, C.c_int32, c_ptr, c_ptr],
+    "nfb_chunk_march": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                        c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
+    "nfb_chunk_composite": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr,
+                            c_ptr, c_f32, c_f32, C.c_int32, c_ptr, c_ptr],
     "nfb_occ_cell_points": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "nfb_occ_ema_update": [c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_i64, c_f32, c_ptr, c_ptr],
     "nfb_occ_binarize_workspace_bytes": [],
@@ -137,6 +143,7 @@ _RESTYPES = {
     "nfb_render_bits_workspace_bytes": C.c_size_t,
     "nfb_head_bits_bytes": C.c_size_t,
     "nfb_occ_binarize_workspace_bytes": C.c_size_t,
+    "nfb_chunk_state_bytes": C.c_size_t,
     "nfb_compact_workspace_bytes": C.c_size_t,
     "nfb_traverse_run_bytes": C.c_size_t,
     "nfb_traverse_scratch_bytes": C.c_size_t,

@@ -1,5 +1,6 @@
 """nerfacc_b200 — B200-native (sm_100a) implementation of nerfacc's rendering hot path behind
 nerfacc's own Python API (reference nerfacc/__init__.py:23-46).  No CPU fallback for packed ops."""
+from .chunked import render_image_with_occgrid_test  # additive: the test-time loop
 from .data_specs import RayIntervals, RaySamples
 from .estimators.occ_grid import OccGridEstimator
 from .estimators.prop_net import PropNetEstimator

@@ -56,7 +56,7 @@ def pdf_loss_rows_ok(q_vals: Tensor, q_cdfs: Tensor, k_vals: Tensor, k_cdfs: Ten
     return (all(t.is_cuda and t.dim() == 2 and t.dtype == torch.float32 for t in ts)
             and q_vals.shape == q_cdfs.shape and k_vals.shape == k_cdfs.shape
             and q_vals.shape[0] == k_vals.shape[0] and q_vals.shape[1] >= 2 and k_vals.shape[1] >= 1
-            and 8 * (2 * k_vals.shape[1] + 3 * q_vals.shape[1]) * 4 <= 200 * 1024
+            and 8 * 3 * k_vals.shape[1] * 4 <= 200 * 1024
             and not q_vals.requires_grad and not q_cdfs.requires_grad and not k_vals.requires_grad)
 
 

@@ -40,6 +40,11 @@ struct RayArgs {
     // re-marches only the rays whose runs overflowed the run buffer)
     const int* __restrict__ ray_list;
     long long n_work;
+    // optional, read by the kernel when it starts (the chunked test-time loop keeps both on the
+    // device so that an iteration needs no host round trip): the length of ray_list (n_work is then
+    // only an upper bound that sizes the launch) and traverse_steps_limit
+    const int* __restrict__ n_work_dev;
+    const int* __restrict__ limit_dev;
 };
 
 // ---------------------------------------------------------------------------------- sinks
@@ -101,7 +106,7 @@ struct SamplingSink {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177
     template <class P>
     __device__ __forceinline__ void one(const P&, float t_last, float t_next, bool, int nS, int) const {
         const long long i = base + nS;
-        ray_indices[i] = r;
+        if (ray_indices) ray_indices[i] = r;
         t_starts[i] = t_last;
         t_ends[i] = t_next;
     }
@@ -182,6 +187,7 @@ struct FillPolicy {
     // where each ray's data starts: info[r * stride]; packed_info (stride 2) or a plain array
     const int64_t* sm_starts; int sm_stride;
     const int64_t* iv_starts; int iv_stride;
+    const int* slot_mul_dev;  // optional: sample starts are slot numbers, times this many samples per slot
     // two-pass: skip rays whose count (info[2r+1]) is zero; single pass: write the counts
     int64_t* sample_info; int64_t* interval_info; bool single_pass;
     float* term;
@@ -204,7 +210,7 @@ struct FillPolicy {
         Sink s = proto;
         s.r = r;
         if constexpr (FULL) { s.sm_base = sm_starts[r * sm_stride]; s.iv_base = iv_starts[r * iv_stride]; }
-        else s.base = sm_starts[r * sm_stride];
+        else s.base = sm_starts[r * sm_stride] * (slot_mul_dev ? (long long)*slot_mul_dev : 1ll);
         return s;
     }
     __device__ __forceinline__ void end(long long r, Sink&, int nS, int nI, float t_last) const {
@@ -237,8 +243,11 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
         *s_nck = common ? make_checkpoints(A.near_s, opt.step_size, s_ck) : 0;
     }
     __syncthreads();
+    MarchOpts o = opt;
+    if (A.limit_dev) o.limit = *A.limit_dev;
+    const long long n_work = A.n_work_dev ? (long long)*A.n_work_dev : (A.ray_list ? A.n_work : A.n_rays);
     march_engine<MIP, DIRECT>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
-                 A.hits, A.ray_list, A.ray_list ? A.n_work : A.n_rays, G, opt, P, s_evt, s_pool, s_ck, *s_nck,
+                 A.hits, A.ray_list, n_work, G, o, P, s_evt, s_pool, s_ck, *s_nck,
                  ray_counter);
 }
 
@@ -494,6 +503,131 @@ __global__ void occ_bounds_kernel(const uint32_t* __restrict__ bits, int n_grids
     }
 }
 
+// ---------------------------------------------------------------------------------- chunked loop
+// The test-time loop of the reference's callers (examples/utils.py:252-425) as three launches per
+// iteration around the user's radiance field, with the loop state (alive list, per-ray near
+// planes, the step limit of the next chunk) kept on the device:
+//   march_kernel (FillPolicy<false>, single pass)  the alive rays march up to k samples from their
+//        termination planes into k-sample slots (k, the list and its length are device values);
+//   chunk_compact_kernel    slots -> the dense, ray-ordered (ray_indices, t_starts, t_ends) the
+//        callback sees (what the reference gets from three boolean-mask selects);
+//   chunk_composite_kernel  weights with prefix_trans = 1 - opacity (volrend.py:312-362), the
+//        alpha_thre filter, rgb / opacity / depth accumulated in place (accumulate_along_rays_ x3),
+//        then the ray's fate: alive iff opacity <= 1 - early_stop_eps and it used its whole chunk
+//        (examples/utils.py:404-411) -> next alive list, its slot number, or a zeroed count;
+//   chunk_plan_kernel       k of the next chunk from the number of rays alive (utils.py:337).
+struct ChunkState {
+    int n_alive;   // length of the current alive list
+    int limit;     // k: samples per ray of the current chunk
+    int n_next;    // rays appended to the next list so far
+    int pad;
+};
+
+__global__ void __launch_bounds__(256)
+chunk_compact_kernel(const int* __restrict__ alive, const ChunkState* __restrict__ st,
+                     const int64_t* __restrict__ sample_info, const float* __restrict__ slot_ts,
+                     const float* __restrict__ slot_te, int64_t* __restrict__ ray_indices,
+                     float* __restrict__ t_starts, float* __restrict__ t_ends) {
+    const int lane = lane_id();
+    const int n_alive = st->n_alive, k = st->limit;
+    for (long long j = (long long)blockIdx.x * 8 + warp_id(); j < n_alive; j += (long long)gridDim.x * 8) {
+        const int r = __ldg(alive + j);
+        const RayChunk c = load_chunk(sample_info, r);
+        const long long src = j * (long long)k;
+        for (int i = lane; i < c.cnt; i += 32) {
+            ray_indices[c.start + i] = r;
+            t_starts[c.start + i] = __ldg(slot_ts + src + i);
+            t_ends[c.start + i] = __ldg(slot_te + src + i);
+        }
+    }
+}
+
+struct ChunkCompositeArgs {
+    const int* alive; int* alive_next; ChunkState* st;
+    int64_t* sample_info; int64_t* slot_of;
+    const float* t_starts; const float* t_ends; const float* sigmas; const float* rgbs;
+    float* rgb; float* opacity; float* depth;
+    float alpha_thre, opc_thre;
+};
+
+__global__ void __launch_bounds__(256) chunk_composite_kernel(const ChunkCompositeArgs p) {
+    const int lane = lane_id();
+    const int n_alive = p.st->n_alive, k = p.st->limit;
+    for (long long j = (long long)blockIdx.x * 8 + warp_id(); j < n_alive; j += (long long)gridDim.x * 8) {
+        const int r = __ldg(p.alive + j);
+        const RayChunk c = load_chunk(p.sample_info, r);
+        const float opac0 = p.opacity[r];
+        const float prefix = __fsub_rn(1.0f, opac0);  // prefix_trans = 1 - opacity[ray_indices]
+        float carry = 0.0f;  // sum of sigma * delta before this round of 32 samples
+        float a_r = 0.0f, a_g = 0.0f, a_b = 0.0f, a_o = 0.0f, a_d = 0.0f;
+        for (int i0 = 0; i0 < c.cnt; i0 += 32) {
+            const int i = i0 + lane;
+            const bool on = i < c.cnt;
+            const long long s = c.start + i;
+            const float ts = on ? __ldg(p.t_starts + s) : 0.0f, te = on ? __ldg(p.t_ends + s) : 0.0f;
+            const float sd = on ? __fmul_rn(__ldg(p.sigmas + s), __fsub_rn(te, ts)) : 0.0f;
+            float x = sd;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const float y = __shfl_up_sync(kFull, x, d);
+                if (lane >= d) x = __fadd_rn(y, x);
+            }
+            const float incl = __fadd_rn(carry, x);
+            float excl = __shfl_up_sync(kFull, incl, 1);
+            if (lane == 0) excl = carry;
+            carry = __shfl_sync(kFull, incl, 31);
+            const float alpha = __fsub_rn(1.0f, expf(-sd));
+            const float T = __fmul_rn(expf(-excl), prefix);
+            float wgt = __fmul_rn(T, alpha);
+            if (!on || (p.alpha_thre > 0.0f && !(alpha >= p.alpha_thre))) wgt = 0.0f;  // utils.py:382-390
+            float v[5];
+            v[0] = on ? __fmul_rn(wgt, __ldg(p.rgbs + 3 * s)) : 0.0f;
+            v[1] = on ? __fmul_rn(wgt, __ldg(p.rgbs + 3 * s + 1)) : 0.0f;
+            v[2] = on ? __fmul_rn(wgt, __ldg(p.rgbs + 3 * s + 2)) : 0.0f;
+            v[3] = wgt;
+            v[4] = __fmul_rn(wgt, __fmul_rn(__fadd_rn(ts, te), 0.5f));  // (t_starts + t_ends) / 2
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) v[q] = __fadd_rn(v[q], __shfl_xor_sync(kFull, v[q], d));
+            }
+            a_r = __fadd_rn(a_r, v[0]); a_g = __fadd_rn(a_g, v[1]); a_b = __fadd_rn(a_b, v[2]);
+            a_o = __fadd_rn(a_o, v[3]); a_d = __fadd_rn(a_d, v[4]);
+        }
+        if (lane == 0) {
+            const float opac = __fadd_rn(opac0, a_o);
+            p.rgb[3 * r] = __fadd_rn(p.rgb[3 * r], a_r);
+            p.rgb[3 * r + 1] = __fadd_rn(p.rgb[3 * r + 1], a_g);
+            p.rgb[3 * r + 2] = __fadd_rn(p.rgb[3 * r + 2], a_b);
+            p.opacity[r] = opac;
+            p.depth[r] = __fadd_rn(p.depth[r], a_d);
+            const bool alive = (opac <= p.opc_thre) && (c.cnt == k);  // utils.py:404-411
+            if (alive) {
+                const int pos = atomicAdd(&p.st->n_next, 1);
+                p.alive_next[pos] = r;
+                p.slot_of[r] = pos;
+            } else {
+                p.sample_info[2 * r + 1] = 0;  // retired: contributes nothing to later chunks' scans
+            }
+        }
+    }
+}
+
+__global__ void chunk_seed_kernel(ChunkState* st, int n_rays) {
+    st->n_alive = 0; st->limit = 0; st->n_next = n_rays; st->pad = 0;
+}
+
+__global__ void chunk_plan_kernel(ChunkState* st, long long n_rays, int min_samples, int64_t* plan_host) {
+    const int n_alive = st->n_next;
+    int k = (int)(n_alive > 0 ? n_rays / n_alive : 64);
+    k = k < 64 ? k : 64;
+    k = k > min_samples ? k : min_samples;  // utils.py:337
+    st->n_alive = n_alive;
+    st->limit = k;
+    st->n_next = 0;
+    if (plan_host) { plan_host[0] = n_alive; plan_host[1] = k; }
+}
+
 static inline unsigned grid_for(long long n, int block, int per_sm = 16) {
     long long b = ceil_div<long long>(n, block);
     const long long cap = (long long)sm_count() * per_sm;
@@ -568,7 +702,7 @@ static RayArgs to_args(const nfb_rays_t* r) {
     a.rays_o = r->rays_o; a.rays_d = r->rays_d; a.rays_mask = r->rays_mask;
     a.near_arr = r->near_planes; a.far_arr = r->far_planes; a.near_s = r->near_plane; a.far_s = r->far_plane;
     a.t_sorted = r->t_sorted; a.t_indices = r->t_indices; a.hits = r->hits; a.n_rays = r->n_rays;
-    a.ray_list = nullptr; a.n_work = 0;
+    a.ray_list = nullptr; a.n_work = 0; a.n_work_dev = nullptr; a.limit_dev = nullptr;
     return a;
 }
 static GridSpec to_grid(const nfb_grid_t* g) {
@@ -834,6 +968,97 @@ NFB_API int nfb_traverse_fill(const nfb_rays_t* rays, const nfb_grid_t* grid,
         if (rc == NFB_OK && totals != nullptr) cudaMemsetAsync(totals + 2, 0, sizeof(int64_t), s);
     }
     return rc;
+}
+
+/* ---- the chunked test-time loop (examples/utils.py:252-425), see the kernels above */
+NFB_API size_t nfb_chunk_state_bytes(void) { return sizeof(nfb::ChunkState); }
+
+NFB_API int nfb_chunk_init(void* state, int64_t n_rays, int32_t min_samples, int64_t* plan_host,
+                           nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(state != nullptr && n_rays >= 0 && n_rays < (1ll << 31), "bad state / n_rays");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // "next" = all rays; the plan kernel turns that into the first chunk
+    chunk_seed_kernel<<<1, 1, 0, s>>>(static_cast<ChunkState*>(state), (int)n_rays);
+    chunk_plan_kernel<<<1, 1, 0, s>>>(static_cast<ChunkState*>(state), n_rays, min_samples, plan_host);
+    count_launch(2);
+    NFB_CHECK_LAUNCH("chunk_init");
+    return NFB_OK;
+}
+
+NFB_API int nfb_chunk_march(const nfb_rays_t* rays, const nfb_grid_t* grid, const nfb_march_t* march,
+                            const int32_t* alive, int64_t n_alive_max, const void* state,
+                            const int64_t* slot_of, int64_t* sample_info, float* slot_t_starts,
+                            float* slot_t_ends, int64_t* ray_indices, float* t_starts, float* t_ends,
+                            int64_t* totals, void* scratch, size_t scratch_bytes, nfb_stream_t stream) {
+    using namespace nfb;
+    int rc = check_common(rays, grid, march);
+    if (rc != NFB_OK) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (rays->n_rays == 0 || n_alive_max <= 0) {
+        if (totals) cudaMemsetAsync(totals, 0, 3 * sizeof(int64_t), s);
+        return NFB_OK;
+    }
+    NFB_CHECK_ARG(alive && state && slot_of && sample_info && slot_t_starts && slot_t_ends && ray_indices && t_starts && t_ends,
+                  "null pointer");
+    NFB_CHECK_ARG(rays->near_planes != nullptr, "the chunked loop keeps per-ray near planes (termination planes) on the device");
+    NFB_CHECK_ARG(n_alive_max <= rays->n_rays, "n_alive_max > n_rays");
+    unsigned long long* counters = counters_of(scratch, scratch_bytes, rays->n_rays);
+    NFB_CHECK_ARG(counters != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
+    const ChunkState* st = static_cast<const ChunkState*>(state);
+    RayArgs A = to_args(rays);
+    A.rays_mask = nullptr;
+    A.ray_list = alive; A.n_work = n_alive_max; A.n_work_dev = &st->n_alive; A.limit_dev = &st->limit;
+    FillPolicy<false> P{};
+    P.rays_mask = nullptr; P.near_arr = A.near_arr; P.near_s = A.near_s;
+    P.sm_starts = slot_of; P.sm_stride = 1; P.slot_mul_dev = &st->limit;
+    P.sample_info = sample_info; P.interval_info = nullptr; P.single_pass = true;
+    P.term = const_cast<float*>(A.near_arr);  // termination planes become the next chunk's near planes, in place
+    P.proto.ray_indices = nullptr; P.proto.t_starts = slot_t_starts; P.proto.t_ends = slot_t_ends;
+    nfb_march_t m2 = *march;
+    m2.traverse_steps_limit = 64;  // (placeholder > 0: the kernel reads the chunk's k from the state)
+    rc = launch_march(A, to_grid(grid), to_opts(&m2), P, counters, s);
+    if (rc != NFB_OK) return rc;
+    rc = launch_ray_scan(sample_info, rays->n_rays, reinterpret_cast<long long*>(totals), scratch, s);
+    if (rc != NFB_OK) return rc;
+    long long b = ceil_div<long long>(n_alive_max, 8);
+    const long long cap = (long long)sm_count() * 16;
+    if (b > cap) b = cap;
+    chunk_compact_kernel<<<(unsigned)b, 256, 0, s>>>(alive, st, sample_info, slot_t_starts, slot_t_ends, ray_indices,
+                                                    t_starts, t_ends);
+    count_launch();
+    NFB_CHECK_LAUNCH("chunk_march");
+    return NFB_OK;
+}
+
+NFB_API int nfb_chunk_composite(const int32_t* alive, int32_t* alive_next, int64_t n_alive_max, void* state,
+                                int64_t* sample_info, int64_t* slot_of, const float* t_starts,
+                                const float* t_ends, const float* sigmas, const float* rgbs, int64_t n_rays,
+                                float* rgb, float* opacity, float* depth, float alpha_thre,
+                                float opacity_thre, int32_t min_samples, int64_t* plan_host,
+                                nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_alive_max >= 0 && n_rays >= 0, "negative size");
+    NFB_CHECK_ARG(state != nullptr, "null state");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (n_alive_max > 0) {
+        NFB_CHECK_ARG(alive && alive_next && sample_info && slot_of && t_starts && t_ends && sigmas && rgbs && rgb &&
+                      opacity && depth, "null pointer");
+        ChunkCompositeArgs a{};
+        a.alive = alive; a.alive_next = alive_next; a.st = static_cast<ChunkState*>(state);
+        a.sample_info = sample_info; a.slot_of = slot_of; a.t_starts = t_starts; a.t_ends = t_ends;
+        a.sigmas = sigmas; a.rgbs = rgbs; a.rgb = rgb; a.opacity = opacity; a.depth = depth;
+        a.alpha_thre = alpha_thre; a.opc_thre = opacity_thre;
+        long long b = ceil_div<long long>(n_alive_max, 8);
+        const long long cap = (long long)sm_count() * 16;
+        if (b > cap) b = cap;
+        chunk_composite_kernel<<<(unsigned)b, 256, 0, s>>>(a);
+        count_launch();
+    }
+    chunk_plan_kernel<<<1, 1, 0, s>>>(static_cast<ChunkState*>(state), n_rays, min_samples, plan_host);
+    count_launch();
+    NFB_CHECK_LAUNCH("chunk_composite");
+    return NFB_OK;
 }
 
 }  // extern "C"

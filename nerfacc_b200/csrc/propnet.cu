@@ -13,8 +13,8 @@
 //   pdf_loss_{fwd,bwd}           searchsorted of the query edges in the key edges, envelope mass
 //                                w_outer, loss = clip(w - w_outer, 0)^2 / (w + eps) per query bin;
 //                                backward writes the dense gradient row of cdfs_key without atomics
-//                                (the ids are monotone along the row, so every key edge sums a
-//                                contiguous range of query bins).
+//                                (the ids are monotone along the row, so the bins that hit one key
+//                                edge sit in neighbouring lanes: a segmented shuffle sum).
 // Elementwise arithmetic is the reference's torch sequence op for op (round-to-nearest each).
 #include "common.cuh"
 
@@ -122,14 +122,6 @@ cdf_from_density_bwd_kernel(const float* __restrict__ t_vals, const float* __res
 }
 
 // ------------------------------------------------------------------ proposal loss
-__device__ __forceinline__ int upper_bound_s(const float* data, int lo, int hi, float val) {
-    while (lo < hi) {
-        const int mid = lo + ((hi - lo) >> 1);
-        if (!(data[mid] > val)) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
 struct PdfLossArgs {
     const float* q_vals;   // [R, Q]   query edges
     const float* q_cdfs;   // [R, Q]
@@ -143,79 +135,109 @@ struct PdfLossArgs {
     float eps;
 };
 
-// per warp in shared memory: key vals [K], key cdfs [K], then (backward) d [Q], left [Q], right [Q]
+// A CTA owns kRowWarps consecutive rays: their key rows are one contiguous span, staged with
+// block-wide 128-bit loads; then one warp per ray.  Query edges are taken 32 at a time with a
+// stride of 31, so that lane l holds edge e0 + l and bin e0 + l (l < 31) finds its right edge's id
+// in the next lane.  The search is the fixed-trip, branch-free upper_bound of pdf.cu.
+// Backward: every bin's +-d goes to the key edge it gathered from; the ids are non-decreasing along
+// the row, so lanes that hit the same edge are neighbours: a segmented shuffle sum, one writer per
+// edge, rows accumulated in shared memory in a fixed order (deterministic) and written once.
+// Shared memory: [kRowWarps][K] key vals, [kRowWarps][K] key cdfs, (backward) [kRowWarps][K] gradient rows.
 template <bool BWD>
 __global__ void __launch_bounds__(kRowWarps * 32) pdf_loss_kernel(const PdfLossArgs p) {
     extern __shared__ float s_loss[];
-    const int lane = lane_id(), w = warp_id();
+    const int lane = lane_id(), w = warp_id(), tid = threadIdx.x;
     const int Q = p.Q, K = p.K, last = K - 1, nb = Q - 1;
-    const int per_warp = 2 * K + (BWD ? 3 * Q : 0);
-    float* s_kv = s_loss + (size_t)w * per_warp;
-    float* s_kc = s_kv + K;
-    float* s_d = s_kc + K;                                   // [nb] -dloss/dw_outer * g
-    int* s_left = reinterpret_cast<int*>(s_d + Q);           // [nb] ids_left of edge i
-    int* s_right = s_left + Q;                               // [nb] ids_right of edge i + 1
-    for (long long r = (long long)blockIdx.x * kRowWarps + w; r < p.n_rays; r += (long long)gridDim.x * kRowWarps) {
-        const float* __restrict__ kv = p.k_vals + r * K;
-        const float* __restrict__ kc = p.k_cdfs + r * K;
-        for (int i = lane; i < K; i += 32) { s_kv[i] = ldg_stream(kv + i); s_kc[i] = ldg_stream(kc + i); }
-        __syncwarp();
-        const float* __restrict__ qv = p.q_vals + r * Q;
-        const float* __restrict__ qc = p.q_cdfs + r * Q;
-        // query edge i = i0 + lane; bin i pairs left(edge i) with right(edge i + 1)
-        for (int i0 = 0; i0 < nb; i0 += 32) {
-            const int i = i0 + lane;
-            const bool on = i < Q;  // edges up to nb are needed (edge nb only for its right id)
-            float c_lo = 0.0f;
-            int left = 0, right = 0;
-            if (on) {
-                const float v = __ldg(qv + i);
-                c_lo = __ldg(qc + i);
-                const int q = upper_bound_s(s_kv, 0, last, v);  // csrc/pdf.cu:245-286
-                left = max(min(q - 1, last), 0);
-                right = max(min(q, last), 0);
+    float* s_kv = s_loss;
+    float* s_kc = s_kv + kRowWarps * K;
+    float* s_g = s_kc + kRowWarps * K;
+    int top = 1;  // largest power of two <= max(last, 1)
+    while (2 * top <= last) top <<= 1;
+    const long long n_tiles = (p.n_rays + kRowWarps - 1) / kRowWarps;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long r0 = tile * kRowWarps;
+        const int rays = (int)((p.n_rays - r0 < kRowWarps) ? (p.n_rays - r0) : kRowWarps);
+        const float* __restrict__ gv = p.k_vals + r0 * K;
+        const float* __restrict__ gc = p.k_cdfs + r0 * K;
+        const int total = rays * K;
+        if (((reinterpret_cast<uintptr_t>(gv) | reinterpret_cast<uintptr_t>(gc)) & 15u) == 0) {
+            const int n4 = total >> 2;
+            for (int i = tid; i < n4; i += kRowWarps * 32) {
+                reinterpret_cast<float4*>(s_kv)[i] = ldg_stream4(gv + 4 * i);
+                reinterpret_cast<float4*>(s_kc)[i] = ldg_stream4(gc + 4 * i);
             }
-            // the next edge's right id and cdf: from the next lane, lane 31 looks its own up
-            int right_n = __shfl_down_sync(kFull, right, 1);
-            float c_hi = __shfl_down_sync(kFull, c_lo, 1);
-            if (lane == 31 && i + 1 < Q) {
-                const float v = __ldg(qv + i + 1);
-                c_hi = __ldg(qc + i + 1);
-                right_n = max(min(upper_bound_s(s_kv, 0, last, v), last), 0);
-            }
-            if (i < nb) {
-                const float wq = __fsub_rn(c_hi, c_lo);                           // prop_net.py:244
-                const float w_outer = __fsub_rn(s_kc[right_n], s_kc[left]);       // :252-254
-                const float c = fmaxf(__fsub_rn(wq, w_outer), 0.0f);              // clip(w - w_outer, min=0)
-                const float den = __fadd_rn(wq, p.eps);
-                if (!BWD) {
-                    stg_stream(p.loss + r * nb + i, __fdiv_rn(__fmul_rn(c, c), den));  // ** 2 / (w + eps)
-                } else {
-                    // autograd of the above: g / den, times 2 c (pow), through clip (c > 0) and the minus
-                    const float gl = ldg_stream(p.g_loss + r * nb + i);
-                    s_d[i] = __fmul_rn(__fdiv_rn(gl, den), __fmul_rn(2.0f, c));
-                    s_left[i] = left;
-                    s_right[i] = right_n;
+            for (int i = 4 * n4 + tid; i < total; i += kRowWarps * 32) { s_kv[i] = ldg_stream(gv + i); s_kc[i] = ldg_stream(gc + i); }
+        } else {
+            for (int i = tid; i < total; i += kRowWarps * 32) { s_kv[i] = ldg_stream(gv + i); s_kc[i] = ldg_stream(gc + i); }
+        }
+        if (BWD)
+            for (int i = tid; i < total; i += kRowWarps * 32) s_g[i] = 0.0f;
+        __syncthreads();
+        if (w < rays) {
+            const long long r = r0 + w;
+            const float* kv = s_kv + w * K;
+            const float* kc = s_kc + w * K;
+            float* gk = s_g + w * K;
+            const float* __restrict__ qv = p.q_vals + r * Q;
+            const float* __restrict__ qc = p.q_cdfs + r * Q;
+            for (int e0 = 0; e0 < nb; e0 += 31) {
+                const int e = e0 + lane;  // my edge; my bin if lane < 31
+                const bool on = e < Q;
+                const float v = on ? __ldg(qv + e) : 0.0f;
+                const float c_lo = on ? __ldg(qc + e) : 0.0f;
+                // ids of nfb_searchsorted (csrc/pdf.cu:245-286): q = upper_bound(key[0..last), v)
+                int qq = 0;
+                if (last > 0) {
+                    for (int st = top; st > 0; st >>= 1) {
+                        const int idx = qq + st;
+                        const float c = kv[min(idx, last) - 1];
+                        qq = (idx <= last && !(c > v)) ? idx : qq;
+                    }
+                }
+                const int left = max(qq - 1, 0), right = qq;  // (qq <= last)
+                const int right_n = __shfl_down_sync(kFull, right, 1);
+                const float c_hi = __shfl_down_sync(kFull, c_lo, 1);
+                const bool bin = lane < 31 && e < nb;
+                float d = 0.0f;
+                if (bin) {
+                    const float wq = __fsub_rn(c_hi, c_lo);                        // prop_net.py:244
+                    const float w_outer = __fsub_rn(kc[right_n], kc[left]);        // :252-254
+                    const float c = fmaxf(__fsub_rn(wq, w_outer), 0.0f);           // clip(w - w_outer, min=0)
+                    const float den = __fadd_rn(wq, p.eps);
+                    if (!BWD) {
+                        stg_stream(p.loss + r * nb + e, __fdiv_rn(__fmul_rn(c, c), den));  // ** 2 / (w + eps)
+                    } else {
+                        // autograd of the above: g / den, times 2 c (pow), through clip and the minus
+                        d = __fmul_rn(__fdiv_rn(ldg_stream(p.g_loss + r * nb + e), den), __fmul_rn(2.0f, c));
+                    }
+                }
+                if (BWD) {
+                    // -d to cdfs_key[right id of the bin's right edge], +d to cdfs_key[left id of its left edge]
+#pragma unroll
+                    for (int pass = 0; pass < 2; ++pass) {
+                        const int id = bin ? (pass == 0 ? right_n : left) : -1 - lane;
+                        float x = pass == 0 ? -d : d;
+#pragma unroll
+                        for (int dd = 1; dd < 32; dd <<= 1) {
+                            const float y = __shfl_up_sync(kFull, x, dd);
+                            const int idy = __shfl_up_sync(kFull, id, dd);
+                            if (lane >= dd && idy == id) x = __fadd_rn(y, x);
+                        }
+                        const int idn = __shfl_down_sync(kFull, id, 1);
+                        // (one writer per edge and pass when the query edges are sorted; atomic so that
+                        // unsorted input cannot lose an update)
+                        if (bin && (lane == 31 || idn != id)) atomicAdd(gk + id, x);
+                        __syncwarp();
+                    }
                 }
             }
-        }
-        if (BWD) {
-            __syncwarp();
-            // g_k_cdfs[k] = -sum_{i: right_i == k} d_i + sum_{i: left_i == k} d_i ; both id rows are
-            // non-decreasing in i: each k owns one contiguous range of each
-            float* __restrict__ gk = p.g_k_cdfs + r * K;
-            for (int k = lane; k < K; k += 32) {
-                float acc = 0.0f;
-                int lo = 0, hi = nb;
-                while (lo < hi) { const int mid = (lo + hi) >> 1; if (s_right[mid] < k) lo = mid + 1; else hi = mid; }
-                for (int i = lo; i < nb && s_right[i] == k; ++i) acc = __fsub_rn(acc, s_d[i]);
-                lo = 0; hi = nb;
-                while (lo < hi) { const int mid = (lo + hi) >> 1; if (s_left[mid] < k) lo = mid + 1; else hi = mid; }
-                for (int i = lo; i < nb && s_left[i] == k; ++i) acc = __fadd_rn(acc, s_d[i]);
-                stg_stream(gk + k, acc);
+            if (BWD) {
+                __syncwarp();
+                float* __restrict__ out = p.g_k_cdfs + r * K;
+                for (int k = lane; k < K; k += 32) stg_stream(out + k, gk[k]);
             }
         }
-        __syncwarp();
+        __syncthreads();
     }
 }
 
@@ -272,13 +294,13 @@ NFB_API int nfb_cdf_from_density_bwd(const float* t_vals, const float* sigmas, c
 
 static int launch_pdf_loss(bool bwd, const nfb::PdfLossArgs& a, cudaStream_t st) {
     using namespace nfb;
-    const size_t smem = (size_t)kRowWarps * (2 * a.K + (bwd ? 3 * a.Q : 0)) * sizeof(float);
+    const size_t smem = (size_t)kRowWarps * a.K * (bwd ? 3 : 2) * sizeof(float);
     if (smem > 200 * 1024) {
-        set_error("pdf_loss: rows too long for shared memory (K = %d, Q = %d)", a.K, a.Q);
+        set_error("pdf_loss: rows too long for shared memory (K = %d)", a.K);
         return NFB_ERR_INVALID_ARGUMENT;
     }
     long long blocks = ceil_div<long long>(a.n_rays, kRowWarps);
-    const long long cap = (long long)sm_count() * 64;
+    const long long cap = (long long)sm_count() * 1024;
     if (blocks > cap) blocks = cap;
     if (bwd) {
         if (smem > 48 * 1024) cudaFuncSetAttribute(pdf_loss_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
