@@ -611,6 +611,7 @@ def spelled_out_loop(pkg, est, o, d, fn, step, cone, early_stop_eps, alpha_thre,
     (this library, or the reference package on the reference kernels)."""
     n = o.shape[0]
     dev = o.device
+    acc_ = getattr(pkg, "accumulate_along_rays_", None) or pkg.volrend.accumulate_along_rays_
     opacity = torch.zeros((n, 1), device=dev)
     depth = torch.zeros((n, 1), device=dev)
     rgb = torch.zeros((n, 3), device=dev)
@@ -648,9 +649,9 @@ def spelled_out_loop(pkg, est, o, d, fn, step, cone, early_stop_eps, alpha_thre,
             vis = alphas >= alpha_thre
             ray_indices, rgbs, weights, t_starts, t_ends = (ray_indices[vis], rgbs[vis], weights[vis],
                                                             t_starts[vis], t_ends[vis])
-        pkg.accumulate_along_rays_(weights, values=rgbs, ray_indices=ray_indices, outputs=rgb)
-        pkg.accumulate_along_rays_(weights, values=None, ray_indices=ray_indices, outputs=opacity)
-        pkg.accumulate_along_rays_(weights, values=(t_starts + t_ends)[..., None] / 2.0, ray_indices=ray_indices,
+        acc_(weights, values=rgbs, ray_indices=ray_indices, outputs=rgb)
+        acc_(weights, values=None, ray_indices=ray_indices, outputs=opacity)
+        acc_(weights, values=(t_starts + t_ends)[..., None] / 2.0, ray_indices=ray_indices,
                                    outputs=depth)
         near_planes = termination_planes
         ray_mask = torch.logical_and(opacity.view(-1) <= opc_thre, packed_info[:, 1] == n_samples)

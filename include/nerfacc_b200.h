@@ -283,13 +283,24 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
  * same buffer, expands them warp-cooperatively instead of marching a second time. */
 NFB_API size_t nfb_traverse_run_bytes(int64_t n_rays);
 
+/* The run-buffer part of pass 2 alone, for outputs that hold `capacity` samples (writes past
+ * them are dropped): lets a caller that remembers the previous step's total expand the runs
+ * BEFORE it reads this step's totals back, so the device does not idle during that host round
+ * trip; if the total turns out larger than `capacity` the caller runs nfb_traverse_fill_sampling
+ * on exact buffers instead. */
+NFB_API int nfb_traverse_expand(int64_t n_rays, const int64_t* sample_info, const void* run_buf,
+                                int64_t capacity, int64_t* ray_indices, float* t_starts, float* t_ends,
+                                void* scratch, size_t scratch_bytes, nfb_stream_t stream);
+
 /* Pass 2, OccGridEstimator.sampling outputs (estimators/occ_grid.py:174-177): for every sample,
- * in packed order, ray_indices, t_starts (= left edge) and t_ends (= right edge). */
+ * in packed order, ray_indices, t_starts (= left edge) and t_ends (= right edge).
+ * n_overflowed = totals[2] of pass 1; or, after nfb_traverse_expand has expanded the runs,
+ * -(totals[2]) - 1 (< 0) to march only the rays whose runs overflowed the buffer. */
 NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                        const nfb_march_t* march, const int64_t* sample_info,
                                        int64_t* ray_indices, float* t_starts, float* t_ends,
                                        const void* run_buf /* or NULL */,
-                                       int64_t n_overflowed /* totals[2] of pass 1; < 0: unknown */,
+                                       int64_t n_overflowed,
                                        void* scratch, size_t scratch_bytes, nfb_stream_t stream);
 
 /* Pass 2, traverse_grids outputs (csrc/grid.cu:445-470): interval edges {vals, ray_indices,

@@ -104,6 +104,7 @@ _PROTOS = {
     "nfb_traverse_count": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                            c_size, c_ptr, c_size, c_ptr],
     "nfb_traverse_scratch_bytes": [c_i64],
+    "nfb_traverse_expand": [c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_traverse_fill_sampling": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                    c_i64, c_ptr, c_size, c_ptr],
     "nfb_chunk_state_bytes": [],

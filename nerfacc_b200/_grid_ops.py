@@ -116,15 +116,19 @@ class Marcher:
         self.march = _C.March(float(step_size), float(cone_angle), int(limit))
         self.run_buf: Optional[Tensor] = None
         self.n_overflowed = -1
+        self._spec: Optional[Tuple[Tensor, Tensor, Tensor]] = None  # outputs expanded ahead of the read-back
 
     def _scratch(self) -> Tensor:
         return _C.scratch(self.dev, int(_C.lib().nfb_traverse_scratch_bytes(self.n_rays)), "ray")
 
-    def count(self, want_intervals: bool, want_term: bool, want_runs: bool = False):
+    def count(self, want_intervals: bool, want_term: bool, want_runs: bool = False, expand_capacity: int = 0):
         """Pass 1.  Returns (sample_info, interval_info|None, termination|None, n_samples, n_edges);
         synchronises the stream once to learn the totals (the only host sync of a traversal).
         With `want_runs` (constant-dt marching only) the pass also records each ray's sample runs
-        so that fill_sampling() can expand them instead of marching again."""
+        so that fill_sampling() can expand them instead of marching again.  With `expand_capacity`
+        (the caller's guess of the total, e.g. the previous step's plus a margin) the runs are
+        expanded into buffers of that many samples BEFORE the totals are read back, so the device
+        works through the host round trip; fill_sampling() keeps them if the total fits."""
         dev, n = self.dev, self.n_rays
         sample_info = torch.empty((n, 2), dtype=torch.long, device=dev)
         interval_info = torch.empty((n, 2), dtype=torch.long, device=dev) if want_intervals else None
@@ -144,12 +148,36 @@ class Marcher:
                 sc.numel(), None if self.run_buf is None else self.run_buf.data_ptr(),
                 0 if self.run_buf is None else self.run_buf.numel(), _C.stream_ptr(dev))
             _C.check(rc, "traverse_count")
+            self._spec = None
+            if self.run_buf is not None and expand_capacity > 0:
+                cap = int(expand_capacity)
+                spec = (torch.empty((cap,), dtype=torch.long, device=dev),
+                        torch.empty((cap,), dtype=torch.float32, device=dev),
+                        torch.empty((cap,), dtype=torch.float32, device=dev))
+                rc = _C.lib().nfb_traverse_expand(n, sample_info.data_ptr(), self.run_buf.data_ptr(), cap,
+                                                  spec[0].data_ptr(), spec[1].data_ptr(), spec[2].data_ptr(),
+                                                  sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
+                _C.check(rc, "traverse_expand")
+                self._spec = spec
             torch.cuda.current_stream(dev).synchronize()
         self.n_overflowed = int(totals[2])
         return sample_info, interval_info, term, int(totals[0]), int(totals[1])
 
     def fill_sampling(self, sample_info: Tensor, n_samples: int):
         dev = self.dev
+        spec, self._spec = self._spec, None
+        if spec is not None and n_samples <= spec[0].shape[0]:
+            # the runs were expanded while the totals travelled to the host
+            ray_indices, t_starts, t_ends = (t[:n_samples] for t in spec)
+            if n_samples > 0 and self.n_overflowed > 0:  # rays whose runs did not fit the buffer: march those
+                with torch.cuda.device(dev):
+                    sc = self._scratch()
+                    rc = _C.lib().nfb_traverse_fill_sampling(
+                        C.byref(self.rays), C.byref(self.grid), C.byref(self.march), sample_info.data_ptr(),
+                        ray_indices.data_ptr(), t_starts.data_ptr(), t_ends.data_ptr(), self.run_buf.data_ptr(),
+                        -self.n_overflowed - 1, sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
+                _C.check(rc, "traverse_fill_sampling")
+            return ray_indices, t_starts, t_ends
         ray_indices = torch.empty((n_samples,), dtype=torch.long, device=dev)
         t_starts = torch.empty((n_samples,), dtype=torch.float32, device=dev)
         t_ends = torch.empty((n_samples,), dtype=torch.float32, device=dev)

@@ -265,7 +265,9 @@ __global__ void __launch_bounds__(kExpandWarps * 32)
 traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info,
                        const Run* __restrict__ runs, const int* __restrict__ n_runs,
                        int64_t* __restrict__ ray_indices, float* __restrict__ t_starts,
-                       float* __restrict__ t_ends, bool vec_ok) {
+                       float* __restrict__ t_ends, bool vec_ok, long long capacity) {
+    // (capacity: the outputs hold that many samples — a speculative launch, made before the host knows
+    // the total, must not write past them; the caller re-runs with exact buffers if the total is larger)
     // the warp's runs in sample order: first sample (relative to the warp's first), length, t0, q, ray
     __shared__ int s_start[kExpandWarps][kExpandRuns];
     __shared__ int s_n[kExpandWarps][kExpandRuns];
@@ -344,6 +346,11 @@ traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info
                         }
                     }
                 }
+                if (i0 + 4 > capacity) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        if (i0 + c >= capacity) ok &= ~(1u << c);
+                }
                 if (ok == 0xfu && vec_ok) {
                     *reinterpret_cast<longlong2*>(ray_indices + i0) = make_longlong2(ri[0], ri[1]);
                     *reinterpret_cast<longlong2*>(ray_indices + i0 + 2) = make_longlong2(ri[2], ri[3]);
@@ -369,7 +376,7 @@ traverse_expand_kernel(long long n_rays, const int64_t* __restrict__ sample_info
 __global__ void __launch_bounds__(kExpandWarps * 32)
 traverse_expand_pool_kernel(const int64_t* __restrict__ sample_info, const RunPool pool,
                             int64_t* __restrict__ ray_indices, float* __restrict__ t_starts,
-                            float* __restrict__ t_ends) {
+                            float* __restrict__ t_ends, long long capacity) {
     unsigned long long cnt = *pool.cursor;
     if (cnt > pool.cap) cnt = pool.cap;
     const int lane = lane_id();
@@ -379,7 +386,7 @@ traverse_expand_pool_kernel(const int64_t* __restrict__ sample_info, const RunPo
         const Run run = *reinterpret_cast<const Run*>(&raw);
         const long long rb = __ldg(pool.ray + e);
         long long i = load_chunk(sample_info, rb).start + run.s0 + lane;
-        for (int j = lane; j < run.n; j += 32, i += 32) {
+        for (int j = lane; j < run.n && i < capacity; j += 32, i += 32) {
             ray_indices[i] = rb;
             t_starts[i] = __fmaf_rn((float)j, run.q, run.t0);
             t_ends[i] = __fmaf_rn((float)(j + 1), run.q, run.t0);
@@ -872,6 +879,42 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
     return NFB_OK;
 }
 
+// the expansion of the run buffer: traverse_expand_kernel + the pooled runs
+static int launch_expand(int64_t n_rays, const int64_t* sample_info, const void* run_buf, int64_t* ray_indices,
+                         float* t_starts, float* t_ends, long long capacity, void* scratch, size_t scratch_bytes,
+                         cudaStream_t s) {
+    using namespace nfb;
+    NFB_CHECK_ARG(aligned16(run_buf) && aligned16(sample_info), "run buffer / sample_info must be 16-byte aligned");
+    const Run* runs = static_cast<const Run*>(run_buf);
+    const int* n_runs = reinterpret_cast<const int*>(runs + n_rays * kRunSlots);
+    const long long groups = (n_rays + 31) / 32;
+    traverse_expand_kernel<<<grid_for(groups, kExpandWarps, 32), kExpandWarps * 32, 0, s>>>(
+        n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends,
+        aligned16(ray_indices) && aligned16(t_starts) && aligned16(t_ends), capacity);
+    count_launch();
+    NFB_CHECK_LAUNCH("traverse_expand");
+    // pooled runs; the count stays on the device (the kernel reads the cursor)
+    unsigned long long* ctr = counters_of(scratch, scratch_bytes, n_rays);
+    NFB_CHECK_ARG(ctr != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(n_rays));
+    const RunPool pool = pool_of(const_cast<void*>(run_buf), n_rays, ctr + 2);
+    traverse_expand_pool_kernel<<<sm_count() * 4, kExpandWarps * 32, 0, s>>>(sample_info, pool, ray_indices, t_starts,
+                                                                             t_ends, capacity);
+    count_launch();
+    NFB_CHECK_LAUNCH("traverse_expand_pool");
+    return NFB_OK;
+}
+
+NFB_API int nfb_traverse_expand(int64_t n_rays, const int64_t* sample_info, const void* run_buf,
+                                int64_t capacity, int64_t* ray_indices, float* t_starts, float* t_ends,
+                                void* scratch, size_t scratch_bytes, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_rays >= 0 && capacity >= 0, "negative size");
+    if (n_rays == 0 || capacity == 0) return NFB_OK;
+    NFB_CHECK_ARG(sample_info && run_buf && ray_indices && t_starts && t_ends, "null pointer");
+    return launch_expand(n_rays, sample_info, run_buf, ray_indices, t_starts, t_ends, capacity, scratch, scratch_bytes,
+                         static_cast<cudaStream_t>(stream));
+}
+
 NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                        const nfb_march_t* march, const int64_t* sample_info,
                                        int64_t* ray_indices, float* t_starts, float* t_ends,
@@ -885,32 +928,23 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     RayArgs A = to_args(rays);
     A.rays_mask = nullptr;
-    const bool expand = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle == 0.0f;
-    const int* n_runs = nullptr;
-    if (expand) {
-        NFB_CHECK_ARG(aligned16(run_buf) && aligned16(sample_info), "run buffer / sample_info must be 16-byte aligned");
-        const Run* runs = static_cast<const Run*>(run_buf);
-        n_runs = reinterpret_cast<const int*>(runs + rays->n_rays * kRunSlots);
-        const long long groups = (rays->n_rays + 31) / 32;
-        traverse_expand_kernel<<<grid_for(groups, kExpandWarps, 32), kExpandWarps * 32, 0, s>>>(
-            rays->n_rays, sample_info, runs, n_runs, ray_indices, t_starts, t_ends,
-            aligned16(ray_indices) && aligned16(t_starts) && aligned16(t_ends));
-        count_launch();
-        NFB_CHECK_LAUNCH("traverse_expand");
-        {   // pooled runs; the count stays on the device (the kernel reads the cursor)
-            unsigned long long* ctr = counters_of(scratch, scratch_bytes, rays->n_rays);
-            NFB_CHECK_ARG(ctr != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(rays->n_rays));
-            const RunPool pool = pool_of(const_cast<void*>(run_buf), rays->n_rays, ctr + 2);
-            traverse_expand_pool_kernel<<<sm_count() * 4, kExpandWarps * 32, 0, s>>>(
-                sample_info, pool, ray_indices, t_starts, t_ends);
-            count_launch();
-            NFB_CHECK_LAUNCH("traverse_expand_pool");
+    const bool have_runs = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle == 0.0f;
+    if (have_runs) {
+        // n_overflowed < 0: nfb_traverse_expand has expanded the runs already; march only the
+        // -n_overflowed - 1 rays that overflowed
+        const bool expanded = n_overflowed < 0;
+        if (expanded) n_overflowed = -n_overflowed - 1;
+        else {
+            rc = launch_expand(rays->n_rays, sample_info, run_buf, ray_indices, t_starts, t_ends,
+                               (long long)1 << 62, scratch, scratch_bytes, s);
+            if (rc != NFB_OK) return rc;
         }
         if (n_overflowed == 0) return NFB_OK;
-        // the few rays with more than kRunSlots runs: re-march exactly those (the count pass
-        // left their ids in the overflow list)
+        // the few rays with more than kRunSlots runs and no room in the pool: re-march exactly
+        // those (the count pass left their ids in the overflow list)
         NFB_CHECK_ARG(n_overflowed > 0 && n_overflowed <= rays->n_rays, "bad n_overflowed");
-        A.ray_list = n_runs + rays->n_rays;
+        const Run* runs = static_cast<const Run*>(run_buf);
+        A.ray_list = reinterpret_cast<const int*>(runs + rays->n_rays * kRunSlots) + rays->n_rays;
         A.n_work = n_overflowed;
     }
     unsigned long long* counters = counters_of(scratch, scratch_bytes, rays->n_rays);

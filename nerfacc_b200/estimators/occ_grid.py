@@ -83,6 +83,7 @@ class OccGridEstimator(AbstractEstimator):
             "binaries", torch.zeros([levels] + resolution.tolist(), dtype=torch.bool)
         )
         self._occ_mean_cache: Optional[Tuple[int, int, float]] = None
+        self._count_hint: dict = {}  # n_rays -> samples marched by the last sampling() call of that size
         # sharded updates (opt-in, see shard_updates): (process group | None, world, rank, seed)
         self._shard: Optional[Tuple[object, int, int, int]] = None
         self._update_count = 0
@@ -174,7 +175,13 @@ class OccGridEstimator(AbstractEstimator):
 
         marcher = Marcher(rays_o, rays_d, self.binaries, self.aabbs, near, far,
                           render_step_size, cone_angle, -1)
-        packed_info, _, _, n_samples, _ = marcher.count(False, False, want_runs=True)
+        # A trainer's sample count drifts slowly from step to step: expand into buffers sized from the
+        # previous call (+ 6 %) while the exact total is on its way to the host; a total that does not
+        # fit is expanded again into exact buffers (results are the same either way).
+        hint = self._count_hint.get(marcher.n_rays, 0)
+        packed_info, _, _, n_samples, _ = marcher.count(
+            False, False, want_runs=True, expand_capacity=(hint + hint // 16 + 4096) if hint > 0 else 0)
+        self._count_hint[marcher.n_rays] = n_samples
         ray_indices, t_starts, t_ends = marcher.fill_sampling(packed_info, n_samples)
         mark_canonical(packed_info, total=n_samples)
         remember_packed_info(ray_indices, packed_info, marcher.n_rays)

@@ -501,3 +501,38 @@ def test_mark_invisible_cells_many_cameras_vs_reference_package(device):
     before = ours.occs.clone()
     ours.mark_invisible_cells(K[:1], c2w[:1], 64, 48, near_plane=0.0)
     assert bool((ours.occs[before == -1] == -1).all())
+
+
+def test_sampling_expands_ahead_of_the_count_readback(device):
+    """From the second call on, sampling() expands the runs into buffers sized from the previous
+    call's total before this call's total has reached the host (nfb_traverse_expand).  Results must
+    be the same as the first (exact-size) call; a total that outgrows the guess, a shrinking one, and
+    rays whose runs overflow the run buffer all take their fallbacks."""
+    import nerfacc_b200 as nf
+
+    rng = np.random.default_rng(7)
+    n_rays, res = 20000, 64
+    o = rng.standard_normal((n_rays, 3)); o = (3.0 * o / np.linalg.norm(o, axis=-1, keepdims=True)).astype(np.float32)
+    d = -o + 0.4 * rng.standard_normal((n_rays, 3)); d = (d / np.linalg.norm(d, axis=-1, keepdims=True)).astype(np.float32)
+    to, td = torch.from_numpy(o).to(device), torch.from_numpy(d).to(device)
+    aabb = np.array([[-1, -1, -1, 1, 1, 1]], np.float32)
+    sparse = rng.random((1, res, res, res)) < 0.02
+    dense = rng.random((1, res, res, res)) < 0.45   # dozens of runs per ray: run-buffer overflow
+    est = nf.OccGridEstimator(aabb[0].tolist(), resolution=res).to(device)
+
+    def check(bins, step):
+        est.binaries = torch.from_numpy(bins).to(device)
+        ri, ts, te = est.sampling(to, td, render_step_size=step)
+        r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, aabb, render_step_size=step)
+        assert ri.shape[0] == r_ri.shape[0]
+        assert (ri.cpu().numpy() == r_ri).all() and (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+        assert (nf.pack_info(ri, n_rays).cpu().numpy() == r_pi).all()
+        return ri.shape[0]
+
+    a = check(sparse, 0.01)       # first call: no guess yet
+    assert est._count_hint[n_rays] == a
+    assert check(sparse, 0.01) == a   # guess fits: speculative buffers kept
+    b = check(dense, 0.01)        # total far above the guess: exact re-expansion, overflowed rays re-marched
+    assert b > 4 * a
+    assert check(dense, 0.01) == b    # guess fits, rays overflow the run buffer: only those are marched again
+    assert check(sparse, 0.02) < a    # shrinking total
