@@ -149,7 +149,11 @@ class Marcher:
                 0 if self.run_buf is None else self.run_buf.numel(), _C.stream_ptr(dev))
             _C.check(rc, "traverse_count")
             self._spec = None
+            counted = None
             if self.run_buf is not None and expand_capacity > 0:
+                # the host waits for the totals only (this event), not for the expansion queued behind them
+                counted = torch.cuda.Event()
+                counted.record(torch.cuda.current_stream(dev))
                 cap = int(expand_capacity)
                 spec = (torch.empty((cap,), dtype=torch.long, device=dev),
                         torch.empty((cap,), dtype=torch.float32, device=dev),
@@ -159,7 +163,9 @@ class Marcher:
                                                   sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
                 _C.check(rc, "traverse_expand")
                 self._spec = spec
-            torch.cuda.current_stream(dev).synchronize()
+                counted.synchronize()
+            else:
+                torch.cuda.current_stream(dev).synchronize()
         self.n_overflowed = int(totals[2])
         return sample_info, interval_info, term, int(totals[0]), int(totals[1])
 

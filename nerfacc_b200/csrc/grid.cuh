@@ -485,7 +485,10 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     const int cap = opt.limit > 0 ? opt.limit : 0x7fffffff;
     const bool const_dt = (step > 0.0f) && (cone == 0.0f);
     const bool fold_empty = const_dt || step <= 0.0f;  // consecutive empty cells fold
-    const bool fold_occ = const_dt;                    // consecutive occupied cells fold
+    // consecutive occupied cells fold whenever there is a step size: the emit loop's state is
+    // t_last alone (dt is re-derived from it every step), so stopping at a cell's exit and resuming
+    // in the next occupied cell visits the same t values as running on to the later exit
+    const bool fold_occ = step > 0.0f;
     // trailing empty cells of a segment leave no trace when their skip folds into the next event
     // or is dropped at the end of the ray: the walk may then stop at the occupied box (setup_dda)
     const bool clip = fold_empty && !P.wants_term();

@@ -111,7 +111,9 @@ def test_sampling_with_sigma_fn_is_one_kernel_and_keeps_the_fast_layout(device):
         _C.prof_enable(False)
     # march (count, expand), the user's callback (torch), then ONE native call: no mask kernel,
     # no separate compaction, no pack_info
-    assert sorted(called) == ["traverse_count", "traverse_fill_sampling", "visibility_compact"], called
+    # (traverse_expand: the second and later calls expand the runs ahead of the count read-back)
+    assert sorted(called) in (["traverse_count", "traverse_fill_sampling", "visibility_compact"],
+                              ["traverse_count", "traverse_expand", "visibility_compact"]), called
     assert called["visibility_compact"][0] == 1
     assert 0 < ri.numel() < ri0.numel()
     assert torch.equal(ri, ri0[mask]) and torch.equal(ts, ts0[mask]) and torch.equal(te, te0[mask])
