@@ -218,6 +218,7 @@ ALGO_BYTES = {
     # algorithmic bytes per launch: S samples, R rays, B = bitfield bytes
     "traverse_count": lambda S, R, B: 24 * R + 16 * R + B,
     "traverse_fill_sampling": lambda S, R, B: 16 * S + 24 * R + 16 * R + B,
+    "traverse_expand": lambda S, R, B: 16 * S + 24 * R + 16 * R + B,  # the same pass, launched ahead of the count read-back
     "render_weight_fwd": lambda S, R, B: 24 * S + 16 * R,
     "render_weight_bwd": lambda S, R, B: 24 * S + 16 * R,
     "composite_fwd": lambda S, R, B: 24 * S + 16 * R + 20 * R,   # read w, rgb, ts, te; write 5 floats/ray
@@ -584,10 +585,12 @@ def run_ours(args) -> None:
         except Exception:
             pass
     traversal = None
-    if "traverse_count" in kernels and "traverse_fill_sampling" in kernels:
-        t_ms = kernels["traverse_count"]["avg_ms"] + kernels["traverse_fill_sampling"]["avg_ms"]
+    fills = [k for k in ("traverse_fill_sampling", "traverse_expand") if k in kernels]
+    if "traverse_count" in kernels and fills:
+        t_ms = kernels["traverse_count"]["avg_ms"] + sum(
+            kernels[k]["avg_ms"] * kernels[k]["launches_per_step"] for k in fills)
         by = 16 * S + 48 * n_rays + B
-        traversal = {"kernels": ["traverse_count", "traverse_fill_sampling"], "bytes": by, "ms": t_ms,
+        traversal = {"kernels": ["traverse_count"] + fills, "bytes": by, "ms": t_ms,
                      "achieved": by / (t_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                      "frac": by / (t_ms * 1e-3) / 1e9 / peak}
     step_roofline = {"bytes_per_step": 120 * S, "ms_per_step": ms / args.steps,

@@ -15,7 +15,6 @@
 //    progressions ("runs"), and pass 2 of OccGridEstimator.sampling is a pure,
 //    warp-cooperative expansion of those runs — the grid is marched once, not twice.
 #include <algorithm>
-#include <cstdlib>
 #include <type_traits>
 
 #include "grid.cuh"
@@ -658,8 +657,8 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float) +
                         (size_t)kPoolWords * kMarchThreads * sizeof(uint32_t) + (kMaxCk + 4) * sizeof(float);
     // cone stepping (dt follows t) folds nothing: events are applied in place, without the queue
-    static const bool cone_queue = [] { const char* e = getenv("NFB_CONE_QUEUE"); return e != nullptr && e[0] == '1'; }();
-    const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f && !cone_queue;
+    // (measured: through the queue a cfg4 march takes 43 ms against 24 ms applied in place)
+    const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
     auto kernel = G.mip != nullptr ? (direct ? march_kernel<true, true, Policy> : march_kernel<true, false, Policy>)
                                    : (direct ? march_kernel<false, true, Policy> : march_kernel<false, false, Policy>);
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {

@@ -516,6 +516,10 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     int mip_base = 0;
     int pend_kind = -1;
     float pend_t = 0.0f;
+    // DIRECT: the cell being marched through (its kind, exit time, the skip's dt fixed at entry, literal
+    // skip steps taken); ckind < 0: none
+    int ckind = -1, lit = 0;
+    float ct = 0.0f, cdt = 0.0f;
     // ---- queue
     int nq = 0;
     uint32_t kinds = 0;
@@ -783,7 +787,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         // the ray, then (b) all lanes walk up to kRoundSteps cells together.  Keeping (a) out of
         // the walk matters for nested grids: a lane that switched inside the walk would run the
         // rest of its round alone.
-        if (have_ray && !in_seg && nq <= kQ - 3) {
+        if (have_ray && !in_seg && ckind < 0 && nq <= kQ - 3) {
             // Left at the occupied box rather than at the end of the segment (the axis stepped last
             // sits on a pulled-in stop): the cells not walked are empty — stand in for them with
             // an empty span, whose t is replaced by the next segment's start or dropped below.
@@ -836,7 +840,75 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         }
         // ------------------------------------------------------------------ produce
         int steps = 0;
-        if (have_ray && in_seg && nq <= kQ - 3) {
+        if constexpr (DIRECT) {
+            // Cone stepping: dt follows t, nothing folds, every cell costs a few steps of a serial
+            // recurrence — a different number per lane.  Walking cell by cell in lock step (visit,
+            // then each lane's emit / skip loop to the end) left 9 of 32 lanes busy.  Instead every
+            // iteration of ONE loop lets a lane take one step of its cell's recurrence and, when the
+            // cell is exhausted, visit the next cell right away: lanes drift apart by cells, not by
+            // idle time.  Same arithmetic in the same order per ray as apply() (grid.cu:189-262).
+            if (have_ray && (in_seg || ckind >= 0)) {
+                do {
+                    if (ckind >= 0) {
+                        const bool emit = ckind == EV_OCC;
+                        const float dt = emit ? calc_dt(t_last, cone, step) : cdt;
+                        const float t_next = __fadd_rn(t_last, dt);
+                        bool done = capped || __fmaf_rn(dt, 0.5f, t_last) >= ct || !(t_next > t_last);
+                        if (!done) {
+                            if (emit) {
+                                sink.one(P, t_last, t_next, continuous, nS, nI);
+                                nI += continuous ? 1 : 2;
+                                nS += 1;
+                                continuous = true;
+                                t_last = t_next;
+                                if (nS >= cap) { capped = true; have_ray = false; }
+                            } else {
+                                t_last = t_next;
+                                if (++lit >= 12) {  // a long skip: the closed form for what remains
+                                    t_last = advance(t_last, dt, ct, 0x7fffffff, dummy, NoPiece());
+                                    done = true;
+                                }
+                            }
+                        }
+                        if (done) {
+                            if (ckind == EV_EMPTY) continuous = false;
+                            ckind = -1;
+                        }
+                    }
+                    if (ckind < 0 && in_seg && have_ray) {
+                        // visit the cell the DDA stands in, then step past it (grid.cu:183-281)
+                        const float t_trav = fminf(fminf(D.tdist[0], fminf(D.tdist[1], D.tdist[2])), tmax_seg);
+                        uint32_t cbit = 1u;
+                        if (MIP) {
+                            const int ci = mip_base + ((D.cur[0] >> G.mip_shift) * G.mres[1] + (D.cur[1] >> G.mip_shift)) * G.mres[2] +
+                                           (D.cur[2] >> G.mip_shift);
+                            cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
+                        }
+                        uint32_t word = 0u;
+                        if (cbit) word = __ldg(G.occ_bits + (cell >> 5));
+                        ckind = (int)((word >> (cell & 31)) & 1u);
+                        ct = t_trav;
+                        lit = 0;
+                        cdt = calc_dt(t_last, cone, step);  // the skip's dt, fixed at the cell's entry (grid.cu:199-203)
+                        const bool px = D.tdist[0] < D.tdist[1] && D.tdist[0] < D.tdist[2];
+                        const bool py = !px && D.tdist[1] < D.tdist[2];
+                        const bool pz = !px && !py;
+                        D.cur[0] += px ? D.stepi[0] : 0;
+                        D.cur[1] += py ? D.stepi[1] : 0;
+                        D.cur[2] += pz ? D.stepi[2] : 0;
+                        D.tdist[0] = px ? __fadd_rn(D.tdist[0], D.delta[0]) : D.tdist[0];
+                        D.tdist[1] = py ? __fadd_rn(D.tdist[1], D.delta[1]) : D.tdist[1];
+                        D.tdist[2] = pz ? __fadd_rn(D.tdist[2], D.delta[2]) : D.tdist[2];
+                        cell += px ? cstride[0] : (py ? cstride[1] : cstride[2]);
+                        const bool leave = (px && D.cur[0] == D.stop[0]) || (py && D.cur[1] == D.stop[1]) ||
+                                           (pz && D.cur[2] == D.stop[2]);
+                        if (leave || ++seg_steps > max_seg_steps) in_seg = false;
+                    }
+                    ++steps;
+                } while ((in_seg || ckind >= 0) && have_ray && steps < 2 * kRoundSteps);
+                if (!have_ray) ckind = -1;  // capped: the ray is over
+            }
+        } else if (have_ray && in_seg && nq <= kQ - 3) {
             // the DDA proper (grid.cu:183-281), branch-free; leaves the loop when the segment
             // ends, the round is over or the queue is (nearly) full
             do {

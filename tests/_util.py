@@ -56,3 +56,26 @@ def record(name, values):
             json.dump(data, f, indent=1, sort_keys=True)
     except Exception:
         pass
+
+
+def err_vs(x, truth):
+    """max |x - t| / (|t| + 1e-2 rms(t)) (the metric of bench_configs.err_vs, numpy)."""
+    x, t = np.asarray(x, np.float64), np.asarray(truth, np.float64)
+    scale = max(float(np.sqrt(np.mean(t * t))), 1e-30)
+    return float(np.max(np.abs(x - t) / (np.abs(t) + 1e-2 * scale))) if t.size else 0.0
+
+
+def rms_err(x, truth):
+    x, t = np.asarray(x, np.float64), np.asarray(truth, np.float64)
+    return float(np.sqrt(np.mean((x - t) ** 2)) / max(np.sqrt(np.mean(t * t)), 1e-300)) if t.size else 0.0
+
+
+def assert_as_close_as_reference(ours, ref32, truth64, what="", tol=1e-5):
+    """north_star's float bar with numbers behind it: `ours` within 1e-5 of a float64 evaluation,
+    or as close to it as the reference's fp32 arithmetic (`ref32`: the oracle's sequential fp32
+    restatement, or the reference's own kernels) is: max error within 2x, RMS error within 1.25x."""
+    e_o, e_r = err_vs(ours, truth64), err_vs(ref32, truth64)
+    r_o, r_r = rms_err(ours, truth64), rms_err(ref32, truth64)
+    ok = e_o <= max(tol, 2.0 * e_r) and r_o <= max(0.1 * tol, 1.25 * r_r)
+    assert ok, f"{what}: max err ours {e_o:.3e} vs reference fp32 {e_r:.3e}; rms ours {r_o:.3e} vs {r_r:.3e}"
+    return e_o, e_r

@@ -257,6 +257,10 @@ def test_propnet_sampling_vs_oracle(device, kind):
     assert len(est.prop_cache) == 0
     ts_ref, te_ref = _oracle_prop_sampling(nets, [48, 24], 16, n_rays, 0.2, 6.0, kind)
     # the network's exp() differs by ulps between CPU and GPU; the resampling amplifies that a bit
+    from tests._util import record
+    record(f"PropNetEstimator.sampling vs the oracle pipeline on CPU networks ({kind}), 300 rays",
+           {"max_rel_ts": float(np.max(np.abs(ts.cpu().numpy() - ts_ref) / np.abs(ts_ref))),
+            "max_rel_te": float(np.max(np.abs(te.cpu().numpy() - te_ref) / np.abs(te_ref)))})
     np.testing.assert_allclose(ts.cpu().numpy(), ts_ref, rtol=2e-4, atol=2e-5)
     np.testing.assert_allclose(te.cpu().numpy(), te_ref, rtol=2e-4, atol=2e-5)
     assert bool((te >= ts).all()) and float(ts.min()) >= 0.2 - 1e-5 and float(te.max()) <= 6.0 + 1e-4
@@ -302,6 +306,11 @@ def test_propnet_loss_and_gradients_vs_torch(device):
         ref = ref + _lossfun_outer(s_final, w_final, iv.vals, c[:, 1:] - c[:, :-1]).mean()
     ref = ref * 2.0
     grads_ref = torch.autograd.grad(ref, params)
+    from tests._util import record
+    record("PropNetEstimator loss/grads vs the torch.searchsorted restatement (_lossfun_outer), 256 rays",
+           {"rel_loss": float((loss - ref).abs() / ref.abs()),
+            "rel_grads": [float((g - gr).abs() / gr.abs().clamp_min(1e-30)) for g, gr in zip(grads, grads_ref)],
+            "grads_ref": [float(gr) for gr in grads_ref]})
     torch.testing.assert_close(loss, ref, rtol=1e-4, atol=1e-8)
     for g, gr in zip(grads, grads_ref):
         torch.testing.assert_close(g, gr, rtol=2e-3, atol=1e-7)
@@ -393,8 +402,10 @@ def test_propnet_vs_reference_package_cfg5(device):
          "max_rel_dt": float(rel_t.max()), "frac_rel_dt_le_1e-5": float((rel_t <= 1e-5).float().mean()),
          "frac_bit_equal": float(((ts == ts_r) & (te == te_r)).float().mean())}
     record("PropNetEstimator.sampling cfg5 vs the reference's PropNetEstimator", m)
+    # measured on a B200 (profiles/r02_*_measured_errors.json): 98.1 % of the edges bit-equal, 99.98 %
+    # within 1e-5 relative, the rest sit in flat stretches of the CDF; max |ds| = 3.6e-6
     assert m["frac_rel_dt_le_1e-5"] >= 0.999, m
-    assert m["max_abs_ds"] <= 1e-4, m
+    assert m["max_abs_ds"] <= 1e-5, m
     del ts, te, ts_r, te_r, ds, rel_t
     torch.cuda.empty_cache()
 
@@ -414,5 +425,6 @@ def test_propnet_vs_reference_package_cfg5(device):
     m2 = {"loss": [l_o, l_r], "grads": [g_o, g_r],
           "rel_loss": abs(l_o - l_r) / abs(l_r), "rel_grads": [abs(a - b) / max(abs(b), 1e-30) for a, b in zip(g_o, g_r)]}
     record("PropNetEstimator.compute_loss + grads, 2^18 rays, vs the reference's PropNetEstimator", m2)
-    assert l_r > 0 and m2["rel_loss"] <= 1e-4, m2
-    assert all(r <= 1e-3 for r in m2["rel_grads"]), m2
+    # measured: loss 6.4e-8 relative, gradients equal to the last bit
+    assert l_r > 0 and m2["rel_loss"] <= 1e-5, m2
+    assert all(r <= 1e-5 for r in m2["rel_grads"]), m2

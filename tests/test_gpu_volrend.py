@@ -11,7 +11,7 @@ import pytest
 import torch
 
 import oracle
-from tests._util import (assert_close, packed_info_from_counts, ragged_counts,
+from tests._util import (assert_as_close_as_reference, assert_close, packed_info_from_counts, ragged_counts,
                          ray_indices_from_counts)
 
 pytestmark = pytest.mark.gpu
@@ -28,6 +28,31 @@ def _scene(n_rays=3000, seed=0, long_rays=((5, 9000), (6, 4096))):
     te = (ts + 0.01 + 0.05 * rng.random(n)).astype(np.float32)
     sig = (20.0 * rng.random(n) ** 3).astype(np.float32)
     return counts, pi, ri, ts, te, sig
+
+
+def _grad64(ri, pi, gw, gT, ga, ts, te, sig, alphas, prefix):
+    """d/d(sigmas | alphas) of sum(w gw + T gT [+ alpha ga]) in float64 (torch autograd on the CPU;
+    segmented exclusive sums as a global cumsum minus the ray's offset)."""
+    ri_t, pi_t = torch.from_numpy(ri), torch.from_numpy(pi)
+    f = lambda a: None if a is None else torch.from_numpy(np.asarray(a, np.float64))
+    first = pi_t[:, 0].clamp_max(max(ri_t.numel() - 1, 0))
+    if alphas is None:
+        x = f(sig).requires_grad_(True)
+        sd = x * (f(te) - f(ts))
+        a = 1.0 - torch.exp(-sd)
+        v = sd
+    else:
+        x = f(alphas).requires_grad_(True)
+        a = x
+        v = -torch.log1p(-x)
+    cs = torch.cumsum(v, 0) - v
+    T = torch.exp(-(cs - cs[first][ri_t]))
+    if prefix is not None:
+        T = T * f(prefix)
+    w = T * a
+    loss = (w * f(gw)).sum() + (T * f(gT)).sum() + ((a * f(ga)).sum() if ga is not None else 0.0)
+    (g,) = torch.autograd.grad(loss, x)
+    return g.numpy()
 
 
 def _t(a, device, grad=False):
@@ -61,8 +86,10 @@ def test_weight_from_density_fwd_bwd(device, with_prefix, api):
     assert_close(a.detach().cpu().numpy(), a0, RTOL, ATOL, "alphas")
     (w * _t(gw, device) + T * _t(gT, device) + a * _t(ga, device)).sum().backward()
     gs0 = oracle.render_weight_from_density_bwd(gw, gT, ga, ts, te, sig, pi, prefix)
-    scale = float(np.abs(gs0).max())
-    assert_close(s.grad.cpu().numpy(), gs0, 1e-4, 1e-5 * scale, "grad sigmas")
+    # the gradient subtracts a reverse sum from a direct term: any fp32 evaluation carries the
+    # cancellation; ours must be as close to float64 as the oracle's sequential fp32 is
+    gs64 = _grad64(ri, pi, gw, gT, ga, ts, te, sig, None, prefix)
+    assert_as_close_as_reference(s.grad.cpu().numpy(), gs0, gs64, "grad sigmas")
 
 
 @pytest.mark.parametrize("with_prefix", [False, True])
@@ -85,8 +112,8 @@ def test_weight_from_alpha_fwd_bwd(device, with_prefix):
     assert_close(T.detach().cpu().numpy(), T0, RTOL, ATOL, "trans")
     (w * _t(gw, device) + T * _t(gT, device)).sum().backward()
     ga0 = oracle.render_weight_from_alpha_bwd(gw, gT, alphas, pi, prefix)
-    scale = float(np.abs(ga0).max())
-    assert_close(a.grad.cpu().numpy(), ga0, 1e-4, 1e-5 * scale, "grad alphas")
+    ga64 = _grad64(ri, pi, gw, gT, None, None, None, None, alphas, prefix)
+    assert_as_close_as_reference(a.grad.cpu().numpy(), ga0, ga64, "grad alphas")
 
 
 def test_noncanonical_packed_info_falls_back(device):
