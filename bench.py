@@ -406,6 +406,12 @@ def run_ours(args) -> None:
     host_c = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
     host_o = torch.empty((n_rays, 1), dtype=torch.float32).pin_memory()
     host_d = torch.empty((n_rays, 1), dtype=torch.float32).pin_memory()
+    # --e2e-output loss (default): a training step's traffic — the batch's target pixels come in with its
+    # rays (36 B/ray), the loss goes out; images: the rendered colours / opacity / depth go out (20 B/ray)
+    loss_out = args.e2e_output == "loss"
+    tgt_host = torch.rand((n_rays, 3), generator=torch.Generator().manual_seed(99 + rank)).pin_memory()
+    tgt_buf = [[torch.empty((cuts[i + 1] - cuts[i], 3), device=dev) for i in range(n_chunks)] for _ in range(2)]
+    host_loss = torch.zeros((max(n_chunks, 1),), dtype=torch.float32).pin_memory()
     sig_c, rgb_c, s_cuts = [], [], [0]
     with torch.no_grad():
         for i in range(n_chunks):
@@ -439,6 +445,8 @@ def run_ours(args) -> None:
                 a, b = cuts[i], cuts[i + 1]
                 o_buf[p][i].copy_(o_host[a:b], non_blocking=True)
                 d_buf[p][i].copy_(d_host[a:b], non_blocking=True)
+                if loss_out:
+                    tgt_buf[p][i].copy_(tgt_host[a:b], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(s_in)
                 ready.append(ev)
@@ -450,6 +458,18 @@ def run_ours(args) -> None:
             ri, ts, te = est.sampling(o_buf[p][i], d_buf[p][i], render_step_size=STEP_SIZE)
             colors, opac, depth, _ = nf.rendering(
                 ts, te, ri, b - a, rgb_sigma_fn=lambda t0, t1, r, i=i: (rgb_c[i], sig_c[i]))
+            if loss_out:
+                # photometric loss against the batch's target pixels (+ small opacity / depth terms so the
+                # backward carries all three gradients, as the device-timed step's does)
+                loss = ((colors - tgt_buf[p][i]) ** 2).mean() + 1e-3 * opac.mean() + 1e-3 * depth.mean()
+                done = torch.cuda.Event()
+                done.record(main)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(done)
+                    host_loss[i:i + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+                loss.record_stream(s_out)
+                loss.backward()
+                continue
             done = torch.cuda.Event()  # the step's results exist after the forward: their D2H copy
             done.record(main)          # overlaps the backward
             with torch.cuda.stream(s_out):
@@ -649,9 +669,15 @@ def run_ours(args) -> None:
                                        "updates_in_timed_region": len([k for k in range(FIRST, FIRST + args.steps)
                                                                        if k % UPDATE_EVERY == 0])})},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": 2 * n_rays * 12 * world, "d2h_bytes_per_step": n_rays * 20 * world,
+                "h2d_bytes_per_step": (3 if loss_out else 2) * n_rays * 12 * world,
+                "d2h_bytes_per_step": (4 * n_chunks if loss_out else n_rays * 20) * world,
+                "output": args.e2e_output,
                 "pipeline": f"{n_chunks} ray blocks/step through OccGridEstimator.sampling + rendering + backward; "
-                            "pinned-host rays in, colours/opacity/depth out to pinned host, every step; "
+                            + ("pinned-host rays and target pixels in, the photometric loss out to pinned host, every step "
+                               "(a training step's traffic; --e2e-output images sends colours/opacity/depth out instead: "
+                               "with 8 ranks copying at once that leg is bound by the box's host-side copy bandwidth, "
+                               "see e2e.per_rank and profiles/r02_e_bench_8gpu_images_out.json); " if loss_out else
+                               "pinned-host rays in, colours/opacity/depth out to pinned host, every step; ") +
                             "H2D / compute / D2H on three streams, the next step's rays copied in while this "
                             "step computes (two device ray buffers), results copied out while the backward runs; "
                             "the closing event waits for both copy streams",
@@ -679,6 +705,8 @@ def main() -> None:
     ap.add_argument("--no-parity", action="store_true", help="skip the pre-flight parity check")
     ap.add_argument("--no-configs", action="store_true", help="skip the cfg3/cfg4/cfg5 side legs")
     ap.add_argument("--no-update", action="store_true", help="leave update_every_n_steps out of the step")
+    ap.add_argument("--e2e-output", default="loss", choices=["loss", "images"],
+                    help="what the end-to-end leg reads back every step")
     ap.add_argument("--e2e-chunks", type=int, default=1,
                     help="ray blocks per step of the end-to-end leg (copies overlap compute across blocks)")
     args = ap.parse_args()
