@@ -412,6 +412,7 @@ def run_ours(args) -> None:
     tgt_host = torch.rand((n_rays, 3), generator=torch.Generator().manual_seed(99 + rank)).pin_memory()
     tgt_buf = [[torch.empty((cuts[i + 1] - cuts[i], 3), device=dev) for i in range(n_chunks)] for _ in range(2)]
     host_loss = torch.zeros((max(n_chunks, 1),), dtype=torch.float32).pin_memory()
+    g_mean = [torch.full((cuts[i + 1] - cuts[i], 1), 1e-3 / (cuts[i + 1] - cuts[i]), device=dev) for i in range(n_chunks)]
     sig_c, rgb_c, s_cuts = [], [], [0]
     with torch.no_grad():
         for i in range(n_chunks):
@@ -461,14 +462,20 @@ def run_ours(args) -> None:
             if loss_out:
                 # photometric loss against the batch's target pixels (+ small opacity / depth terms so the
                 # backward carries all three gradients, as the device-timed step's does)
-                loss = ((colors - tgt_buf[p][i]) ** 2).mean() + 1e-3 * opac.mean() + 1e-3 * depth.mean()
+                # (its value and its three gradients written out by hand: six small kernels instead of the
+                # twenty-odd autograd would launch for the same expression)
+                with torch.no_grad():
+                    diff = colors - tgt_buf[p][i]
+                    loss = torch.dot(diff.view(-1), diff.view(-1)) / diff.numel() \
+                        + 1e-3 * (opac.sum() + depth.sum()) / (b - a)
+                    g_loss_c = diff * (2.0 / diff.numel())
                 done = torch.cuda.Event()
                 done.record(main)
                 with torch.cuda.stream(s_out):
                     s_out.wait_event(done)
-                    host_loss[i:i + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+                    host_loss[i:i + 1].copy_(loss.reshape(1), non_blocking=True)
                 loss.record_stream(s_out)
-                loss.backward()
+                torch.autograd.backward([colors, opac, depth], [g_loss_c, g_mean[i], g_mean[i]])
                 continue
             done = torch.cuda.Event()  # the step's results exist after the forward: their D2H copy
             done.record(main)          # overlaps the backward

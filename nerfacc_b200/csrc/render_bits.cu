@@ -308,9 +308,16 @@ __device__ __forceinline__ void render_fwd_stream(const RenderBitsArgs& p, const
         float (&ts)[4] = bts[AHEAD ? (k & 1) : 0], (&te)[4] = bte[AHEAD ? (k & 1) : 0], (&fv)[4] = bfv[AHEAD ? (k & 1) : 0];
         float (&rgb)[4][3] = brgb[AHEAD ? (k & 1) : 0];
         // this vector's ray ends (mine to write) and the ray id of the first of them
-        uint32_t em;
+        uint32_t em, hn = 0u;
         if (k < kWtVec) {
-            em = end_nibble(p.bits, gg, p.n) & wt.mask(k);
+            // one 5-bit window of the head bits: heads of my four items and of the one after them
+            uint32_t win = 0u;
+            if (gg >= 0 && gg < p.n) {
+                const uint32_t lo = __ldg(p.bits + (gg >> 5)), hi = __ldg(p.bits + (gg >> 5) + 1);
+                win = __funnelshift_r(lo, hi, (unsigned)(gg & 31));
+            }
+            hn = win & 0xfu;
+            em = (win >> 1) & 0xfu & wt.mask(k);
         } else {
             const int d = wt.p_nx - 1 - 4 * lane;  // the overhang's one end: item p_nx - 1
             em = (wt.over && d >= 0 && d < 4) ? (1u << d) : 0u;
@@ -319,7 +326,7 @@ __device__ __forceinline__ void render_fwd_stream(const RenderBitsArgs& p, const
         long long rid = 0;
         if (em) rid = __ldg(p.ray_indices + gg + cf);
         VecHeads H;
-        H.init(k < kWtVec ? head_nibble<false>(p.bits, gg, p.n) : 0u, lane);
+        H.init(hn, lane);
         // transmittance and weights
         float al[4], x[4], tm[4];
 #pragma unroll
@@ -352,12 +359,13 @@ __device__ __forceinline__ void render_fwd_stream(const RenderBitsArgs& p, const
         io.store(p.trans, k, T);
         if (DENSITY) io.store(p.alphas_out, k, al);
         io.store(p.weights, k, w);
-        // the five per-ray sums
+        // the five per-ray sums, scanned together: five independent shuffle chains in flight
+        // instead of one (a lone chain leaves the warp waiting on each shuffle's latency)
         const bool of = cf == 0 ? H.o0 : (cf == 1 ? H.o1 : (cf == 2 ? H.o2 : H.o3));
-        float sel[5];
+        float sel[5], run[5], uf[5];
 #pragma unroll
         for (int ch = 0; ch < 5; ++ch) {
-            float u0, u1, u2, u3, e;
+            float u0, u1, u2, u3;
             if (ch < 3) {
                 u0 = __fmul_rn(w[0], rgb[0][ch < 3 ? ch : 0]); u1 = __fmul_rn(w[1], rgb[1][ch < 3 ? ch : 0]);
                 u2 = __fmul_rn(w[2], rgb[2][ch < 3 ? ch : 0]); u3 = __fmul_rn(w[3], rgb[3][ch < 3 ? ch : 0]);
@@ -367,9 +375,33 @@ __device__ __forceinline__ void render_fwd_stream(const RenderBitsArgs& p, const
                 u0 = __fmul_rn(w[0], tm[0]); u1 = __fmul_rn(w[1], tm[1]);
                 u2 = __fmul_rn(w[2], tm[2]); u3 = __fmul_rn(w[3], tm[3]);
             }
-            vec_segscan<SumOp>(u0, u1, u2, u3, e, wc[ch], H, lane);
-            const float uf = cf == 0 ? u0 : (cf == 1 ? u1 : (cf == 2 ? u2 : u3));
-            sel[ch] = of ? __fadd_rn(e, uf) : uf;
+            if (!H.h1) u1 = __fadd_rn(u0, u1);
+            if (!H.h2) u2 = __fadd_rn(u1, u2);
+            if (!H.h3) u3 = __fadd_rn(u2, u3);
+            float f = u3;
+            if (cf == 2) f = u2;
+            if (cf == 1) f = u1;
+            if (cf == 0) f = u0;
+            uf[ch] = f;
+            run[ch] = u3;
+        }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const bool take = d <= H.lim;
+#pragma unroll
+            for (int ch = 0; ch < 5; ++ch) {
+                const float y = __shfl_up_sync(kFull, run[ch], d);
+                if (take) run[ch] = __fadd_rn(y, run[ch]);
+            }
+        }
+#pragma unroll
+        for (int ch = 0; ch < 5; ++ch) {
+            float e = __shfl_up_sync(kFull, run[ch], 1);
+            if (lane == 0) e = wc[ch];
+            else if (H.nhb) e = __fadd_rn(wc[ch], e);
+            const float t31 = __shfl_sync(kFull, run[ch], 31);
+            wc[ch] = (H.hmask == 0u) ? __fadd_rn(wc[ch], t31) : t31;
+            sel[ch] = of ? __fadd_rn(e, uf[ch]) : uf[ch];
         }
         if (em) {
             float* __restrict__ pc = p.colors + 3 * rid;
@@ -381,17 +413,22 @@ __device__ __forceinline__ void render_fwd_stream(const RenderBitsArgs& p, const
             while (more) {
                 const int c = __ffs(more) - 1;
                 more &= more - 1u;
+                // (rare; its operands are read back rather than kept in registers across the scans:
+                // the weights this thread has just written, the inputs from L1/L2)
                 float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f, a4 = 0.0f;
 #pragma unroll
                 for (int j = 1; j < 4; ++j) {
                     const bool hj = j == 1 ? H.h1 : (j == 2 ? H.h2 : H.h3);
                     if (j <= c) {
                         if (hj) { a0 = a1 = a2 = a3 = a4 = 0.0f; }
-                        a0 = __fadd_rn(a0, __fmul_rn(w[j], rgb[j][0]));
-                        a1 = __fadd_rn(a1, __fmul_rn(w[j], rgb[j][1]));
-                        a2 = __fadd_rn(a2, __fmul_rn(w[j], rgb[j][2]));
-                        a3 = __fadd_rn(a3, w[j]);
-                        a4 = __fadd_rn(a4, __fmul_rn(w[j], tm[j]));
+                        const long long gi = gg + j;
+                        const float wj = __ldcg(p.weights + gi);
+                        const float tmj = __fmul_rn(__fadd_rn(__ldg(p.t_starts + gi), __ldg(p.t_ends + gi)), 0.5f);
+                        a0 = __fadd_rn(a0, __fmul_rn(wj, __ldg(p.rgbs + 3 * gi)));
+                        a1 = __fadd_rn(a1, __fmul_rn(wj, __ldg(p.rgbs + 3 * gi + 1)));
+                        a2 = __fadd_rn(a2, __fmul_rn(wj, __ldg(p.rgbs + 3 * gi + 2)));
+                        a3 = __fadd_rn(a3, wj);
+                        a4 = __fadd_rn(a4, __fmul_rn(wj, tmj));
                     }
                 }
                 const long long r = __ldg(p.ray_indices + gg + c);
