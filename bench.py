@@ -411,8 +411,8 @@ def run_ours(args) -> None:
     loss_out = args.e2e_output == "loss"
     tgt_host = torch.rand((n_rays, 3), generator=torch.Generator().manual_seed(99 + rank)).pin_memory()
     tgt_buf = [[torch.empty((cuts[i + 1] - cuts[i], 3), device=dev) for i in range(n_chunks)] for _ in range(2)]
-    host_loss = torch.zeros((max(n_chunks, 1),), dtype=torch.float32).pin_memory()
-    g_mean = [torch.full((cuts[i + 1] - cuts[i], 1), 1e-3 / (cuts[i + 1] - cuts[i]), device=dev) for i in range(n_chunks)]
+    host_loss = torch.zeros((3 * max(n_chunks, 1),), dtype=torch.float32).pin_memory()
+    g_mean = [torch.full((cuts[i + 1] - cuts[i], 1), 1e-3, device=dev) for i in range(n_chunks)]
     sig_c, rgb_c, s_cuts = [], [], [0]
     with torch.no_grad():
         for i in range(n_chunks):
@@ -428,6 +428,24 @@ def run_ours(args) -> None:
             sig_c.append(sigmas.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
             rgb_c.append(rgbs.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
 
+    buf_ready = [None, None]
+
+    def copy_in(q):
+        if buf_free[q] is not None:
+            s_in.wait_event(buf_free[q])
+        evs = []
+        with torch.cuda.stream(s_in):
+            for i in range(n_chunks):
+                a, b = cuts[i], cuts[i + 1]
+                o_buf[q][i].copy_(o_host[a:b], non_blocking=True)
+                d_buf[q][i].copy_(d_host[a:b], non_blocking=True)
+                if loss_out:
+                    tgt_buf[q][i].copy_(tgt_host[a:b], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(s_in)
+                evs.append(ev)
+        return evs
+
     def step_e2e():
         # Steps are not drained one by one (a training loop is not either): the timed region ends
         # after the main stream has waited for both copy streams, every step's copies in and out
@@ -438,19 +456,13 @@ def run_ours(args) -> None:
         if not args.no_update:
             est.update_every_n_steps(state["step"], occ_eval_fn, occ_thre=1e-2, n=UPDATE_EVERY)
         state["step"] += 1
-        if buf_free[p] is not None:
-            s_in.wait_event(buf_free[p])
-        ready = []
-        with torch.cuda.stream(s_in):
-            for i in range(n_chunks):
-                a, b = cuts[i], cuts[i + 1]
-                o_buf[p][i].copy_(o_host[a:b], non_blocking=True)
-                d_buf[p][i].copy_(d_host[a:b], non_blocking=True)
-                if loss_out:
-                    tgt_buf[p][i].copy_(tgt_host[a:b], non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(s_in)
-                ready.append(ev)
+        # the data loader's prefetch: this step's inputs were copied in while the step before it computed
+        # (the very first call copies its own); the copy issued now is the NEXT step's — one H2D copy of a
+        # full batch per step, inside the timed region, on its own stream
+        if buf_ready[p] is None:
+            buf_ready[p] = copy_in(p)
+        ready = buf_ready[p]
+        buf_ready[1 - p] = copy_in(1 - p)
         for i in range(n_chunks):
             a, b = cuts[i], cuts[i + 1]
             main.wait_event(ready[i])
@@ -462,19 +474,17 @@ def run_ours(args) -> None:
             if loss_out:
                 # photometric loss against the batch's target pixels (+ small opacity / depth terms so the
                 # backward carries all three gradients, as the device-timed step's does)
-                # (its value and its three gradients written out by hand: six small kernels instead of the
-                # twenty-odd autograd would launch for the same expression)
+                # loss = 1/2 sum (c - c*)^2 + 1e-3 (sum opacity + sum depth): its three gradients are the
+                # residual itself and two constant tensors, its three terms go out as three floats
                 with torch.no_grad():
-                    diff = colors - tgt_buf[p][i]
-                    loss = torch.dot(diff.view(-1), diff.view(-1)) / diff.numel() \
-                        + 1e-3 * (opac.sum() + depth.sum()) / (b - a)
-                    g_loss_c = diff * (2.0 / diff.numel())
+                    g_loss_c = colors - tgt_buf[p][i]
+                    terms = torch.stack([torch.dot(g_loss_c.view(-1), g_loss_c.view(-1)), opac.sum(), depth.sum()])
                 done = torch.cuda.Event()
                 done.record(main)
                 with torch.cuda.stream(s_out):
                     s_out.wait_event(done)
-                    host_loss[i:i + 1].copy_(loss.reshape(1), non_blocking=True)
-                loss.record_stream(s_out)
+                    host_loss[3 * i:3 * i + 3].copy_(terms, non_blocking=True)
+                terms.record_stream(s_out)
                 torch.autograd.backward([colors, opac, depth], [g_loss_c, g_mean[i], g_mean[i]])
                 continue
             done = torch.cuda.Event()  # the step's results exist after the forward: their D2H copy
@@ -677,7 +687,7 @@ def run_ours(args) -> None:
                                                                        if k % UPDATE_EVERY == 0])})},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": (3 if loss_out else 2) * n_rays * 12 * world,
-                "d2h_bytes_per_step": (4 * n_chunks if loss_out else n_rays * 20) * world,
+                "d2h_bytes_per_step": (12 * n_chunks if loss_out else n_rays * 20) * world,
                 "output": args.e2e_output,
                 "pipeline": f"{n_chunks} ray blocks/step through OccGridEstimator.sampling + rendering + backward; "
                             + ("pinned-host rays and target pixels in, the photometric loss out to pinned host, every step "
@@ -685,9 +695,10 @@ def run_ours(args) -> None:
                                "with 8 ranks copying at once that leg is bound by the box's host-side copy bandwidth, "
                                "see e2e.per_rank and profiles/r02_e_bench_8gpu_images_out.json); " if loss_out else
                                "pinned-host rays in, colours/opacity/depth out to pinned host, every step; ") +
-                            "H2D / compute / D2H on three streams, the next step's rays copied in while this "
-                            "step computes (two device ray buffers), results copied out while the backward runs; "
-                            "the closing event waits for both copy streams",
+                            "H2D / compute / D2H on three streams; every step issues ONE full-batch H2D copy — the "
+                            "next step's inputs, prefetched into the other of two device buffers while this step "
+                            "computes, as a data loader does (the first step's own copy precedes it) — results "
+                            "copied out while the backward runs; the closing event waits for both copy streams",
                 "per_rank": per_rank, "cpu_affinity": affinity},
         "gpu_launches": launches,
         "roofline": roofline, "traversal": traversal, "step_roofline": step_roofline, "hbm_kernels": hbm_kernels,

@@ -297,6 +297,8 @@ __device__ __forceinline__ float checkpoint_before(const float* __restrict__ ck,
 //   EV_RAY    a new ray starts:  payload = ray id; retires the previous ray of the lane
 constexpr int kQ = 16;          // events queued per lane
 constexpr int kRoundSteps = 32; // DDA cells per lane between two refill checks
+constexpr int kConeSteps = 4;    // cone stepping: recurrence steps per lane between two cell visits
+constexpr int kConeLiteral = 16; // ... literal skip steps in one cell before the closed form takes over
 constexpr int kPoolWords = 16;  // words per prepared ray (x 32 slots per warp)
 enum { EV_EMPTY = 0, EV_OCC = 1, EV_SEG = 2, EV_RAY = 3 };
 
@@ -516,10 +518,14 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     int mip_base = 0;
     int pend_kind = -1;
     float pend_t = 0.0f;
-    // DIRECT: the cell being marched through (its kind, exit time, the skip's dt fixed at entry, literal
-    // skip steps taken); ckind < 0: none
-    int ckind = -1, lit = 0;
-    float ct = 0.0f, cdt = 0.0f;
+    // DIRECT: the cell being marched through — its exit time (-inf: no cell; every step's "half a step
+    // ahead reaches the exit" test is then true and the step changes nothing), whether it emits, the
+    // skip's dt fixed at its entry, and the loop iterations spent skipping in it
+    constexpr float kNoCell = -1e38f * 1e38f;  // -inf
+    float ct = kNoCell, cdt = 0.0f;
+    bool cemit = false;
+    int lit = 0;
+    uint32_t nword = 0u;  // DIRECT: occupancy word of the cell the DDA stands in
     // ---- queue
     int nq = 0;
     uint32_t kinds = 0;
@@ -538,6 +544,16 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     auto push_pending = [&]() {
         if (pend_kind >= 0) { push(pend_kind, pend_t); pend_kind = -1; }
     };
+    // fine occupancy word of the current cell, fetched only under a set mip bit
+    auto occupancy_word = [&]() -> uint32_t {
+        uint32_t cbit = 1u;
+        if (MIP) {
+            const int ci = mip_base + ((D.cur[0] >> G.mip_shift) * G.mres[1] + (D.cur[1] >> G.mip_shift)) * G.mres[2] +
+                           (D.cur[2] >> G.mip_shift);
+            cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
+        }
+        return cbit ? __ldg(G.occ_bits + (cell >> 5)) : 0u;
+    };
     auto enter_segment = [&](int level) {
         cstride[0] = D.stepi[0] * G.res[1] * G.res[2];
         cstride[1] = D.stepi[1] * G.res[2];
@@ -546,6 +562,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         mip_base = level * G.mip_cells_per_level;
         in_seg = true;
         seg_steps = 0;
+        if constexpr (DIRECT) nword = occupancy_word();
     };
 
     // ---- the t_last recurrence: one ray boundary / one event
@@ -787,7 +804,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         // the ray, then (b) all lanes walk up to kRoundSteps cells together.  Keeping (a) out of
         // the walk matters for nested grids: a lane that switched inside the walk would run the
         // rest of its round alone.
-        if (have_ray && !in_seg && ckind < 0 && nq <= kQ - 3) {
+        if (have_ray && !in_seg && ct == kNoCell && nq <= kQ - 3) {
             // Left at the occupied box rather than at the end of the segment (the axis stepped last
             // sits on a pulled-in stop): the cells not walked are empty — stand in for them with
             // an empty span, whose t is replaced by the next segment's start or dropped below.
@@ -843,51 +860,21 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         if constexpr (DIRECT) {
             // Cone stepping: dt follows t, nothing folds, every cell costs a few steps of a serial
             // recurrence — a different number per lane.  Walking cell by cell in lock step (visit,
-            // then each lane's emit / skip loop to the end) left 9 of 32 lanes busy.  Instead every
-            // iteration of ONE loop lets a lane take one step of its cell's recurrence and, when the
-            // cell is exhausted, visit the next cell right away: lanes drift apart by cells, not by
-            // idle time.  Same arithmetic in the same order per ray as apply() (grid.cu:189-262).
-            if (have_ray && (in_seg || ckind >= 0)) {
+            // then each lane's emit / skip loop to the end) left 9 of 32 lanes busy; one step per
+            // iteration left the visit running for the 6 lanes that had just finished a cell.
+            // Every iteration of ONE loop visits a cell (the lanes that need one) and then takes up
+            // to kConeSteps steps of its recurrence: most cells are over within one iteration, so
+            // most lanes visit in most iterations.  The occupancy word of the cell the DDA stands
+            // in is fetched when the DDA gets there, one visit ahead of its use.  Same arithmetic
+            // in the same order per ray as apply() (grid.cu:189-262).
+            if (have_ray && (in_seg || ct != kNoCell)) {
                 do {
-                    if (ckind >= 0) {
-                        const bool emit = ckind == EV_OCC;
-                        const float dt = emit ? calc_dt(t_last, cone, step) : cdt;
-                        const float t_next = __fadd_rn(t_last, dt);
-                        bool done = capped || __fmaf_rn(dt, 0.5f, t_last) >= ct || !(t_next > t_last);
-                        if (!done) {
-                            if (emit) {
-                                sink.one(P, t_last, t_next, continuous, nS, nI);
-                                nI += continuous ? 1 : 2;
-                                nS += 1;
-                                continuous = true;
-                                t_last = t_next;
-                                if (nS >= cap) { capped = true; have_ray = false; }
-                            } else {
-                                t_last = t_next;
-                                if (++lit >= 12) {  // a long skip: the closed form for what remains
-                                    t_last = advance(t_last, dt, ct, 0x7fffffff, dummy, NoPiece());
-                                    done = true;
-                                }
-                            }
-                        }
-                        if (done) {
-                            if (ckind == EV_EMPTY) continuous = false;
-                            ckind = -1;
-                        }
-                    }
-                    if (ckind < 0 && in_seg && have_ray) {
+                    if (ct == kNoCell && in_seg) {
                         // visit the cell the DDA stands in, then step past it (grid.cu:183-281)
-                        const float t_trav = fminf(fminf(D.tdist[0], fminf(D.tdist[1], D.tdist[2])), tmax_seg);
-                        uint32_t cbit = 1u;
-                        if (MIP) {
-                            const int ci = mip_base + ((D.cur[0] >> G.mip_shift) * G.mres[1] + (D.cur[1] >> G.mip_shift)) * G.mres[2] +
-                                           (D.cur[2] >> G.mip_shift);
-                            cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
-                        }
-                        uint32_t word = 0u;
-                        if (cbit) word = __ldg(G.occ_bits + (cell >> 5));
-                        ckind = (int)((word >> (cell & 31)) & 1u);
-                        ct = t_trav;
+                        ct = fminf(fminf(D.tdist[0], fminf(D.tdist[1], D.tdist[2])), tmax_seg);
+                        cemit = (nword >> (cell & 31)) & 1u;
+                        // an empty cell ends a run of samples: nothing reads `continuous` before the cell is over
+                        continuous = continuous && cemit;
                         lit = 0;
                         cdt = calc_dt(t_last, cone, step);  // the skip's dt, fixed at the cell's entry (grid.cu:199-203)
                         const bool px = D.tdist[0] < D.tdist[1] && D.tdist[0] < D.tdist[2];
@@ -903,10 +890,34 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                         const bool leave = (px && D.cur[0] == D.stop[0]) || (py && D.cur[1] == D.stop[1]) ||
                                            (pz && D.cur[2] == D.stop[2]);
                         if (leave || ++seg_steps > max_seg_steps) in_seg = false;
+                        else nword = occupancy_word();
+                    }
+#pragma unroll
+                    for (int j = 0; j < kConeSteps; ++j) {
+                        // one step of the cell's recurrence, branch-free: lanes at an emit, at a skip
+                        // and between cells all run the same instructions.  (The reference also leaves
+                        // an emitting cell right after a sample that reaches its exit; here the next
+                        // step's test sees that, with the same result.)
+                        const float dt = cemit ? calc_dt(t_last, cone, step) : cdt;
+                        const float t_next = __fadd_rn(t_last, dt);
+                        const bool stop = __fmaf_rn(dt, 0.5f, t_last) >= ct || !(t_next > t_last) || nS >= cap;
+                        const bool em = !stop && cemit;
+                        if (em) sink.one(P, t_last, t_next, continuous, nS, nI);
+                        nI += em ? (continuous ? 1 : 2) : 0;
+                        nS += em ? 1 : 0;
+                        continuous = continuous || em;
+                        t_last = stop ? t_last : t_next;
+                        ct = stop ? kNoCell : ct;
+                    }
+                    if (nS >= cap) { capped = true; have_ray = false; }
+                    if (ct != kNoCell && !cemit && ++lit >= kConeLiteral / kConeSteps) {
+                        // a long skip: the closed form for what remains
+                        t_last = advance(t_last, cdt, ct, 0x7fffffff, dummy, NoPiece());
+                        ct = kNoCell;
                     }
                     ++steps;
-                } while ((in_seg || ckind >= 0) && have_ray && steps < 2 * kRoundSteps);
-                if (!have_ray) ckind = -1;  // capped: the ray is over
+                } while ((in_seg || ct != kNoCell) && have_ray && steps < kRoundSteps);
+                if (!have_ray) ct = kNoCell;  // capped: the ray is over
             }
         } else if (have_ray && in_seg && nq <= kQ - 3) {
             // the DDA proper (grid.cu:183-281), branch-free; leaves the loop when the segment

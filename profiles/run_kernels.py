@@ -54,7 +54,7 @@ if "cfg3" in which:
     torch.cuda.empty_cache()
 
 if "cfg4" in which:
-    n_rays = 1 << 17
+    n_rays = 1 << int(os.environ.get("NFB_CFG4_LOG2_RAYS", "17"))
     est = nf.OccGridEstimator(BC.CFG4["roi"], resolution=BC.CFG4["res"], levels=BC.CFG4["levels"]).to(dev)
     est.binaries = BC.cfg4_binaries(dev)
     o, d = BC.cfg4_rays(n_rays, 4321, dev)
