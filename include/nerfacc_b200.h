@@ -292,6 +292,22 @@ NFB_API int nfb_traverse_expand(int64_t n_rays, const int64_t* sample_info, cons
                                 int64_t capacity, int64_t* ray_indices, float* t_starts, float* t_ends,
                                 void* scratch, size_t scratch_bytes, nfb_stream_t stream);
 
+/* The same for cone stepping (step_size > 0 and cone_angle != 0; csrc/grid.cu:23-28, 208-262): dt
+ * follows t, so a run of samples has no closed form, but it is still the pure recurrence
+ * t += calc_dt(t) from its first t.  Given a piece log as `run_buf` (nfb_traverse_piece_bytes(n_rays)
+ * bytes, 16-byte aligned, contents need not be initialised) pass 1 cuts every run into pieces of at
+ * most 32 samples and logs one 16-byte record per piece; nfb_traverse_expand_cone — or
+ * nfb_traverse_fill_sampling given the same buffer — replays the pieces instead of marching the grid
+ * again.  totals[2] != 0 after pass 1: the log ran full (more than 32 pieces per ray on average);
+ * call nfb_traverse_fill_sampling with run_buf = NULL, which marches.  After
+ * nfb_traverse_expand_cone has run, nfb_traverse_fill_sampling takes n_overflowed = -1 and does
+ * nothing. */
+NFB_API size_t nfb_traverse_piece_bytes(int64_t n_rays);
+NFB_API int nfb_traverse_expand_cone(int64_t n_rays, const int64_t* sample_info, const void* piece_buf,
+                                     float step_size, float cone_angle, int64_t capacity,
+                                     int64_t* ray_indices, float* t_starts, float* t_ends,
+                                     void* scratch, size_t scratch_bytes, nfb_stream_t stream);
+
 /* Pass 2, OccGridEstimator.sampling outputs (estimators/occ_grid.py:174-177): for every sample,
  * in packed order, ray_indices, t_starts (= left edge) and t_ends (= right edge).
  * n_overflowed = totals[2] of pass 1; or, after nfb_traverse_expand has expanded the runs,

@@ -105,6 +105,9 @@ _PROTOS = {
                            c_size, c_ptr, c_size, c_ptr],
     "nfb_traverse_scratch_bytes": [c_i64],
     "nfb_traverse_expand": [c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
+    "nfb_traverse_piece_bytes": [c_i64],
+    "nfb_traverse_expand_cone": [c_i64, c_ptr, c_ptr, C.c_float, C.c_float, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_size,
+                                 c_ptr],
     "nfb_traverse_fill_sampling": [_sp(Rays), _sp(Grid), _sp(March), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                    c_i64, c_ptr, c_size, c_ptr],
     "nfb_chunk_state_bytes": [],
@@ -147,6 +150,7 @@ _RESTYPES = {
     "nfb_chunk_state_bytes": C.c_size_t,
     "nfb_compact_workspace_bytes": C.c_size_t,
     "nfb_traverse_run_bytes": C.c_size_t,
+    "nfb_traverse_piece_bytes": C.c_size_t,
     "nfb_traverse_scratch_bytes": C.c_size_t,
 }
 

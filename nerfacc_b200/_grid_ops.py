@@ -139,8 +139,11 @@ class Marcher:
         self.run_buf = None
         with torch.cuda.device(dev):
             sc = self._scratch()
-            if want_runs and self.march.step_size > 0.0 and self.march.cone_angle == 0.0:
-                self.run_buf = _C.scratch(dev, int(_C.lib().nfb_traverse_run_bytes(n)), "runs")
+            cone = self.march.cone_angle != 0.0
+            if want_runs and self.march.step_size > 0.0:
+                # constant dt: runs (arithmetic progressions); cone stepping: the piece log
+                size = _C.lib().nfb_traverse_piece_bytes(n) if cone else _C.lib().nfb_traverse_run_bytes(n)
+                self.run_buf = _C.scratch(dev, int(size), "runs")
             rc = _C.lib().nfb_traverse_count(
                 C.byref(self.rays), C.byref(self.grid), C.byref(self.march), sample_info.data_ptr(),
                 None if interval_info is None else interval_info.data_ptr(),
@@ -158,15 +161,24 @@ class Marcher:
                 spec = (torch.empty((cap,), dtype=torch.long, device=dev),
                         torch.empty((cap,), dtype=torch.float32, device=dev),
                         torch.empty((cap,), dtype=torch.float32, device=dev))
-                rc = _C.lib().nfb_traverse_expand(n, sample_info.data_ptr(), self.run_buf.data_ptr(), cap,
-                                                  spec[0].data_ptr(), spec[1].data_ptr(), spec[2].data_ptr(),
-                                                  sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
-                _C.check(rc, "traverse_expand")
+                if cone:
+                    rc = _C.lib().nfb_traverse_expand_cone(
+                        n, sample_info.data_ptr(), self.run_buf.data_ptr(), self.march.step_size, self.march.cone_angle,
+                        cap, spec[0].data_ptr(), spec[1].data_ptr(), spec[2].data_ptr(), sc.data_ptr(), sc.numel(),
+                        _C.stream_ptr(dev))
+                    _C.check(rc, "traverse_expand_cone")
+                else:
+                    rc = _C.lib().nfb_traverse_expand(n, sample_info.data_ptr(), self.run_buf.data_ptr(), cap,
+                                                      spec[0].data_ptr(), spec[1].data_ptr(), spec[2].data_ptr(),
+                                                      sc.data_ptr(), sc.numel(), _C.stream_ptr(dev))
+                    _C.check(rc, "traverse_expand")
                 self._spec = spec
                 counted.synchronize()
             else:
                 torch.cuda.current_stream(dev).synchronize()
         self.n_overflowed = int(totals[2])
+        if cone and self.run_buf is not None and self.n_overflowed != 0:
+            self.run_buf, self._spec, self.n_overflowed = None, None, 0  # the piece log ran full: pass 2 marches
         return sample_info, interval_info, term, int(totals[0]), int(totals[1])
 
     def fill_sampling(self, sample_info: Tensor, n_samples: int):
@@ -175,7 +187,7 @@ class Marcher:
         if spec is not None and n_samples <= spec[0].shape[0]:
             # the runs were expanded while the totals travelled to the host
             ray_indices, t_starts, t_ends = (t[:n_samples] for t in spec)
-            if n_samples > 0 and self.n_overflowed > 0:  # rays whose runs did not fit the buffer: march those
+            if n_samples > 0 and self.n_overflowed > 0 and self.march.cone_angle == 0.0:  # rays whose runs did not fit the buffer: march those
                 with torch.cuda.device(dev):
                     sc = self._scratch()
                     rc = _C.lib().nfb_traverse_fill_sampling(

@@ -51,6 +51,7 @@ struct RayArgs {
 // Sink methods take the policy first: it is a kernel parameter (constant bank), so what a sink
 // needs from it costs no registers.
 struct CountSink {
+    static constexpr bool kPieces = false;
     template <class P> __device__ __forceinline__ void run(const P&, float, float, int, bool, int, int) const {}
     template <class P> __device__ __forceinline__ void one(const P&, float, float, bool, int, int) const {}
 };
@@ -75,6 +76,7 @@ struct RunPool {
 };
 
 struct RunSink {
+    static constexpr bool kPieces = false;
     int idx, r;
     bool failed;
     // Every piece advance() hands over becomes one run: pieces are contiguous only at binade
@@ -98,7 +100,30 @@ struct RunSink {
     template <class P> __device__ __forceinline__ void one(const P&, float, float, bool, int, int) { failed = true; }
 };
 
+// Piece log written by the count pass when marching with cone stepping (cone_angle > 0, step_size > 0):
+// dt follows t, so a run of samples has no closed form — but it is still the pure recurrence
+// t += calc_dt(t) from its first t.  The engine (grid.cuh, kPieces) cuts every run into pieces of at
+// most kPieceLen samples and appends one record (t0, n, s0, ray) per piece: the first sample of the
+// piece is sample s0 of its ray and starts at t0.  Pass 2 (traverse_expand_cone_kernel) replays the
+// pieces, 32 at a time, instead of marching the grid again.
+constexpr int kPiecesPerRay = 32;  // log capacity per ray on average; a full log sends pass 2 back to marching
+struct PieceLog {
+    int4* __restrict__ log;           // [n_chunks][kPieceChunk]
+    int* __restrict__ chunk_fill;     // records in use per chunk (zeroed before the pass)
+    unsigned long long* __restrict__ cursor;  // next free chunk
+    unsigned long long* __restrict__ failed;  // set when the log ran out of chunks
+    int n_chunks;
+};
+struct PieceSink {
+    static constexpr bool kPieces = true;
+    float p_t0;  // the open piece: starts at sample p_s0 of the ray, at t = p_t0
+    int p_s0;
+    template <class P> __device__ __forceinline__ void run(const P&, float, float, int, bool, int, int) const {}
+    template <class P> __device__ __forceinline__ void one(const P&, float, float, bool, int, int) const {}
+};
+
 struct SamplingSink {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177), one lane per ray
+    static constexpr bool kPieces = false;
     int64_t* __restrict__ ray_indices;
     float* __restrict__ t_starts;
     float* __restrict__ t_ends;
@@ -118,6 +143,7 @@ struct SamplingSink {  // OccGridEstimator.sampling outputs (occ_grid.py:174-177
 };
 
 struct FullSink {  // traverse_grids outputs (grid.cu:218-255)
+    static constexpr bool kPieces = false;
     float* __restrict__ iv_vals; int64_t* __restrict__ iv_ray;
     uint8_t* __restrict__ iv_left; uint8_t* __restrict__ iv_right;
     float* __restrict__ sm_vals; int64_t* __restrict__ sm_ray; uint8_t* __restrict__ sm_valid;
@@ -149,9 +175,11 @@ struct FullSink {  // traverse_grids outputs (grid.cu:218-255)
 
 // ---------------------------------------------------------------------------------- policies
 // Pass 1: counts (into packed_info[2r+1]), termination planes and, optionally, the run buffer.
-template <bool RUNS>
+// MODE: 0 counts only, 1 + the run buffer (constant dt), 2 + the piece log (cone stepping)
+template <int MODE>
 struct CountPolicy {
-    using Sink = typename std::conditional<RUNS, RunSink, CountSink>::type;
+    static constexpr bool RUNS = MODE == 1;
+    using Sink = typename std::conditional<MODE == 1, RunSink, typename std::conditional<MODE == 2, PieceSink, CountSink>::type>::type;
     int64_t* __restrict__ sample_info;
     int64_t* __restrict__ interval_info;
     float* __restrict__ term;
@@ -160,12 +188,14 @@ struct CountPolicy {
     int* __restrict__ overflow_list;
     unsigned long long* __restrict__ n_overflow;
     RunPool pool;
+    PieceLog pieces;
     __device__ __forceinline__ bool accept(long long) const { return true; }
     __device__ __forceinline__ void skipped(long long) const {}
     __device__ __forceinline__ bool wants_term() const { return term != nullptr; }
     __device__ __forceinline__ Sink begin(long long r) const {
         Sink s;
         if constexpr (RUNS) { s.idx = 0; s.r = (int)r; s.failed = false; }
+        if constexpr (MODE == 2) { s.p_t0 = 0.0f; s.p_s0 = 0; }
         return s;
     }
     __device__ __forceinline__ void end(long long r, Sink& s, int nS, int nI, float t_last) const {
@@ -391,6 +421,62 @@ traverse_expand_pool_kernel(const int64_t* __restrict__ sample_info, const RunPo
             t_starts[i] = __fmaf_rn((float)j, run.q, run.t0);
             t_ends[i] = __fmaf_rn((float)(j + 1), run.q, run.t0);
         }
+    }
+}
+
+// Pass 2 of OccGridEstimator.sampling when pass 1 left a piece log (cone stepping): a warp takes 32
+// records, every lane replays its piece's recurrence (<= kPieceLen steps, the arithmetic of the march:
+// t_next = t + calc_dt(t)) into shared memory, and the warp then writes the 32 pieces row by row — each a
+// contiguous stretch of ray_indices / t_starts / t_ends.  Chunks are read in whatever order the count
+// pass's warps filled them; where a record lands depends only on its ray's offset and its s0.
+constexpr int kConeExpandWarps = 8;
+__global__ void __launch_bounds__(kConeExpandWarps * 32)
+traverse_expand_cone_kernel(const int64_t* __restrict__ sample_info, const int4* __restrict__ log,
+                            const int* __restrict__ chunk_fill, const unsigned long long* __restrict__ cursor,
+                            int n_chunks, float step, float cone, int64_t* __restrict__ ray_indices,
+                            float* __restrict__ t_starts, float* __restrict__ t_ends, long long capacity) {
+    __shared__ float s_t[kConeExpandWarps][32][kPieceLen + 1];
+    const int lane = lane_id(), w = warp_id();
+    unsigned long long used = *cursor;
+    if (used > (unsigned long long)n_chunks) used = (unsigned long long)n_chunks;
+    constexpr int kGroups = kPieceChunk / 32;
+    const long long n_groups = (long long)used * kGroups;
+    for (long long g = (long long)blockIdx.x * kConeExpandWarps + w; g < n_groups;
+         g += (long long)gridDim.x * kConeExpandWarps) {
+        const int chunk = (int)(g / kGroups), first = (int)(g % kGroups) * 32;
+        const int fill = __ldg(chunk_fill + chunk);
+        if (first >= fill) continue;
+        int n = 0, rid = 0;
+        long long base = 0;
+        float t = 0.0f;
+        if (first + lane < fill) {
+            const int4 rec = __ldg(log + (long long)chunk * kPieceChunk + first + lane);
+            t = __int_as_float(rec.x);
+            n = rec.y;
+            rid = rec.w;
+            base = __ldg(reinterpret_cast<const long long*>(sample_info) + 2 * (long long)rid) + rec.z;
+        }
+        int nmax = n;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) nmax = max(nmax, __shfl_xor_sync(kFull, nmax, d));
+        float* row = s_t[w][lane];
+        for (int j = 0; j <= nmax; ++j) {
+            if (j <= n) row[j] = t;
+            t = __fadd_rn(t, calc_dt(t, cone, step));
+        }
+        __syncwarp();
+        for (int k = 0; k < 32; ++k) {
+            const int nk = __shfl_sync(kFull, n, k);
+            if (nk == 0) continue;
+            const long long bk = __shfl_sync(kFull, base, k);
+            const long long rk = __shfl_sync(kFull, rid, k);
+            if (lane < nk && bk + lane < capacity) {
+                ray_indices[bk + lane] = rk;
+                t_starts[bk + lane] = s_t[w][k][lane];
+                t_ends[bk + lane] = s_t[w][k][lane + 1];
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -746,6 +832,24 @@ static RunPool pool_of(void* run_buf, long long n, unsigned long long* cursor) {
     return P;
 }
 
+// the piece log of n rays (see nfb_traverse_piece_bytes): chunk_fill ints (padded to 16 B) | records
+static int piece_chunks(long long n) {
+    // kPiecesPerRay records per ray on average + one partly used chunk per marching warp
+    const long long warps = (long long)sm_count() * 2 * (kMarchThreads / 32);
+    long long c = (n * kPiecesPerRay + kPieceChunk - 1) / kPieceChunk + (n / 32 + 1 < warps ? n / 32 + 1 : warps) + 1;
+    return (int)(c < (1ll << 30) ? c : (1ll << 30));
+}
+static size_t piece_fill_bytes(int n_chunks) { return ((size_t)n_chunks * sizeof(int) + 15) & ~(size_t)15; }
+static PieceLog pieces_of(void* buf, long long n, unsigned long long* counters) {
+    PieceLog L;
+    L.n_chunks = piece_chunks(n);
+    L.chunk_fill = static_cast<int*>(buf);
+    L.log = reinterpret_cast<int4*>(static_cast<char*>(buf) + piece_fill_bytes(L.n_chunks));
+    L.failed = counters + 1;
+    L.cursor = counters + 2;
+    return L;
+}
+
 static unsigned long long* counters_of(void* scratch, size_t scratch_bytes, long long n_rays) {
     const size_t need = nfb_traverse_scratch_bytes(n_rays);
     if (scratch == nullptr || scratch_bytes < need) return nullptr;
@@ -833,6 +937,12 @@ NFB_API size_t nfb_traverse_run_bytes(int64_t n_rays) {
            n * nfb::kPoolPerRay * (sizeof(nfb::Run) + sizeof(int)) + 16;
 }
 
+NFB_API size_t nfb_traverse_piece_bytes(int64_t n_rays) {
+    const long long n = n_rays > 0 ? n_rays : 0;
+    const int c = nfb::piece_chunks(n);
+    return nfb::piece_fill_bytes(c) + (size_t)c * nfb::kPieceChunk * sizeof(int4) + 16;
+}
+
 NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
                                const nfb_march_t* march, int64_t* sample_info,
                                int64_t* interval_info, float* termination_planes,
@@ -853,22 +963,35 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
     A.rays_mask = nullptr;  // the two-pass path ignores rays_mask (grid.cu:418,450)
     const GridSpec G = to_grid(grid);
     const bool want_runs = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle == 0.0f;
-    if (want_runs) {
+    const bool want_pieces = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle != 0.0f;
+    if (want_pieces) {
+        NFB_CHECK_ARG(run_buf_bytes >= nfb_traverse_piece_bytes(rays->n_rays), "piece log too small");
+        NFB_CHECK_ARG(aligned16(run_buf), "piece log must be 16-byte aligned");
+        CountPolicy<2> P;
+        P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
+        P.runs = nullptr; P.n_runs = nullptr; P.overflow_list = nullptr; P.n_overflow = nullptr; P.pool = RunPool{};
+        P.pieces = pieces_of(run_buf, rays->n_rays, counters);
+        cudaMemsetAsync(counters + 1, 0, 2 * sizeof(unsigned long long), s);
+        cudaMemsetAsync(P.pieces.chunk_fill, 0, piece_fill_bytes(P.pieces.n_chunks), s);
+        rc = launch_march(A, G, to_opts(march), P, counters, s);
+    } else if (want_runs) {
         NFB_CHECK_ARG(run_buf_bytes >= nfb_traverse_run_bytes(rays->n_rays), "run buffer too small");
         NFB_CHECK_ARG(aligned16(run_buf), "run buffer must be 16-byte aligned");
-        CountPolicy<true> P;
+        CountPolicy<1> P;
         P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
         P.runs = static_cast<Run*>(run_buf);
         P.n_runs = reinterpret_cast<int*>(P.runs + rays->n_rays * kRunSlots);
         P.overflow_list = P.n_runs + rays->n_rays;
         P.n_overflow = counters + 1;
         P.pool = pool_of(run_buf, rays->n_rays, counters + 2);
+        P.pieces = PieceLog{};
         cudaMemsetAsync(counters + 1, 0, 2 * sizeof(unsigned long long), s);
         rc = launch_march(A, G, to_opts(march), P, counters, s);
     } else {
-        CountPolicy<false> P;
+        CountPolicy<0> P;
         P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;
         P.runs = nullptr; P.n_runs = nullptr; P.overflow_list = nullptr; P.n_overflow = nullptr; P.pool = RunPool{};
+        P.pieces = PieceLog{};
         cudaMemsetAsync(counters + 1, 0, sizeof(unsigned long long), s);
         rc = launch_march(A, G, to_opts(march), P, counters, s);
     }
@@ -905,6 +1028,36 @@ static int launch_expand(int64_t n_rays, const int64_t* sample_info, const void*
     return NFB_OK;
 }
 
+static int launch_expand_cone(int64_t n_rays, const int64_t* sample_info, const void* piece_buf, float step, float cone,
+                              int64_t* ray_indices, float* t_starts, float* t_ends, long long capacity, void* scratch,
+                              size_t scratch_bytes, cudaStream_t s) {
+    using namespace nfb;
+    NFB_CHECK_ARG(aligned16(piece_buf) && aligned16(sample_info), "piece log / sample_info must be 16-byte aligned");
+    unsigned long long* ctr = counters_of(scratch, scratch_bytes, n_rays);
+    NFB_CHECK_ARG(ctr != nullptr, "scratch too small: need %zu bytes", nfb_traverse_scratch_bytes(n_rays));
+    const PieceLog L = pieces_of(const_cast<void*>(piece_buf), n_rays, ctr);
+    // sized for the whole log; the kernel reads how many chunks were handed out
+    const long long groups = (long long)L.n_chunks * (kPieceChunk / 32);
+    traverse_expand_cone_kernel<<<grid_for(groups, kConeExpandWarps, 6), kConeExpandWarps * 32, 0, s>>>(
+        sample_info, L.log, L.chunk_fill, L.cursor, L.n_chunks, step, cone, ray_indices, t_starts, t_ends, capacity);
+    count_launch();
+    NFB_CHECK_LAUNCH("traverse_expand_cone");
+    return NFB_OK;
+}
+
+NFB_API int nfb_traverse_expand_cone(int64_t n_rays, const int64_t* sample_info, const void* piece_buf,
+                                     float step_size, float cone_angle, int64_t capacity, int64_t* ray_indices,
+                                     float* t_starts, float* t_ends, void* scratch, size_t scratch_bytes,
+                                     nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n_rays >= 0 && capacity >= 0, "negative size");
+    if (n_rays == 0 || capacity == 0) return NFB_OK;
+    NFB_CHECK_ARG(sample_info && piece_buf && ray_indices && t_starts && t_ends, "null pointer");
+    NFB_CHECK_ARG(step_size > 0.0f && cone_angle != 0.0f, "the piece log belongs to cone stepping");
+    return launch_expand_cone(n_rays, sample_info, piece_buf, step_size, cone_angle, ray_indices, t_starts, t_ends,
+                              capacity, scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
+}
+
 NFB_API int nfb_traverse_expand(int64_t n_rays, const int64_t* sample_info, const void* run_buf,
                                 int64_t capacity, int64_t* ray_indices, float* t_starts, float* t_ends,
                                 void* scratch, size_t scratch_bytes, nfb_stream_t stream) {
@@ -929,6 +1082,14 @@ NFB_API int nfb_traverse_fill_sampling(const nfb_rays_t* rays, const nfb_grid_t*
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     RayArgs A = to_args(rays);
     A.rays_mask = nullptr;
+    if (run_buf != nullptr && march->step_size > 0.0f && march->cone_angle != 0.0f) {
+        // cone stepping: the count pass left a complete piece log (a caller whose log ran full —
+        // totals[2] != 0 — passes no run_buf and gets the march below)
+        NFB_CHECK_ARG(n_overflowed == 0 || n_overflowed == -1, "a full piece log cannot be expanded: pass run_buf = NULL");
+        if (n_overflowed < 0) return NFB_OK;  // nfb_traverse_expand_cone has run already
+        return launch_expand_cone(rays->n_rays, sample_info, run_buf, march->step_size, march->cone_angle, ray_indices,
+                                  t_starts, t_ends, (long long)1 << 62, scratch, scratch_bytes, s);
+    }
     const bool have_runs = run_buf != nullptr && march->step_size > 0.0f && march->cone_angle == 0.0f;
     if (have_runs) {
         // n_overflowed < 0: nfb_traverse_expand has expanded the runs already; march only the

@@ -297,6 +297,12 @@ __device__ __forceinline__ float checkpoint_before(const float* __restrict__ ck,
 //   EV_RAY    a new ray starts:  payload = ray id; retires the previous ray of the lane
 constexpr int kQ = 16;          // events queued per lane
 constexpr int kRoundSteps = 32; // DDA cells per lane between two refill checks
+// Cone stepping, count pass with a piece log (grid.cu, PieceSink): the samples of a ray come in
+// pieces of <= kPieceLen consecutive samples that follow the recurrence t += calc_dt(t) from the
+// piece's first t; the count pass appends one 16-byte record per piece to a log (chunks of
+// kPieceChunk records handed out to warps), and pass 2 replays the pieces instead of marching again.
+constexpr int kPieceLen = 32;
+constexpr int kPieceChunk = 256;
 constexpr int kConeSteps = 4;    // cone stepping: recurrence steps per lane between two cell visits
 constexpr int kConeLiteral = 16; // ... literal skip steps in one cell before the closed form takes over
 constexpr int kPoolWords = 16;  // words per prepared ray (x 32 slots per warp)
@@ -535,6 +541,29 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     float t_last = 0.0f;
     int nS = 0, nI = 0, dummy = 0;
     typename Policy::Sink sink;
+    // piece log (Policy::Sink::kPieces): the chunk this warp appends to and how much of it is used
+    int log_chunk = -1, log_used = kPieceChunk;
+    auto append_piece = [&](bool mine, float t0, int n, int s0, int rid) {
+        if constexpr (Policy::Sink::kPieces) {
+            const unsigned m = __ballot_sync(kFull, mine);
+            if (m == 0u) return;
+            const int cnt = __popc(m);
+            if (log_used + cnt > kPieceChunk) {  // (a chunk is closed with a few slots unused rather than split)
+                int c = 0;
+                if (lane == 0) {
+                    if (log_chunk >= 0) P.pieces.chunk_fill[log_chunk] = log_used;
+                    c = (int)atomicAdd(P.pieces.cursor, 1ull);
+                    if (c >= P.pieces.n_chunks) { c = -1; *P.pieces.failed = 1ull; }
+                }
+                log_chunk = __shfl_sync(kFull, c, 0);
+                log_used = 0;
+            }
+            if (mine && log_chunk >= 0)
+                P.pieces.log[(long long)log_chunk * kPieceChunk + log_used + __popc(m & lt_mask)] =
+                    make_int4(__float_as_int(t0), n, s0, rid);
+            log_used += cnt;
+        }
+    };
 
     auto push = [&](int kind, float t) {
         s_evt[nq * nthr + tid] = t;
@@ -716,6 +745,8 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         }
         const int k = __popc(mask & lt_mask);
         const int avail = pool_cnt - pool_head;
+        if constexpr (Policy::Sink::kPieces)  // the open piece of the ray that ends here
+            append_piece(need && k < avail && c_have && nS > sink.p_s0, sink.p_t0, nS - sink.p_s0, sink.p_s0, (int)c_r);
         if (need && k < avail) {
             const uint32_t* __restrict__ e = pool + pool_head + k;
             r = (long long)(int)e[0];
@@ -867,9 +898,11 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             // most lanes visit in most iterations.  The occupancy word of the cell the DDA stands
             // in is fetched when the DDA gets there, one visit ahead of its use.  Same arithmetic
             // in the same order per ray as apply() (grid.cu:189-262).
-            if (have_ray && (in_seg || ct != kNoCell)) {
+            // (the loop is warp-uniform: lanes without a cell or a ray run it predicated off — the steps
+            // change nothing when ct is -inf — so the piece log can use full-mask collectives inside)
+            if (__any_sync(kFull, have_ray && (in_seg || ct != kNoCell))) {
                 do {
-                    if (ct == kNoCell && in_seg) {
+                    if (ct == kNoCell && in_seg && have_ray) {
                         // visit the cell the DDA stands in, then step past it (grid.cu:183-281)
                         ct = fminf(fminf(D.tdist[0], fminf(D.tdist[1], D.tdist[2])), tmax_seg);
                         cemit = (nword >> (cell & 31)) & 1u;
@@ -892,6 +925,9 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                         if (leave || ++seg_steps > max_seg_steps) in_seg = false;
                         else nword = occupancy_word();
                     }
+                    [[maybe_unused]] const int nS0 = nS;
+                    [[maybe_unused]] const float t_i0 = t_last;
+                    [[maybe_unused]] const bool cont0 = continuous;
 #pragma unroll
                     for (int j = 0; j < kConeSteps; ++j) {
                         // one step of the cell's recurrence, branch-free: lanes at an emit, at a skip
@@ -909,6 +945,14 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                         t_last = stop ? t_last : t_next;
                         ct = stop ? kNoCell : ct;
                     }
+                    if constexpr (Policy::Sink::kPieces) {
+                        // Samples emitted in this iteration start with its first step (a cell that does not emit
+                        // at once is over).  They open a new piece after a gap, or when the open piece could
+                        // otherwise outgrow kPieceLen; the piece before it is complete and goes to the log.
+                        const bool newp = nS > nS0 && (!cont0 || nS0 - sink.p_s0 > kPieceLen - kConeSteps);
+                        append_piece(newp && nS0 > sink.p_s0, sink.p_t0, nS0 - sink.p_s0, sink.p_s0, (int)c_r);
+                        if (newp) { sink.p_t0 = t_i0; sink.p_s0 = nS0; }
+                    }
                     if (nS >= cap) { capped = true; have_ray = false; }
                     if (ct != kNoCell && !cemit && ++lit >= kConeLiteral / kConeSteps) {
                         // a long skip: the closed form for what remains
@@ -916,7 +960,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                         ct = kNoCell;
                     }
                     ++steps;
-                } while ((in_seg || ct != kNoCell) && have_ray && steps < kRoundSteps);
+                } while (__any_sync(kFull, (in_seg || ct != kNoCell) && have_ray) && steps < kRoundSteps);
                 if (!have_ray) ct = kNoCell;  // capped: the ray is over
             }
         } else if (have_ray && in_seg && nq <= kQ - 3) {
@@ -961,6 +1005,10 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         if constexpr (!DIRECT) {
             if (eager || __any_sync(kFull, nq > kQ - 4)) consume();
         }
+    }
+    if constexpr (Policy::Sink::kPieces) {
+        append_piece(c_have && nS > sink.p_s0, sink.p_t0, nS - sink.p_s0, sink.p_s0, (int)c_r);
+        if (lane == 0 && log_chunk >= 0) P.pieces.chunk_fill[log_chunk] = log_used;
     }
     if (c_have) P.end(c_r, sink, nS, nI, t_last);
 }

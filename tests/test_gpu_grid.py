@@ -536,3 +536,63 @@ def test_sampling_expands_ahead_of_the_count_readback(device):
     assert b > 4 * a
     assert check(dense, 0.01) == b    # guess fits, rays overflow the run buffer: only those are marched again
     assert check(sparse, 0.02) < a    # shrinking total
+
+
+def test_cone_sampling_from_the_piece_log(device):
+    """Cone stepping: pass 1 logs every run of samples as pieces of <= 32 samples and pass 2 replays
+    them (nfb_traverse_expand_cone) instead of marching again.  Bit-exact against the oracle for: a
+    shell scene (runs of hundreds of samples at small t, cut into many pieces), nested levels, the
+    speculative expansion from the second call on, a total that outgrows the guess, and a busy grid
+    whose pieces fill the log (more than 32 per ray) so that pass 2 falls back to marching."""
+    import nerfacc_b200 as nf
+    from nerfacc_b200 import _C
+
+    rng = np.random.default_rng(11)
+    n_rays, res = 6000, 64
+    o = rng.standard_normal((n_rays, 3)); o = (2.5 * o / np.linalg.norm(o, axis=-1, keepdims=True)).astype(np.float32)
+    d = -o + 0.5 * rng.standard_normal((n_rays, 3)); d = (d / np.linalg.norm(d, axis=-1, keepdims=True)).astype(np.float32)
+    to, td = torch.from_numpy(o).to(device), torch.from_numpy(d).to(device)
+    lin = (np.arange(res) + 0.5) / res * 2 - 1
+    X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
+    rad = np.sqrt(X * X + Y * Y + Z * Z)
+    shell = ((rad > 0.6) & (rad < 0.9))
+    kw = dict(render_step_size=1e-3, cone_angle=0.004, near_plane=0.05)
+
+    def check(est, bins, aabbs, expect_calls):
+        est.binaries = torch.from_numpy(bins).to(device)
+        _C.prof_enable(True)
+        try:
+            ri, ts, te = est.sampling(to, td, **kw)
+            torch.cuda.synchronize()
+            names = list(_C.prof_collect().keys())  # in order of first call
+        finally:
+            _C.prof_enable(False)
+        r_ri, r_ts, r_te, r_pi = oracle.sampling(o, d, bins, aabbs, **kw)
+        assert ri.shape[0] == r_ri.shape[0] > 0
+        assert (ri.cpu().numpy() == r_ri).all() and (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+        assert [n for n in names if n.startswith("traverse")] == expect_calls, names
+        return ri.shape[0]
+
+    # one level
+    est = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=res, levels=1).to(device)
+    aabbs = est.aabbs.cpu().numpy()
+    sparse = shell[None] & (rng.random((1, res, res, res)) < 0.5)
+    a = check(est, shell[None], aabbs, ["traverse_count", "traverse_fill_sampling"])  # no guess yet: exact buffers
+    assert a > 50 * n_rays  # long runs: cut into several pieces each
+    assert check(est, shell[None], aabbs, ["traverse_count", "traverse_expand_cone"]) == a  # the guess fits
+    b = check(est, sparse, aabbs, ["traverse_count", "traverse_expand_cone"])  # fewer samples, many short runs
+    assert b < a
+    # the total outgrows the guess: expanded ahead into too small buffers, then again into exact ones
+    assert check(est, shell[None], aabbs, ["traverse_count", "traverse_expand_cone", "traverse_fill_sampling"]) == a
+    # nested levels
+    est3 = nf.OccGridEstimator([-0.5, -0.5, -0.5, 0.5, 0.5, 0.5], resolution=res, levels=3).to(device)
+    bins3 = np.stack([shell | (rng.random((res, res, res)) < 0.01) for _ in range(3)])
+    check(est3, bins3, est3.aabbs.cpu().numpy(), ["traverse_count", "traverse_fill_sampling"])
+    check(est3, bins3, est3.aabbs.cpu().numpy(), ["traverse_count", "traverse_expand_cone"])
+    # a grid so busy that the log runs full (runs of one or two cells, more than 32 pieces per ray):
+    # pass 2 marches (the speculative expansion's output is discarded)
+    est_b = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=128, levels=1).to(device)
+    busy128 = rng.random((1, 128, 128, 128)) < 0.5
+    n1 = check(est_b, busy128, est_b.aabbs.cpu().numpy(), ["traverse_count", "traverse_fill_sampling"])
+    assert check(est_b, busy128, est_b.aabbs.cpu().numpy(),
+                 ["traverse_count", "traverse_expand_cone", "traverse_fill_sampling"]) == n1
