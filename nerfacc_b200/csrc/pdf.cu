@@ -144,118 +144,178 @@ struct PdfTileArgs {
 
 __device__ __forceinline__ float stot_apply(int mode, float s, float c0, float c1) {
     const float a = __fadd_rn(__fmul_rn(s, c1), __fmul_rn(__fsub_rn(1.0f, s), c0));
-    return mode == 2 ? __fdiv_rn(1.0f, a) : a;
+    return mode == 2 ? __frcp_rn(a) : a;  // (the correctly rounded reciprocal: what 1.0f / a is)
 }
 
-// BINS: 0 general (binary search + one IEEE division per sample), 1 a single input bin
+// ---- 1-D bulk copies (TMA) for the tile's input span: one instruction per array instead of a
+// block-wide loop of 128-bit loads and stores; completion is counted in bytes on an mbarrier.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@!p bra WAIT_%=;\n\t}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// q = upper_bound(c[0..n), u) (pdf.cu:44-63: the count of leading entries <= u) for a sorted row in
+// shared memory, as a ladder of power-of-two steps without bounds checks: `top` is the largest power
+// of two <= n (ltop its log2).  If c[top-1] <= u the answer lies in [top, n]: continue from
+// base = n + 1 - top (<= top, so c[base-1] <= u as well) where the remaining steps top/2 .. 1 reach
+// exactly up to n; else it lies in [0, top-1] and base = 0.  Every probe c[base + st - 1] is inside the
+// row.  Three instructions per step: a load at a constant offset, a compare, a conditional add.
+__device__ __forceinline__ int ladder_upper_bound(const float* c, int n, int top, int ltop, float u) {
+    const float* q = !(c[top - 1] > u) ? c + (n + 1 - top) : c;
+#define NFB_LADDER(st) q += !(q[(st) - 1] > u) ? (st) : 0;
+    switch (ltop) {
+        case 19: NFB_LADDER(1 << 18) case 18: NFB_LADDER(1 << 17) case 17: NFB_LADDER(1 << 16)
+        case 16: NFB_LADDER(1 << 15) case 15: NFB_LADDER(1 << 14) case 14: NFB_LADDER(1 << 13)
+        case 13: NFB_LADDER(1 << 12) case 12: NFB_LADDER(1 << 11) case 11: NFB_LADDER(1 << 10)
+        case 10: NFB_LADDER(1 << 9) case 9: NFB_LADDER(1 << 8) case 8: NFB_LADDER(1 << 7)
+        case 7: NFB_LADDER(1 << 6) case 6: NFB_LADDER(1 << 5) case 5: NFB_LADDER(1 << 4)
+        case 4: NFB_LADDER(1 << 3) case 3: NFB_LADDER(1 << 2) case 2: NFB_LADDER(1 << 1)
+        case 1: NFB_LADDER(1)
+        default: break;
+    }
+#undef NFB_LADDER
+    return (int)(q - c);
+}
+
+// BINS: 0 general (ladder search + one IEEE division per sample), 1 a single input bin
 // (n_in == 2: PropNetEstimator's first level, the uniform CDF — no search, the bin's constants in
-// registers), 2 few bins (n_in - 1 <= 32, fewer than half as many as samples): search, slopes from a
-// per-ray table.  STOT: 0 off, 1 uniform, 2 lindisp.  The loop body is straight-line: the search
-// runs a fixed number of branch-free steps, all lanes store every iteration, and the first and last
-// edge (pdf.cu:178-196, 224-238) are patched by lane 0 after the loop.
+// registers), 2 few bins (n_in - 1 <= 32, fewer than half
+// as many as samples): search, slopes from a per-ray table.  STOT: 0 off, 1 uniform, 2 lindisp.
+// The loop body is straight-line: all lanes store every iteration, and the first and last edge
+// (pdf.cu:178-196, 224-238) are patched by lane 0 after the loop.
 template <int STOT, bool CENTRES, int BINS>
 __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kernel(const PdfTileArgs p) {
-    extern __shared__ float s_pdf[];
+    extern __shared__ __align__(16) float s_pdf[];
     const int lane = lane_id(), w = warp_id(), tid = threadIdx.x;
     const int n_in = p.n_in, n_out = p.n_out, last = n_in - 1;
-    float* s_cdf = s_pdf;                              // [rt][n_in]
-    float* s_val = s_cdf + (size_t)p.rt * n_in;        // [rt][n_in]
+    uint64_t* bar = reinterpret_cast<uint64_t*>(s_pdf);  // 16 bytes reserved
+    float* s_cdf = s_pdf + 4;                          // [rt][n_in]
+    float* s_val = s_cdf + (size_t)p.rt * n_in;        // [rt][n_in]   (rt * n_in is a multiple of 4)
     float* s_bin = s_val + (size_t)p.rt * n_in + w * 64;  // per warp: [32] slope, [32] degenerate midpoint
-    int top = 1;  // largest power of two <= last (search steps)
-    while (2 * top <= last) top <<= 1;
-    const long long n_tiles = (p.n_rays + p.rt - 1) / p.rt;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long r0 = tile * p.rt;
+    int top = 1, ltop = 0;  // largest power of two <= last
+    while (2 * top <= last) { top <<= 1; ++ltop; }
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    uint32_t phase = 0;
+    const int n_tiles = (int)((p.n_rays + p.rt - 1) / p.rt);
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long r0 = (long long)tile * p.rt;
         const int rays = (int)((p.n_rays - r0 < p.rt) ? (p.n_rays - r0) : p.rt);
         const float* __restrict__ gc = p.cdfs + r0 * n_in;
         const float* __restrict__ gv = p.vals + r0 * n_in;
         const int total = rays * n_in;
-        if (((reinterpret_cast<uintptr_t>(gc) | reinterpret_cast<uintptr_t>(gv)) & 15u) == 0) {
-            const int n4 = total >> 2;
-            for (int i = tid; i < n4; i += kPdfWarps * 32) {
-                reinterpret_cast<float4*>(s_cdf)[i] = __ldg(reinterpret_cast<const float4*>(gc) + i);
-                reinterpret_cast<float4*>(s_val)[i] = __ldg(reinterpret_cast<const float4*>(gv) + i);
+        if ((((reinterpret_cast<uintptr_t>(gc) | reinterpret_cast<uintptr_t>(gv)) & 15u) | (total & 3)) == 0) {
+            // the tile's rows are one contiguous, 16-byte aligned span of each array
+            if (tid == 0) {
+                // (the rows were last touched through the generic proxy: the previous tile's reads)
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(bar, 2u * total * 4u);
+                bulk_g2s(s_cdf, gc, total * 4u, bar);
+                bulk_g2s(s_val, gv, total * 4u, bar);
             }
-            for (int i = 4 * n4 + tid; i < total; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
+            mbar_wait(bar, phase);
+            phase ^= 1u;
         } else {
             for (int i = tid; i < total; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
+            __syncthreads();
         }
-        __syncthreads();
         for (int j = w; j < rays; j += kPdfWarps) {
-            const float* cdf = s_cdf + (size_t)j * n_in;
-            const float* val = s_val + (size_t)j * n_in;
-            float* __restrict__ ge = p.out_edges + (r0 + j) * (n_out + 1);
-            float* __restrict__ gt = STOT ? p.out_t_edges + (r0 + j) * (n_out + 1) : nullptr;
-            float* __restrict__ gs = CENTRES ? p.out_centres + (r0 + j) * n_out : nullptr;
+            const float* cdf = s_cdf + j * n_in;
+            const float* val = s_val + j * n_in;
+            float* __restrict__ ge = p.out_edges + (r0 + j) * (n_out + 1) + lane;
+            float* __restrict__ gt = STOT ? p.out_t_edges + (r0 + j) * (n_out + 1) + lane : nullptr;
+            float* __restrict__ gs = CENTRES ? p.out_centres + (r0 + j) * n_out + lane : nullptr;
             const float u_floor = cdf[0], u_ceil = cdf[last];
             const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
             const float b = p.bias ? __ldg(p.bias + r0 + j) : 0.5f;
             const float t_min = val[0], t_max = val[last];
-            float slope1 = 0.0f, mid1 = 0.0f;  // BINS == 1: the one bin
-            bool flat1 = false;
+            float t0 = 0.0f, t1 = 0.0f, tl = 0.0f, tl2 = 0.0f;  // centres 0, 1, n_out-1, n_out-2
             if (BINS == 1) {
                 const float du = __fsub_rn(u_ceil, u_floor);
-                flat1 = du < 1e-10f;  // pdf.cu:159-160
-                slope1 = __fdiv_rn(__fsub_rn(t_max, t_min), du);
-                mid1 = __fmul_rn(__fadd_rn(t_min, t_max), 0.5f);
-            } else if (BINS == 2) {
-                if (lane < last) {
-                    const float du = __fsub_rn(cdf[lane + 1], cdf[lane]);
-                    const bool flat = du < 1e-10f;
-                    // a flat bin keeps its midpoint in the second slot; other bins a NaN there
-                    s_bin[lane] = __fdiv_rn(__fsub_rn(val[lane + 1], val[lane]), du);
-                    s_bin[32 + lane] = flat ? __fmul_rn(__fadd_rn(val[lane], val[lane + 1]), 0.5f) : __int_as_float(0x7fc00000);
-                }
-                __syncwarp();
-            }
-            float carry_prev = 0.0f;  // centre of sample i0 - 1
-            float t0 = 0.0f, t1 = 0.0f, tl = 0.0f, tl2 = 0.0f;  // centres 0, 1, n_out-1, n_out-2
-            for (int i0 = 0; i0 < n_out; i0 += 32) {
-                const int sid = i0 + lane;
-                const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
-                float t;
-                if (BINS == 1) {
+                const bool flat1 = du < 1e-10f;  // pdf.cu:159-160
+                const float slope1 = __fdiv_rn(__fsub_rn(t_max, t_min), du);
+                const float mid1 = __fmul_rn(__fadd_rn(t_min, t_max), 0.5f);
+                // centre of sample k (any k, also -1: only its use at sid == 0 is patched below)
+                auto centre = [&](int k) {
+                    const float u = __fmaf_rn(__fadd_rn((float)k, b), u_step, u_floor);
                     // upper_bound over the single leading edge: p0 = 0, p1 = 1 when cdf[0] <= u, else both 0
-                    const bool in_bin = !(u_floor > u);
-                    t = flat1 ? mid1 : __fmaf_rn(__fsub_rn(u, u_floor), slope1, t_min);
-                    if (!in_bin) t = __fmul_rn(__fadd_rn(t_min, t_min), 0.5f);  // degenerate pair (0, 0): du = 0 < 1e-10
-                } else {
-                    // q = upper_bound(cdf[0..last), u) (pdf.cu:44-63): the count of leading entries <= u
-                    int q = 0;
-                    for (int st = top; st > 0; st >>= 1) {
-                        const int idx = q + st;
-                        const float c = cdf[min(idx, last) - 1];
-                        q = (idx <= last && !(c > u)) ? idx : q;
+                    float t = flat1 ? mid1 : __fmaf_rn(__fsub_rn(u, u_floor), slope1, t_min);
+                    if (u_floor > u) t = __fmul_rn(__fadd_rn(t_min, t_min), 0.5f);  // degenerate pair (0, 0): du = 0 < 1e-10
+                    return t;
+                };
+                float carry_prev = 0.0f;  // centre of sample i0 - 1
+                for (int i0 = 0; i0 < n_out; i0 += 32) {
+                    const int sid = i0 + lane;
+                    const float t = centre(sid);
+                    float t_prev = __shfl_up_sync(kFull, t, 1);
+                    if (lane == 0) t_prev = carry_prev;
+                    carry_prev = __shfl_sync(kFull, t, 31);
+                    const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                    if (sid < n_out) {
+                        if (CENTRES) gs[i0] = t;
+                        ge[i0] = e;  // (edge 0 is patched below)
+                        if (STOT) gt[i0] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
                     }
-                    const int p0 = max(q - 1, 0), p1 = q;  // q <= last
+                }
+                t0 = centre(0); t1 = centre(1); tl = centre(n_out - 1); tl2 = centre(n_out - 2);
+            } else {
+                if (BINS == 2) {
+                    if (lane < last) {
+                        const float du = __fsub_rn(cdf[lane + 1], cdf[lane]);
+                        const bool flat = du < 1e-10f;
+                        // a flat bin keeps its midpoint in the second slot; other bins a NaN there
+                        s_bin[lane] = __fdiv_rn(__fsub_rn(val[lane + 1], val[lane]), du);
+                        s_bin[32 + lane] = flat ? __fmul_rn(__fadd_rn(val[lane], val[lane + 1]), 0.5f) : __int_as_float(0x7fc00000);
+                    }
+                    __syncwarp();
+                }
+                float carry_prev = 0.0f;  // centre of sample i0 - 1
+                for (int i0 = 0; i0 < n_out; i0 += 32) {
+                    const int sid = i0 + lane;
+                    const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
+                    const int q = ladder_upper_bound(cdf, last, top, ltop, u);  // <= last
+                    const int p0 = max(q - 1, 0);
                     const float u_lower = cdf[p0], t_lower = val[p0];
-                    if (BINS == 2 && p1 == p0 + 1) {
+                    float t;
+                    if (BINS == 2 && q == p0 + 1) {
                         const float mid = s_bin[32 + p0];
                         t = (mid == mid) ? mid : __fmaf_rn(__fsub_rn(u, u_lower), s_bin[p0], t_lower);
                     } else {
-                        const float u_upper = cdf[p1], t_upper = val[p1];
+                        const float u_upper = cdf[q], t_upper = val[q];
                         const float du = __fsub_rn(u_upper, u_lower);
                         const float scaling = __fdiv_rn(__fsub_rn(t_upper, t_lower), du);
                         t = (du < 1e-10f) ? __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f)
                                           : __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
                     }
-                }
-                const bool valid = sid < n_out;
-                if (CENTRES && valid) gs[sid] = t;
-                float t_prev = __shfl_up_sync(kFull, t, 1);
-                if (lane == 0) t_prev = carry_prev;
-                if (i0 == 0) { t0 = __shfl_sync(kFull, t, 0); t1 = __shfl_sync(kFull, t, 1); }
-                if (i0 + 32 >= n_out) {  // the last chunk: centres n_out-1 and n_out-2
-                    const int l = n_out - 1 - i0;
-                    tl = __shfl_sync(kFull, t, l);
-                    tl2 = (l > 0) ? __shfl_sync(kFull, t, l > 0 ? l - 1 : 0) : carry_prev;
-                }
-                carry_prev = __shfl_sync(kFull, t, 31);
-                // compute_intervels_kernel, pdf.cu:169-241: interior edges are midpoints of neighbouring centres
-                const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
-                if (valid) {
-                    ge[sid] = e;  // (edge 0 is patched below)
-                    if (STOT) gt[sid] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
+                    float t_prev = __shfl_up_sync(kFull, t, 1);
+                    if (lane == 0) t_prev = carry_prev;
+                    if (i0 == 0) { t0 = __shfl_sync(kFull, t, 0); t1 = __shfl_sync(kFull, t, 1); }
+                    if (i0 + 32 >= n_out) {  // the last chunk: centres n_out-1 and n_out-2
+                        const int l = n_out - 1 - i0;
+                        tl = __shfl_sync(kFull, t, l);
+                        tl2 = (l > 0) ? __shfl_sync(kFull, t, l > 0 ? l - 1 : 0) : carry_prev;
+                    }
+                    carry_prev = __shfl_sync(kFull, t, 31);
+                    // compute_intervels_kernel, pdf.cu:169-241: interior edges are midpoints of neighbouring centres
+                    const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                    if (sid < n_out) {
+                        if (CENTRES) gs[i0] = t;
+                        ge[i0] = e;  // (edge 0 is patched below)
+                        if (STOT) gt[i0] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
+                    }
                 }
             }
             if (lane == 0) {
@@ -360,7 +420,7 @@ static int importance_sampling_impl(const float* vals, const float* cdfs, const 
     if (in_info == nullptr && n_out_per_ray == nullptr) {
         // batched in, batched out: CTA tiles of rays when a useful tile fits in shared memory
         const long long per_ray = 2 * n_in;
-        const long long fixed = (long long)kPdfWarps * 64;
+        const long long fixed = (long long)kPdfWarps * 64 + 4;  // per-warp slope tables + the copy barrier
         int rt = 64;
         while (rt > 4 && (per_ray * rt + fixed) * 4 > 48 * 1024) rt >>= 1;
         if ((per_ray * rt + fixed) * 4 <= 48 * 1024 && n_in < (1 << 20) && n_out < (1 << 20) && out_edges != nullptr &&
