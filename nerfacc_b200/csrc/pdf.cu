@@ -173,9 +173,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // base = n + 1 - top (<= top, so c[base-1] <= u as well) where the remaining steps top/2 .. 1 reach
 // exactly up to n; else it lies in [0, top-1] and base = 0.  Every probe c[base + st - 1] is inside the
 // row.  Three instructions per step: a load at a constant offset, a compare, a conditional add.
+// The probes go through a 32-bit shared-memory address (a pointer would drag its 64-bit generic twin
+// through every step).
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ int ladder_upper_bound(const float* c, int n, int top, int ltop, float u) {
-    const float* q = !(c[top - 1] > u) ? c + (n + 1 - top) : c;
-#define NFB_LADDER(st) q += !(q[(st) - 1] > u) ? (st) : 0;
+    const uint32_t c0 = smem_u32(c);
+    uint32_t q = !(lds_f32(c0 + 4u * (top - 1)) > u) ? c0 + 4u * (n + 1 - top) : c0;
+#define NFB_LADDER(st) { const float v_ = lds_f32(q + 4u * ((st) - 1)); if (!(v_ > u)) q += 4u * (st); }
     switch (ltop) {
         case 19: NFB_LADDER(1 << 18) case 18: NFB_LADDER(1 << 17) case 17: NFB_LADDER(1 << 16)
         case 16: NFB_LADDER(1 << 15) case 15: NFB_LADDER(1 << 14) case 14: NFB_LADDER(1 << 13)
@@ -187,7 +195,7 @@ __device__ __forceinline__ int ladder_upper_bound(const float* c, int n, int top
         default: break;
     }
 #undef NFB_LADDER
-    return (int)(q - c);
+    return (int)((q - c0) >> 2);
 }
 
 // BINS: 0 general (ladder search + one IEEE division per sample), 1 a single input bin
