@@ -147,57 +147,6 @@ __device__ __forceinline__ float stot_apply(int mode, float s, float c0, float c
     return mode == 2 ? __frcp_rn(a) : a;  // (the correctly rounded reciprocal: what 1.0f / a is)
 }
 
-// ---- 1-D bulk copies (TMA) for the tile's input span: one instruction per array instead of a
-// block-wide loop of 128-bit loads and stores; completion is counted in bytes on an mbarrier.
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
-                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-                 "@!p bra WAIT_%=;\n\t}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-
-// q = upper_bound(c[0..n), u) (pdf.cu:44-63: the count of leading entries <= u) for a sorted row in
-// shared memory, as a ladder of power-of-two steps without bounds checks: `top` is the largest power
-// of two <= n (ltop its log2).  If c[top-1] <= u the answer lies in [top, n]: continue from
-// base = n + 1 - top (<= top, so c[base-1] <= u as well) where the remaining steps top/2 .. 1 reach
-// exactly up to n; else it lies in [0, top-1] and base = 0.  Every probe c[base + st - 1] is inside the
-// row.  Three instructions per step: a load at a constant offset, a compare, a conditional add.
-// The probes go through a 32-bit shared-memory address (a pointer would drag its 64-bit generic twin
-// through every step).
-__device__ __forceinline__ float lds_f32(uint32_t addr) {
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ int ladder_upper_bound(const float* c, int n, int top, int ltop, float u) {
-    const uint32_t c0 = smem_u32(c);
-    uint32_t q = !(lds_f32(c0 + 4u * (top - 1)) > u) ? c0 + 4u * (n + 1 - top) : c0;
-#define NFB_LADDER(st) { const float v_ = lds_f32(q + 4u * ((st) - 1)); if (!(v_ > u)) q += 4u * (st); }
-    switch (ltop) {
-        case 19: NFB_LADDER(1 << 18) case 18: NFB_LADDER(1 << 17) case 17: NFB_LADDER(1 << 16)
-        case 16: NFB_LADDER(1 << 15) case 15: NFB_LADDER(1 << 14) case 14: NFB_LADDER(1 << 13)
-        case 13: NFB_LADDER(1 << 12) case 12: NFB_LADDER(1 << 11) case 11: NFB_LADDER(1 << 10)
-        case 10: NFB_LADDER(1 << 9) case 9: NFB_LADDER(1 << 8) case 8: NFB_LADDER(1 << 7)
-        case 7: NFB_LADDER(1 << 6) case 6: NFB_LADDER(1 << 5) case 5: NFB_LADDER(1 << 4)
-        case 4: NFB_LADDER(1 << 3) case 3: NFB_LADDER(1 << 2) case 2: NFB_LADDER(1 << 1)
-        case 1: NFB_LADDER(1)
-        default: break;
-    }
-#undef NFB_LADDER
-    return (int)((q - c0) >> 2);
-}
-
 // BINS: 0 general (ladder search + one IEEE division per sample), 1 a single input bin
 // (n_in == 2: PropNetEstimator's first level, the uniform CDF — no search, the bin's constants in
 // registers), 2 few bins (n_in - 1 <= 32, fewer than half
@@ -370,16 +319,19 @@ __global__ void __launch_bounds__(kPdfWarps * 32) searchsorted_kernel(const Sear
         if (qc <= 0) continue;
         const int n_k = (int)kc, last = n_k - 1;
         const float* key = p.key + k0;
-        if (n_k > 0 && n_k <= p.smem_floats_per_warp) {
+        const bool staged = n_k > 0 && n_k <= p.smem_floats_per_warp;
+        if (staged) {
             for (int i = lane; i < n_k; i += 32) s_row[i] = __ldg(key + i);
             __syncwarp();
             key = s_row;
         }
+        const int ltop = last > 0 ? 31 - __clz(last) : 0, top = 1 << ltop;  // largest power of two <= last
         // batched query: ids relative to the key row; packed query: absolute positions (pdf.cu:278-284)
         const long long off = p.q_info ? k0 : 0;
         for (long long i = lane; i < qc; i += 32) {
             const float v = __ldg(p.query + q0 + i);
-            const int q = (n_k > 0) ? upper_bound(key, 0, last, v) : 0;
+            const int q = (n_k <= 0) ? 0 : (staged && last > 0 ? ladder_upper_bound(key, last, top, ltop, v)
+                                                                : upper_bound(key, 0, last, v));
             const int l = max(min(q - 1, last), 0), h = max(min(q, last), 0);
             p.ids_left[q0 + i] = off + l;
             p.ids_right[q0 + i] = off + h;

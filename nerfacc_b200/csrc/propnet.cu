@@ -138,7 +138,7 @@ struct PdfLossArgs {
 // A CTA owns kRowWarps consecutive rays: their key rows are one contiguous span, staged with
 // block-wide 128-bit loads; then one warp per ray.  Query edges are taken 32 at a time with a
 // stride of 31, so that lane l holds edge e0 + l and bin e0 + l (l < 31) finds its right edge's id
-// in the next lane.  The search is the fixed-trip, branch-free upper_bound of pdf.cu.
+// in the next lane.  The search is the bounds-check-free ladder of common.cuh.
 // Backward: every bin's +-d goes to the key edge it gathered from; the ids are non-decreasing along
 // the row, so lanes that hit the same edge are neighbours: a segmented shuffle sum, one writer per
 // edge, rows accumulated in shared memory in a fixed order (deterministic) and written once.
@@ -151,8 +151,8 @@ __global__ void __launch_bounds__(kRowWarps * 32) pdf_loss_kernel(const PdfLossA
     float* s_kv = s_loss;
     float* s_kc = s_kv + kRowWarps * K;
     float* s_g = s_kc + kRowWarps * K;
-    int top = 1;  // largest power of two <= max(last, 1)
-    while (2 * top <= last) top <<= 1;
+    int top = 1, ltop = 0;  // largest power of two <= max(last, 1)
+    while (2 * top <= last) { top <<= 1; ++ltop; }
     const long long n_tiles = (p.n_rays + kRowWarps - 1) / kRowWarps;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const long long r0 = tile * kRowWarps;
@@ -186,14 +186,7 @@ __global__ void __launch_bounds__(kRowWarps * 32) pdf_loss_kernel(const PdfLossA
                 const float v = on ? __ldg(qv + e) : 0.0f;
                 const float c_lo = on ? __ldg(qc + e) : 0.0f;
                 // ids of nfb_searchsorted (csrc/pdf.cu:245-286): q = upper_bound(key[0..last), v)
-                int qq = 0;
-                if (last > 0) {
-                    for (int st = top; st > 0; st >>= 1) {
-                        const int idx = qq + st;
-                        const float c = kv[min(idx, last) - 1];
-                        qq = (idx <= last && !(c > v)) ? idx : qq;
-                    }
-                }
+                const int qq = last > 0 ? ladder_upper_bound(kv, last, top, ltop, v) : 0;
                 const int left = max(qq - 1, 0), right = qq;  // (qq <= last)
                 const int right_n = __shfl_down_sync(kFull, right, 1);
                 const float c_hi = __shfl_down_sync(kFull, c_lo, 1);
