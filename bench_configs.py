@@ -307,6 +307,16 @@ def bench_cfg3(nf, dev, peak, R, n_rays=1 << 20, total=1 << 24):
     if R:
         res["weights_fwd_bwd"]["err_grad_ours_vs_ref_cuda"] = err_vs(ours_fb(), ref_fb())
 
+    # pack_info from ray_indices (a fresh view every call: the identity-keyed recall of a known
+    # packed_info must miss; the view itself moves no data)
+    P = refpkg()
+    res["pack_info"] = _entry(8 * S + 16 * n_rays, lambda: nf.pack_info(ri[:], n_rays),
+                              (lambda: P.pack_info(ri, n_rays)) if P is not None else None, peak,
+                              note="pack_info(ray_indices): read 8 B/sample, write (start, count) per ray; the reference "
+                                   "(pack.py:43-46) is index_add_ + cumsum + stack in torch")
+    if P is not None:
+        res["pack_info"]["equal_to_ref"] = bool(torch.equal(nf.pack_info(ri[:], n_rays), P.pack_info(ri, n_rays).to(torch.long)))
+
     eps, thre = 1e-4, 1e-2
 
     from nerfacc_b200 import _occ_ops

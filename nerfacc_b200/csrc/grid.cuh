@@ -531,7 +531,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
     float ct = kNoCell, cdt = 0.0f;
     bool cemit = false;
     int lit = 0;
-    uint32_t nword = 0u;  // occupancy word of the cell the DDA stands in (fetched a cell ahead of its use)
+    uint32_t nword = 0u;  // DIRECT: occupancy word of the cell the DDA stands in (fetched a cell ahead of its use)
     // ---- queue
     int nq = 0;
     uint32_t kinds = 0;
@@ -591,7 +591,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         mip_base = level * G.mip_cells_per_level;
         in_seg = true;
         seg_steps = 0;
-        nword = occupancy_word();
+        if constexpr (DIRECT) nword = occupancy_word();
     };
 
     // ---- the t_last recurrence: one ray boundary / one event
@@ -968,8 +968,9 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
             // ends, the round is over or the queue is (nearly) full
             do {
                 const float t_trav = fminf(fminf(D.tdist[0], fminf(D.tdist[1], D.tdist[2])), tmax_seg);
-                // (the cell's occupancy word was fetched when the DDA got here, one cell ago)
-                const int kind = (int)((nword >> (cell & 31)) & 1u);  // EV_OCC == 1, EV_EMPTY == 0
+                // fine bit, fetched only under a set mip bit.  (Fetching it one cell ahead, as the cone loop
+                // does, was measured here: 0.788 ms against 0.754 ms — one more live register in this loop.)
+                const int kind = (int)((occupancy_word() >> (cell & 31)) & 1u);  // EV_OCC == 1, EV_EMPTY == 0
                 if constexpr (DIRECT) {
                     apply(kind, t_trav);
                 } else {
@@ -990,7 +991,6 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 const bool leave = (px && D.cur[0] == D.stop[0]) || (py && D.cur[1] == D.stop[1]) ||
                                    (pz && D.cur[2] == D.stop[2]);
                 if (leave || ++seg_steps > max_seg_steps) in_seg = false;  // (the bound only trips on NaN rays)
-                else nword = occupancy_word();
                 ++steps;
             } while (in_seg && steps < kRoundSteps && nq <= kQ - 3 && (!DIRECT || have_ray));
         }

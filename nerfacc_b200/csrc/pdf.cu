@@ -153,10 +153,15 @@ __device__ __forceinline__ float stot_apply(int mode, float s, float c0, float c
 // as many as samples): search, slopes from a per-ray table.  STOT: 0 off, 1 uniform, 2 lindisp.
 // The loop body is straight-line: all lanes store every iteration, and the first and last edge
 // (pdf.cu:178-196, 224-238) are patched by lane 0 after the loop.
-template <int STOT, bool CENTRES, int BINS>
+template <int STOT, bool CENTRES, int BINS, bool HALF>
 __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kernel(const PdfTileArgs p) {
     extern __shared__ __align__(16) float s_pdf[];
+    // HALF: a ray per half-warp (16 lanes), two rays per warp at a time: rows whose last chunk of 32
+    // samples would be at most half full (48 samples: 3 rounds for two rays instead of 4)
+    constexpr int L = HALF ? 16 : 32;   // lanes per ray
+    constexpr int RPW = HALF ? 2 : 1;   // rays per warp at a time
     const int lane = lane_id(), w = warp_id(), tid = threadIdx.x;
+    const int ll = lane & (L - 1), sub = HALF ? lane >> 4 : 0;
     const int n_in = p.n_in, n_out = p.n_out, last = n_in - 1;
     uint64_t* bar = reinterpret_cast<uint64_t*>(s_pdf);  // 16 bytes reserved
     float* s_cdf = s_pdf + 4;                          // [rt][n_in]
@@ -189,12 +194,15 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
             for (int i = tid; i < total; i += kPdfWarps * 32) { s_cdf[i] = __ldg(gc + i); s_val[i] = __ldg(gv + i); }
             __syncthreads();
         }
-        for (int j = w; j < rays; j += kPdfWarps) {
+        for (int jj = w * RPW; jj < rays; jj += kPdfWarps * RPW) {
+            // (uniform loop: the second half-warp of an odd tail repeats the first one's ray and stores nothing)
+            const bool live = jj + sub < rays;
+            const int j = live ? jj + sub : jj;
             const float* cdf = s_cdf + j * n_in;
             const float* val = s_val + j * n_in;
-            float* __restrict__ ge = p.out_edges + (r0 + j) * (n_out + 1) + lane;
-            float* __restrict__ gt = STOT ? p.out_t_edges + (r0 + j) * (n_out + 1) + lane : nullptr;
-            float* __restrict__ gs = CENTRES ? p.out_centres + (r0 + j) * n_out + lane : nullptr;
+            float* __restrict__ ge = p.out_edges + (r0 + j) * (n_out + 1) + ll;
+            float* __restrict__ gt = STOT ? p.out_t_edges + (r0 + j) * (n_out + 1) + ll : nullptr;
+            float* __restrict__ gs = CENTRES ? p.out_centres + (r0 + j) * n_out + ll : nullptr;
             const float u_floor = cdf[0], u_ceil = cdf[last];
             const float u_step = __fdiv_rn(__fsub_rn(u_ceil, u_floor), (float)n_out);
             const float b = p.bias ? __ldg(p.bias + r0 + j) : 0.5f;
@@ -214,14 +222,14 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
                     return t;
                 };
                 float carry_prev = 0.0f;  // centre of sample i0 - 1
-                for (int i0 = 0; i0 < n_out; i0 += 32) {
-                    const int sid = i0 + lane;
+                for (int i0 = 0; i0 < n_out; i0 += L) {
+                    const int sid = i0 + ll;
                     const float t = centre(sid);
-                    float t_prev = __shfl_up_sync(kFull, t, 1);
-                    if (lane == 0) t_prev = carry_prev;
-                    carry_prev = __shfl_sync(kFull, t, 31);
+                    float t_prev = __shfl_up_sync(kFull, t, 1, L);
+                    if (ll == 0) t_prev = carry_prev;
+                    carry_prev = __shfl_sync(kFull, t, L - 1, L);
                     const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
-                    if (sid < n_out) {
+                    if (sid < n_out && live) {
                         if (CENTRES) gs[i0] = t;
                         ge[i0] = e;  // (edge 0 is patched below)
                         if (STOT) gt[i0] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
@@ -240,8 +248,8 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
                     __syncwarp();
                 }
                 float carry_prev = 0.0f;  // centre of sample i0 - 1
-                for (int i0 = 0; i0 < n_out; i0 += 32) {
-                    const int sid = i0 + lane;
+                for (int i0 = 0; i0 < n_out; i0 += L) {
+                    const int sid = i0 + ll;
                     const float u = __fmaf_rn(__fadd_rn((float)sid, b), u_step, u_floor);
                     const int q = ladder_upper_bound(cdf, last, top, ltop, u);  // <= last
                     const int p0 = max(q - 1, 0);
@@ -257,25 +265,25 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
                         t = (du < 1e-10f) ? __fmul_rn(__fadd_rn(t_lower, t_upper), 0.5f)
                                           : __fmaf_rn(__fsub_rn(u, u_lower), scaling, t_lower);
                     }
-                    float t_prev = __shfl_up_sync(kFull, t, 1);
-                    if (lane == 0) t_prev = carry_prev;
-                    if (i0 == 0) { t0 = __shfl_sync(kFull, t, 0); t1 = __shfl_sync(kFull, t, 1); }
-                    if (i0 + 32 >= n_out) {  // the last chunk: centres n_out-1 and n_out-2
+                    float t_prev = __shfl_up_sync(kFull, t, 1, L);
+                    if (ll == 0) t_prev = carry_prev;
+                    if (i0 == 0) { t0 = __shfl_sync(kFull, t, 0, L); t1 = __shfl_sync(kFull, t, 1, L); }
+                    if (i0 + L >= n_out) {  // the last chunk: centres n_out-1 and n_out-2
                         const int l = n_out - 1 - i0;
-                        tl = __shfl_sync(kFull, t, l);
-                        tl2 = (l > 0) ? __shfl_sync(kFull, t, l > 0 ? l - 1 : 0) : carry_prev;
+                        tl = __shfl_sync(kFull, t, l, L);
+                        tl2 = (l > 0) ? __shfl_sync(kFull, t, l > 0 ? l - 1 : 0, L) : carry_prev;
                     }
-                    carry_prev = __shfl_sync(kFull, t, 31);
+                    carry_prev = __shfl_sync(kFull, t, L - 1, L);
                     // compute_intervels_kernel, pdf.cu:169-241: interior edges are midpoints of neighbouring centres
                     const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
-                    if (sid < n_out) {
+                    if (sid < n_out && live) {
                         if (CENTRES) gs[i0] = t;
                         ge[i0] = e;  // (edge 0 is patched below)
                         if (STOT) gt[i0] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
                     }
                 }
             }
-            if (lane == 0) {
+            if (ll == 0 && live) {
                 const float half0 = __fmul_rn(__fsub_rn(n_out > 1 ? t1 : t0, t0), 0.5f);
                 const float e0 = fmaxf(__fsub_rn(t0, half0), t_min);
                 const float halfn = (n_out > 1) ? __fmul_rn(__fsub_rn(tl, tl2), 0.5f) : half0;
@@ -292,9 +300,12 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
 
 template <int STOT, bool CENTRES>
 static void launch_is_tile(const PdfTileArgs& t, int bins, unsigned blocks, size_t smem, cudaStream_t st) {
-    if (bins == 1) importance_sampling_tile_kernel<STOT, CENTRES, 1><<<blocks, kPdfWarps * 32, smem, st>>>(t);
-    else if (bins == 2) importance_sampling_tile_kernel<STOT, CENTRES, 2><<<blocks, kPdfWarps * 32, smem, st>>>(t);
-    else importance_sampling_tile_kernel<STOT, CENTRES, 0><<<blocks, kPdfWarps * 32, smem, st>>>(t);
+    // a ray per half-warp when that saves rounds (general path only: the slope tables are per warp)
+    const bool half = bins == 0 && (t.n_out + 15) / 16 < 2 * ((t.n_out + 31) / 32);
+    if (bins == 1) importance_sampling_tile_kernel<STOT, CENTRES, 1, false><<<blocks, kPdfWarps * 32, smem, st>>>(t);
+    else if (bins == 2) importance_sampling_tile_kernel<STOT, CENTRES, 2, false><<<blocks, kPdfWarps * 32, smem, st>>>(t);
+    else if (half) importance_sampling_tile_kernel<STOT, CENTRES, 0, true><<<blocks, kPdfWarps * 32, smem, st>>>(t);
+    else importance_sampling_tile_kernel<STOT, CENTRES, 0, false><<<blocks, kPdfWarps * 32, smem, st>>>(t);
 }
 
 struct SearchArgs {
