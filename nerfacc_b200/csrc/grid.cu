@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <type_traits>
 
+#include <cstdlib>
 #include "grid.cuh"
 
 namespace nfb {
@@ -758,7 +759,12 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     // a warp takes 32 rays at a time: one CTA per 32 rays until the machine is full, so that
     // small launches (a re-march list, a test-time chunk) spread over all SMs
     long long b = ceil_div<long long>(A.ray_list ? A.n_work : A.n_rays, 32);
-    const long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
+    long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
+    {   // EXPERIMENT: limit the persistent grid (leave room for a concurrent kernel)
+        static int lim = -1;
+        if (lim < 0) { const char* e = getenv("NFB_MARCH_CTAS"); lim = e ? atoi(e) : 0; }
+        if (lim > 0 && (long long)lim < cap) cap = lim;
+    }
     if (b > cap) b = cap;
     if (b < 1) b = 1;
     // Rays are handed out dynamically, `batch` per warp at a time: 32 when there is work for
