@@ -17,7 +17,6 @@
 #include <algorithm>
 #include <type_traits>
 
-#include <cstdlib>
 #include "grid.cuh"
 
 namespace nfb {
@@ -442,21 +441,31 @@ traverse_expand_cone_kernel(const int64_t* __restrict__ sample_info, const int4*
     if (used > (unsigned long long)n_chunks) used = (unsigned long long)n_chunks;
     constexpr int kGroups = kPieceChunk / 32;
     const long long n_groups = (long long)used * kGroups;
-    for (long long g = (long long)blockIdx.x * kConeExpandWarps + w; g < n_groups;
-         g += (long long)gridDim.x * kConeExpandWarps) {
+    // the records of group g (one per lane) and where their rays' samples start: two dependent global
+    // loads, issued one group ahead of their use
+    auto fetch = [&](long long g, int4& rec, long long& base, int& n) {
+        n = 0; base = 0; rec = make_int4(0, 0, 0, 0);
+        if (g >= n_groups) return;
         const int chunk = (int)(g / kGroups), first = (int)(g % kGroups) * 32;
         const int fill = __ldg(chunk_fill + chunk);
-        if (first >= fill) continue;
-        int n = 0, rid = 0;
-        long long base = 0;
-        float t = 0.0f;
         if (first + lane < fill) {
-            const int4 rec = __ldg(log + (long long)chunk * kPieceChunk + first + lane);
-            t = __int_as_float(rec.x);
+            rec = __ldg(log + (long long)chunk * kPieceChunk + first + lane);
             n = rec.y;
-            rid = rec.w;
-            base = __ldg(reinterpret_cast<const long long*>(sample_info) + 2 * (long long)rid) + rec.z;
+            base = __ldg(reinterpret_cast<const long long*>(sample_info) + 2 * (long long)rec.w) + rec.z;
         }
+    };
+    const long long stride = (long long)gridDim.x * kConeExpandWarps;
+    int4 rec_n; long long base_n; int n_n;
+    long long g = (long long)blockIdx.x * kConeExpandWarps + w;
+    fetch(g, rec_n, base_n, n_n);
+    for (; g < n_groups; g += stride) {
+        const int4 rec = rec_n;
+        const long long base = base_n;
+        const int n = n_n;
+        fetch(g + stride, rec_n, base_n, n_n);
+        if (__ballot_sync(kFull, n > 0) == 0u) continue;
+        float t = __int_as_float(rec.x);
+        const int rid = rec.w;
         int nmax = n;
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) nmax = max(nmax, __shfl_xor_sync(kFull, nmax, d));
@@ -759,12 +768,7 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     // a warp takes 32 rays at a time: one CTA per 32 rays until the machine is full, so that
     // small launches (a re-march list, a test-time chunk) spread over all SMs
     long long b = ceil_div<long long>(A.ray_list ? A.n_work : A.n_rays, 32);
-    long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
-    {   // EXPERIMENT: limit the persistent grid (leave room for a concurrent kernel)
-        static int lim = -1;
-        if (lim < 0) { const char* e = getenv("NFB_MARCH_CTAS"); lim = e ? atoi(e) : 0; }
-        if (lim > 0 && (long long)lim < cap) cap = lim;
-    }
+    const long long cap = (long long)sm_count() * (smem <= 112 * 1024 ? 2 : 1);
     if (b > cap) b = cap;
     if (b < 1) b = 1;
     // Rays are handed out dynamically, `batch` per warp at a time: 32 when there is work for

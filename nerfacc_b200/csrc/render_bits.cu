@@ -14,7 +14,6 @@
 //             are gathered through it (L1-resident rows), g_rgb is written and one reverse
 //             segmented sum gives g_sigma / g_alpha.  44 B/sample, no dense ray_indices read.
 // Rows of rays without samples are zero: the entry point clears the outputs first.
-#include <cstdlib>
 #include <type_traits>
 
 #include "warp_tile.cuh"
@@ -838,12 +837,7 @@ NFB_API int nfb_render_bits_bwd(int from_density, const float* g_colors, const f
     a.vec_ok = all_aligned16_rb({alphas, t_starts, t_ends, sigmas, rgbs, trans, g_weights, g_trans, g_alphas,
                                  g_in, g_rgbs});
     const unsigned grid = (unsigned)ceil_div<long long>(a.n_tiles, kWarps);
-    static int variant = -1;  // EXPERIMENT
-    if (variant < 0) { const char* e = getenv("NFB_BWD_VARIANT"); variant = e ? atoi(e) : 0; }
-    if (from_density && variant == 1) render_bits_bwd_stream_kernel<true, 2, true><<<grid, kThreads, 0, s>>>(a);
-    else if (from_density && variant == 2) render_bits_bwd_stream_kernel<true, 3, true><<<grid, kThreads, 0, s>>>(a);
-    else if (from_density && variant == 3) render_bits_bwd_stream_kernel<true, 4, false><<<grid, kThreads, 0, s>>>(a);
-    else if (from_density) render_bits_bwd_stream_kernel<true, 3, false><<<grid, kThreads, 0, s>>>(a);
+    if (from_density) render_bits_bwd_stream_kernel<true, 3, false><<<grid, kThreads, 0, s>>>(a);
     else render_bits_bwd_stream_kernel<false, 3, false><<<grid, kThreads, 0, s>>>(a);
     count_launch();
     NFB_CHECK_LAUNCH("render_bits_bwd");
