@@ -209,6 +209,17 @@ NFB_HD float advance(float t, const float dt, const float target, const int cap,
                 piece(t, q, k);
                 steps += k;
                 t = t_at(k);
+                // The step after a stretch — usually the one that crosses into the next binade — is taken
+                // right here, literally, instead of costing a trip around the loop (with 32 lanes, one of
+                // them nearly always crosses a binade, and the others wait for it).
+                if (steps < cap && !((HALF ? rn_fma(dt, 0.5f, t) : t) >= target)) {
+                    const float t2 = rn_add(t, dt);
+                    if (t2 > t) {
+                        piece(t, rn_sub(t2, t), 1);
+                        steps += 1;
+                        t = t2;
+                    }
+                }
                 continue;
             }
         }
@@ -581,7 +592,12 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                            (D.cur[2] >> G.mip_shift);
             cbit = (G.mip[ci >> 5] >> (ci & 31)) & 1u;
         }
-        return cbit ? __ldg(G.occ_bits + (cell >> 5)) : 0u;
+        // a predicated load, not a branch around one (the compiler will not speculate a load: its branch
+        // with the reconvergence bookkeeping cost 14 instructions per cell against 4)
+        uint32_t word = 0u;
+        asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p ld.global.nc.u32 %0, [%2];\n\t}"
+            : "+r"(word) : "r"(cbit), "l"(G.occ_bits + (cell >> 5)));
+        return word;
     };
     auto enter_segment = [&](int level) {
         cstride[0] = D.stepi[0] * G.res[1] * G.res[2];
