@@ -623,6 +623,9 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         if (capped) return;
         const bool emit = (kind == EV_OCC);
         const bool doit = !(kind == EV_SEG && continuous);
+        // (launch_march picks DIRECT exactly when step > 0 and cone != 0: the queue kernels do not carry
+        // the cone branches — the march is a 90 KB kernel with 10 % of its stalls on instruction fetch;
+        // the same pruning of the DIRECT kernels changed their register allocation for the worse)
         if (step <= 0.0f) {  // one interval per occupied voxel crossing
             if (!emit) {
                 if (doit) t_last = t;
@@ -633,7 +636,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 continuous = true;
                 t_last = t;
             }
-        } else if (const_dt) {
+        } else if (DIRECT ? const_dt : true) {  // constant dt (the only case the queue kernels see with a step)
             if (doit) {
                 if (emit) {
                     t_last = advance(t_last, step, t, cap, nS, [&](float t0, float q, int k) {
@@ -653,7 +656,7 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                 }
             }
         } else if (!emit) {
-            // cone_angle > 0, skip: dt is fixed at the cell's entry (grid.cu:157-161, 199-203).
+            // cone_angle > 0 (DIRECT), skip: dt is fixed at the cell's entry (grid.cu:157-161, 199-203).
             // Cells are about as long as dt: a few literal steps first, the closed form for
             // what remains.
             if (doit) {
