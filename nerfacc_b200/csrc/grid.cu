@@ -257,12 +257,16 @@ struct FillPolicy {
 // [prepared-ray pool: warps x kPoolWords x 32 words].
 constexpr int kMarchThreads = 384;  // x 2 CTAs/SM: 85 registers per thread (512 x 2 = 64 spills ten loop invariants of the DDA)
 
-template <bool MIP, bool DIRECT, class Policy>
+// SINGLE: one grid level, known at compile time — everything the engine does for nested levels
+// (event sorting, later segments and their DDA setup) folds away: a smaller kernel stalls less on
+// instruction fetch.  Instantiated for the constant-dt count pass only (launch_march).
+template <bool MIP, bool DIRECT, class Policy, bool SINGLE = false>
 __global__ void __launch_bounds__(kMarchThreads, 2)
 march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
              unsigned long long* ray_counter) {
     extern __shared__ uint32_t s_dyn[];
-    const GridSpec G = stage_mip(Gp, s_dyn);
+    GridSpec G = stage_mip(Gp, s_dyn);
+    if (SINGLE) G.n_grids = 1;
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
     uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * kMarchThreads);
     float* s_ck = reinterpret_cast<float*>(s_pool + kPoolWords * kMarchThreads);
@@ -757,6 +761,10 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
     auto kernel = G.mip != nullptr ? (direct ? march_kernel<true, true, Policy> : march_kernel<true, false, Policy>)
                                    : (direct ? march_kernel<false, true, Policy> : march_kernel<false, false, Policy>);
+    if constexpr (std::is_same<Policy, CountPolicy<1>>::value) {
+        if (G.n_grids == 1 && !direct)
+            kernel = G.mip != nullptr ? march_kernel<true, false, Policy, true> : march_kernel<false, false, Policy, true>;
+    }
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
         set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
         return NFB_ERR_CUDA;
