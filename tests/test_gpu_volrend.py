@@ -221,7 +221,8 @@ def test_accumulate_fwd_bwd(device, dim, known_layout):
     # in-place variant on the same layout: outputs += ray sums (rows of empty rays keep their value)
     acc = torch.full((R, ref.shape[1]), 0.25, device=device)
     nf.accumulate_along_rays_(w.detach(), None if v is None else v.detach(), rit, acc)
-    assert_close(acc.cpu().numpy(), ref + 0.25, 1e-5, 2e-6 * max(scale, 1.0), "accumulate_")
+    # (rows wider than 4 go through atomics: the summation order, and with it the last bits, vary from run to run)
+    assert_close(acc.cpu().numpy(), ref + 0.25, 1e-5, (4e-6 if (dim or 1) > 4 else 2e-6) * max(scale, 1.0), "accumulate_")
     assert (acc.cpu().numpy()[counts == 0] == 0.25).all()
 
 
