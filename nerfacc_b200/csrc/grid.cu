@@ -761,10 +761,10 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
     auto kernel = G.mip != nullptr ? (direct ? march_kernel<true, true, Policy> : march_kernel<true, false, Policy>)
                                    : (direct ? march_kernel<false, true, Policy> : march_kernel<false, false, Policy>);
-    if constexpr (std::is_same<Policy, CountPolicy<1>>::value) {
-        if (G.n_grids == 1 && !direct)
-            kernel = G.mip != nullptr ? march_kernel<true, false, Policy, true> : march_kernel<false, false, Policy, true>;
-    }
+    if (G.n_grids == 1)
+        kernel = G.mip != nullptr
+                     ? (direct ? march_kernel<true, true, Policy, true> : march_kernel<true, false, Policy, true>)
+                     : (direct ? march_kernel<false, true, Policy, true> : march_kernel<false, false, Policy, true>);
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
         set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
         return NFB_ERR_CUDA;

@@ -584,6 +584,14 @@ def test_cone_sampling_from_the_piece_log(device):
     assert b < a
     # the total outgrows the guess: expanded ahead into too small buffers, then again into exact ones
     assert check(est, shell[None], aabbs, ["traverse_count", "traverse_expand_cone", "traverse_fill_sampling"]) == a
+    # per-ray near / far planes (t_min / t_max): pieces start wherever the ray does
+    t_min = (rng.random(n_rays) * 2.0).astype(np.float32)
+    t_max = (t_min + 0.2 + rng.random(n_rays) * 2.0).astype(np.float32)
+    est.binaries = torch.from_numpy(shell[None]).to(device)
+    ri, ts, te = est.sampling(to, td, t_min=torch.from_numpy(t_min).to(device), t_max=torch.from_numpy(t_max).to(device), **kw)
+    r_ri, r_ts, r_te, _ = oracle.sampling(o, d, shell[None], aabbs, t_min=t_min, t_max=t_max, **kw)
+    assert ri.shape[0] == r_ri.shape[0] > 0
+    assert (ri.cpu().numpy() == r_ri).all() and (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
     # nested levels
     est3 = nf.OccGridEstimator([-0.5, -0.5, -0.5, 0.5, 0.5, 0.5], resolution=res, levels=3).to(device)
     bins3 = np.stack([shell | (rng.random((res, res, res)) < 0.01) for _ in range(3)])
