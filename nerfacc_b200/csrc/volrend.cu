@@ -404,7 +404,7 @@ __global__ void __launch_bounds__(kThreads) weight_bwd_kernel(const WeightBwdArg
 // Dense packed layouts with head bits (warp_tile.cuh): identical math per sample, no block
 // barrier and no look-back wait on the critical path.  n_tiles counts warp tiles here.
 template <bool DENSITY>
-__global__ void __launch_bounds__(kThreads, 3) weight_fwd_bits_kernel(const WeightFwdArgs p) {
+__global__ void __launch_bounds__(kThreads, DENSITY ? 3 : 4) weight_fwd_bits_kernel(const WeightFwdArgs p) {
     WarpTile<false> wt;
     if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
     float v[kWtNV][4];   // scanned quantity: (1-a) or sd
@@ -477,7 +477,7 @@ __global__ void __launch_bounds__(kThreads, 3) weight_fwd_bits_kernel(const Weig
 }
 
 template <bool DENSITY>
-__global__ void __launch_bounds__(kThreads, 3) weight_bwd_bits_kernel(const WeightBwdArgs p) {
+__global__ void __launch_bounds__(kThreads, DENSITY ? 3 : 4) weight_bwd_bits_kernel(const WeightBwdArgs p) {
     WarpTile<true> wt;
     if (!wt.init(p.bits, p.n, p.n_tiles, p.vec_ok)) return;
     float v[kWtNV][4];    // s = (g_T + g_w*a) * T, reverse-exclusive-summed
