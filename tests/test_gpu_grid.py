@@ -604,3 +604,35 @@ def test_cone_sampling_from_the_piece_log(device):
     n1 = check(est_b, busy128, est_b.aabbs.cpu().numpy(), ["traverse_count", "traverse_fill_sampling"])
     assert check(est_b, busy128, est_b.aabbs.cpu().numpy(),
                  ["traverse_count", "traverse_expand_cone", "traverse_fill_sampling"]) == n1
+
+
+@pytest.mark.parametrize("n_rays", [0, 1, 33, 257])
+@pytest.mark.parametrize("fill", ["empty", "full", "shell"])
+def test_cone_sampling_small_and_degenerate(device, n_rays, fill):
+    """The piece log at the edges: no rays, fewer rays than a warp, a grid without any occupied cell
+    (no pieces at all), a grid that is all one run per ray (only full pieces and one tail)."""
+    import nerfacc_b200 as nf
+
+    rng = np.random.default_rng(5 + n_rays)
+    res = 32
+    o = rng.standard_normal((n_rays, 3)); o = (2.0 * o / np.maximum(np.linalg.norm(o, axis=-1, keepdims=True), 1e-9)).astype(np.float32)
+    d = -o + 0.3 * rng.standard_normal((n_rays, 3)); d = (d / np.maximum(np.linalg.norm(d, axis=-1, keepdims=True), 1e-9)).astype(np.float32)
+    lin = (np.arange(res) + 0.5) / res * 2 - 1
+    X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
+    rad = np.sqrt(X * X + Y * Y + Z * Z)
+    bins = {"empty": np.zeros((1, res, res, res), bool), "full": np.ones((1, res, res, res), bool),
+            "shell": ((rad > 0.5) & (rad < 0.8))[None]}[fill]
+    est = nf.OccGridEstimator([-1.0, -1.0, -1.0, 1.0, 1.0, 1.0], resolution=res, levels=1).to(device)
+    est.binaries = torch.from_numpy(bins).to(device)
+    to, td = torch.from_numpy(o).to(device), torch.from_numpy(d).to(device)
+    kw = dict(render_step_size=2e-3, cone_angle=0.003, near_plane=0.1)
+    for _ in range(2):  # exact buffers, then the speculative expansion
+        ri, ts, te = est.sampling(to, td, **kw)
+        if n_rays == 0:
+            assert ri.numel() == 0 and ts.numel() == 0
+            continue
+        r_ri, r_ts, r_te, _ = oracle.sampling(o, d, bins, est.aabbs.cpu().numpy(), **kw)
+        assert ri.shape[0] == r_ri.shape[0]
+        assert (ri.cpu().numpy() == r_ri).all() and (ts.cpu().numpy() == r_ts).all() and (te.cpu().numpy() == r_te).all()
+        if fill == "empty":
+            assert ri.numel() == 0

@@ -52,6 +52,25 @@ def test_importance_sampling_batched_vs_oracle(device, n_in, n_out, stratified):
     assert iv.packed_info is None and sm.packed_info is None
 
 
+@pytest.mark.parametrize("n_rays", [1, 3, 70])
+@pytest.mark.parametrize("n_in,n_out", [(97, 48), (5, 80), (2, 256), (257, 96)])
+def test_importance_sampling_batched_tile_edges(device, n_rays, n_in, n_out):
+    """The tile kernel's variants at ray counts that leave tiles, warps and half-warps partly empty:
+    a ray per half-warp (48 samples), the per-ray slope table (5 -> 80), the single bin (2 -> 256), the
+    ladder search (257 -> 96); spans too short or misaligned for the bulk copy take the plain loop."""
+    import nerfacc_b200 as nf
+
+    rng = np.random.default_rng(n_rays * 131 + n_in)
+    vals, cdf = _cdf_rows(rng, n_rays, n_in)
+    for with_centres in (True, False):
+        iv, sm = nf.importance_sampling(nf.RayIntervals(vals=_t(vals, device)), _t(cdf, device), n_out,
+                                        _samples=with_centres)
+        e_ref, c_ref = oracle.importance_sampling(vals, cdf, n_out)
+        assert np.array_equal(iv.vals.cpu().numpy(), e_ref)
+        if with_centres:
+            assert np.array_equal(sm.vals.cpu().numpy(), c_ref)
+
+
 def test_importance_sampling_packed_input_vs_oracle(device):
     import nerfacc_b200 as nf
 
