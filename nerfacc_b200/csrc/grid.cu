@@ -255,21 +255,27 @@ struct FillPolicy {
 // ---------------------------------------------------------------------------------- kernels
 // Persistent CTAs: dynamic shared memory = [mip words][event queue kQ x blockDim floats]
 // [prepared-ray pool: warps x kPoolWords x 32 words].
+constexpr int kConeThreads = 512;
 constexpr int kMarchThreads = 384;  // x 2 CTAs/SM: 85 registers per thread (512 x 2 = 64 spills ten loop invariants of the DDA)
 
 // SINGLE: one grid level, known at compile time — everything the engine does for nested levels
 // (event sorting, later segments and their DDA setup) folds away: a smaller kernel stalls less on
 // instruction fetch.  Instantiated for the constant-dt count pass only (launch_march).
+// Cone kernels (DIRECT) run 512 threads per CTA at 64 registers: a launch of 2^17 rays then has a lane per
+// ray instead of two rays behind one another on some lanes (cfg4 sampling at 2^17 rays: 1.74 -> 1.64 ms;
+// at 2^20 rays 10.03 -> 10.14 ms; 640 threads: 2.06 / 11.7 ms); the queue kernels lose 7 % at 512 and stay at 384.
+template <bool DIRECT> constexpr int march_threads() { return DIRECT ? kConeThreads : kMarchThreads; }
+
 template <bool MIP, bool DIRECT, class Policy, bool SINGLE = false>
-__global__ void __launch_bounds__(kMarchThreads, 2)
+__global__ void __launch_bounds__(march_threads<DIRECT>(), 2)
 march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
              unsigned long long* ray_counter) {
     extern __shared__ uint32_t s_dyn[];
     GridSpec G = stage_mip(Gp, s_dyn);
     if (SINGLE) G.n_grids = 1;
     float* s_evt = reinterpret_cast<float*>(s_dyn + ((Gp.mip_words + 3) & ~3));
-    uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * kMarchThreads);
-    float* s_ck = reinterpret_cast<float*>(s_pool + kPoolWords * kMarchThreads);
+    uint32_t* s_pool = reinterpret_cast<uint32_t*>(s_evt + kQ * march_threads<DIRECT>());
+    float* s_ck = reinterpret_cast<float*>(s_pool + kPoolWords * march_threads<DIRECT>());
     int* s_nck = reinterpret_cast<int*>(s_ck + kMaxCk);
     // constant dt from one near plane: all rays walk one t sequence, checkpointed once per CTA
     if (threadIdx.x == 0) {
@@ -754,11 +760,12 @@ constexpr size_t kCounterBytes = 64;  // ray counter + overflow counter, at the 
 template <class Policy>
 static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& opt, const Policy& P,
                         unsigned long long* counter, cudaStream_t s) {
-    const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * kMarchThreads * sizeof(float) +
-                        (size_t)kPoolWords * kMarchThreads * sizeof(uint32_t) + (kMaxCk + 4) * sizeof(float);
     // cone stepping (dt follows t) folds nothing: events are applied in place, without the queue
     // (measured: through the queue a cfg4 march takes 43 ms against 24 ms applied in place)
     const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
+    const int threads = direct ? kConeThreads : kMarchThreads;
+    const size_t smem = (size_t)((G.mip_words + 3) & ~3) * 4 + (size_t)kQ * threads * sizeof(float) +
+                        (size_t)kPoolWords * threads * sizeof(uint32_t) + (kMaxCk + 4) * sizeof(float);
     auto kernel = G.mip != nullptr ? (direct ? march_kernel<true, true, Policy> : march_kernel<true, false, Policy>)
                                    : (direct ? march_kernel<false, true, Policy> : march_kernel<false, false, Policy>);
     if (G.n_grids == 1)
@@ -785,11 +792,11 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     MarchOpts o2 = opt;
     {
         const long long n_work = A.ray_list ? A.n_work : A.n_rays;
-        const long long warps = b * (kMarchThreads / 32);
+        const long long warps = b * (threads / 32);
         long long per = ceil_div<long long>(n_work, warps * 2);
         o2.batch = (int)(per < 8 ? 8 : (per > 32 ? 32 : per));
     }
-    kernel<<<(unsigned)b, kMarchThreads, smem, s>>>(A, G, o2, P, counter);
+    kernel<<<(unsigned)b, threads, smem, s>>>(A, G, o2, P, counter);
     count_launch();
     NFB_CHECK_LAUNCH("march_kernel");
     return NFB_OK;
@@ -853,7 +860,7 @@ static RunPool pool_of(void* run_buf, long long n, unsigned long long* cursor) {
 // the piece log of n rays (see nfb_traverse_piece_bytes): chunk_fill ints (padded to 16 B) | records
 static int piece_chunks(long long n) {
     // kPiecesPerRay records per ray on average + one partly used chunk per marching warp
-    const long long warps = (long long)sm_count() * 2 * (kMarchThreads / 32);
+    const long long warps = (long long)sm_count() * 2 * (kConeThreads / 32);
     long long c = (n * kPiecesPerRay + kPieceChunk - 1) / kPieceChunk + (n / 32 + 1 < warps ? n / 32 + 1 : warps) + 1;
     return (int)(c < (1ll << 30) ? c : (1ll << 30));
 }
