@@ -266,10 +266,24 @@ constexpr int kMarchThreads = 384;  // x 2 CTAs/SM: 85 registers per thread (512
 // at 2^20 rays 10.03 -> 10.14 ms; 640 threads: 2.06 / 11.7 ms); the queue kernels lose 7 % at 512 and stay at 384.
 template <bool DIRECT> constexpr int march_threads() { return DIRECT ? kConeThreads : kMarchThreads; }
 
-template <bool MIP, bool DIRECT, class Policy, bool SINGLE = false>
+// One thread per ray: the ray's first segment and its DDA state at the occupied box (prepare_ray), 64 bytes
+// per ray, for a march_kernel launched right behind it with `prepped` set.
+__global__ void __launch_bounds__(256)
+march_prepare_kernel(const RayArgs A, const GridSpec G, bool clip, uint4* __restrict__ out) {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= A.n_rays) return;
+    uint32_t w[16];
+    prepare_ray(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices, A.hits, G, r, clip, w);
+    out[4 * r] = make_uint4(w[0], w[1], w[2], w[3]);
+    out[4 * r + 1] = make_uint4(w[4], w[5], w[6], w[7]);
+    out[4 * r + 2] = make_uint4(w[8], w[9], w[10], w[11]);
+    out[4 * r + 3] = make_uint4(w[12], w[13], w[14], w[15]);
+}
+
+template <bool MIP, bool DIRECT, class Policy, bool SINGLE = false, bool PREPPED = false>
 __global__ void __launch_bounds__(march_threads<DIRECT>(), 2)
 march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
-             unsigned long long* ray_counter) {
+             unsigned long long* ray_counter, const uint4* __restrict__ prepped) {
     extern __shared__ uint32_t s_dyn[];
     GridSpec G = stage_mip(Gp, s_dyn);
     if (SINGLE) G.n_grids = 1;
@@ -286,9 +300,9 @@ march_kernel(const RayArgs A, const GridSpec Gp, const MarchOpts opt, Policy P,
     MarchOpts o = opt;
     if (A.limit_dev) o.limit = *A.limit_dev;
     const long long n_work = A.n_work_dev ? (long long)*A.n_work_dev : (A.ray_list ? A.n_work : A.n_rays);
-    march_engine<MIP, DIRECT>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
+    march_engine<MIP, DIRECT, Policy, PREPPED>(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices,
                  A.hits, A.ray_list, n_work, G, o, P, s_evt, s_pool, s_ck, *s_nck,
-                 ray_counter);
+                 ray_counter, prepped);
 }
 
 // Pass 2 of OccGridEstimator.sampling when pass 1 left a run buffer: no marching at all.
@@ -759,7 +773,7 @@ constexpr size_t kCounterBytes = 64;  // ray counter + overflow counter, at the 
 // for the mip and the event queue; zeroes the ray counter first.
 template <class Policy>
 static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& opt, const Policy& P,
-                        unsigned long long* counter, cudaStream_t s) {
+                        unsigned long long* counter, cudaStream_t s, uint4* prep_buf = nullptr, bool clip = false) {
     // cone stepping (dt follows t) folds nothing: events are applied in place, without the queue
     // (measured: through the queue a cfg4 march takes 43 ms against 24 ms applied in place)
     const bool direct = opt.step_size > 0.0f && opt.cone_angle != 0.0f;
@@ -796,7 +810,24 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
         long long per = ceil_div<long long>(n_work, warps * 2);
         o2.batch = (int)(per < 8 ? 8 : (per > 32 ? 32 : per));
     }
-    kernel<<<(unsigned)b, threads, smem, s>>>(A, G, o2, P, counter);
+    const uint4* prepped = nullptr;
+    bool use_prep = false;
+    if constexpr (std::is_same<Policy, CountPolicy<1>>::value)
+        use_prep = prep_buf != nullptr && !direct && G.n_grids == 1 && A.ray_list == nullptr && A.n_work_dev == nullptr &&
+                   A.n_rays > 0;
+    if (use_prep) {
+        if constexpr (std::is_same<Policy, CountPolicy<1>>::value)
+            kernel = G.mip != nullptr ? march_kernel<true, false, Policy, true, true> : march_kernel<false, false, Policy, true, true>;
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+            set_error("cannot reserve %zu bytes of shared memory for the marching kernel", smem);
+            return NFB_ERR_CUDA;
+        }
+        march_prepare_kernel<<<(unsigned)ceil_div<long long>(A.n_rays, 256), 256, 0, s>>>(A, G, clip, prep_buf);
+        count_launch();
+        NFB_CHECK_LAUNCH("march_prepare_kernel");
+        prepped = prep_buf;
+    }
+    kernel<<<(unsigned)b, threads, smem, s>>>(A, G, o2, P, counter, prepped);
     count_launch();
     NFB_CHECK_LAUNCH("march_kernel");
     return NFB_OK;
@@ -875,6 +906,11 @@ static PieceLog pieces_of(void* buf, long long n, unsigned long long* counters) 
     return L;
 }
 
+static uint4* prepared_of(void* scratch, long long n_rays) {
+    const size_t one = (ray_scan_status_bytes(n_rays) + 63) & ~(size_t)63;
+    return reinterpret_cast<uint4*>(static_cast<char*>(scratch) + 2 * one);
+}
+
 static unsigned long long* counters_of(void* scratch, size_t scratch_bytes, long long n_rays) {
     const size_t need = nfb_traverse_scratch_bytes(n_rays);
     if (scratch == nullptr || scratch_bytes < need) return nullptr;
@@ -896,8 +932,9 @@ static int scan_both(int64_t* sample_info, int64_t* interval_info, long long n_r
 extern "C" {
 
 NFB_API size_t nfb_traverse_scratch_bytes(int64_t n_rays) {
+    // two ray-scan status arrays | prepared-ray records (64 B per ray) | counters
     const size_t one = (nfb::ray_scan_status_bytes(n_rays) + 63) & ~(size_t)63;
-    return 2 * one + nfb::kCounterBytes;
+    return 2 * one + (size_t)(n_rays > 0 ? n_rays : 0) * 64 + nfb::kCounterBytes;
 }
 
 NFB_API int nfb_ray_aabb_intersect(const float* rays_o, const float* rays_d, const float* aabbs,
@@ -1011,7 +1048,10 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
         P.pool = pool_of(run_buf, rays->n_rays, counters + 2);
         P.pieces = PieceLog{};
         cudaMemsetAsync(counters + 1, 0, 2 * sizeof(unsigned long long), s);
-        rc = launch_march(A, G, to_opts(march), P, counters, s);
+        // (the engine's `clip`: constant dt folds empty cells; without termination planes the walk may stop
+        // at the occupied box)
+        rc = launch_march(A, G, to_opts(march), P, counters, s, prepared_of(scratch, rays->n_rays),
+                          /*clip=*/termination_planes == nullptr);
     } else {
         CountPolicy<0> P;
         P.sample_info = sample_info; P.interval_info = interval_info; P.term = termination_planes;

@@ -484,9 +484,53 @@ __device__ __forceinline__ void load_events(const float (&o)[3], const float (&d
 // Sink: run(P, t0, q, k, continuous, nS, nI) — k samples with edges t0 + j*q (constant-dt runs) —
 // and one(P, t_last, t_next, continuous, nS, nI); `continuous`, nS, nI are the state before the call.
 //
+// What the walk of a ray starts from: its first segment, the DDA set up in it and moved to the occupied
+// box (jump_ahead).  16 words: [0] 1 = has a segment, 2 = misses the occupied box; [1] level, segment
+// index, step signs, pulled-in-stop mask; [2] end of the empty stretch before the first cell walked;
+// [3] the segment's t_max; [4..15] tdist, delta, cur, stop.  Computed inside the march (prepare) or, for
+// the plain single-level count pass, by march_prepare_kernel ahead of it: a thread per ray at full
+// occupancy instead of 500 instructions inlined into a kernel that is short of registers.
+__device__ __forceinline__ void prepare_ray(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                            const float* __restrict__ near_arr, float near_s,
+                                            const float* __restrict__ far_arr, float far_s,
+                                            const float* __restrict__ t_sorted, const int64_t* __restrict__ t_indices,
+                                            const uint8_t* __restrict__ hits, const GridSpec& G, long long cand,
+                                            bool clip, uint32_t (&w)[16]) {
+    const int m = G.n_grids;
+    float o[3], d[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { o[k] = __ldg(rays_o + 3 * cand + k); d[k] = __ldg(rays_d + 3 * cand + k); }
+    const float near = near_arr ? __ldg(near_arr + cand) : near_s;
+    const float far = far_arr ? __ldg(far_arr + cand) : far_s;
+    RayEvents pev;
+    load_events(o, d, cand, t_sorted, t_indices, hits, G, pev);
+    Dda S = {};
+    float tmin = 0.0f, tmax = 0.0f, t_first = 0.0f;
+    int level = 0, si = 0;
+    bool miss = false;
+    const bool found = find_segment(pev, m, si, near, far, tmin, tmax, level);
+    if (found) {
+        setup_dda(o, d, G, level, tmin, tmax, S, clip);
+        t_first = tmin;
+        if (clip) miss = jump_ahead(o, d, G, level, tmin, tmax, S, t_first);
+    }
+    w[0] = (found ? 1u : 0u) | (miss ? 2u : 0u);
+    w[1] = (found ? 1u : 0u) | ((uint32_t)level << 1) | ((uint32_t)si << 8) | ((uint32_t)(S.stepi[0] + 1) << 16) |
+           ((uint32_t)(S.stepi[1] + 1) << 18) | ((uint32_t)(S.stepi[2] + 1) << 20) | ((uint32_t)S.cm << 22);
+    w[2] = __float_as_uint(t_first);  // end of the (empty) stretch before the first cell walked
+    w[3] = __float_as_uint(tmax);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        w[4 + k] = __float_as_uint(S.tdist[k]);
+        w[7 + k] = __float_as_uint(S.delta[k]);
+        w[10 + k] = (uint32_t)S.cur[k];
+        w[13 + k] = (uint32_t)S.stop[k];
+    }
+}
+
 // Shared memory: s_evt = [kQ][blockDim.x] floats (event queue), s_pool = [warps][kPoolWords][32]
 // words (prepared rays).
-template <bool MIP, bool DIRECT, class Policy>
+template <bool MIP, bool DIRECT, class Policy, bool PREPPED = false>
 __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const float* __restrict__ rays_d,
                                              const float* __restrict__ near_arr, float near_s,
@@ -498,7 +542,8 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
                                              const GridSpec& G, const MarchOpts& opt, Policy& P,
                                              float* __restrict__ s_evt, uint32_t* __restrict__ s_pool,
                                              const float* __restrict__ s_ck, int n_ck,
-                                             unsigned long long* __restrict__ ray_counter) {
+                                             unsigned long long* __restrict__ ray_counter,
+                                             const uint4* __restrict__ prepped = nullptr) {
     const int m = G.n_grids;
     const float step = opt.step_size, cone = opt.cone_angle;
     const int cap = opt.limit > 0 ? opt.limit : 0x7fffffff;
@@ -703,29 +748,22 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         // work item -> ray id (identity unless a work list is given)
         const long long cand = !ok ? 0 : (ray_list ? (long long)__ldg(ray_list + base + lane) : (long long)base + lane);
         if (ok && !P.accept(cand)) { P.skipped(cand); ok = false; }
-        Dda S = {};
-        float tmin = 0.0f, tmax = 0.0f, t_first = 0.0f;
-        int level = 0, si = 0;
-        bool found = false, miss = false;
+        uint32_t w[16];
         if (ok) {
-            float o[3], d[3];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) { o[k] = __ldg(rays_o + 3 * cand + k); d[k] = __ldg(rays_d + 3 * cand + k); }
-            const float near = near_arr ? __ldg(near_arr + cand) : near_s;
-            const float far = far_arr ? __ldg(far_arr + cand) : far_s;
-            RayEvents pev;
-            load_events(o, d, cand, t_sorted, t_indices, hits, G, pev);
-            found = find_segment(pev, m, si, near, far, tmin, tmax, level);
-            if (found) {
-                setup_dda(o, d, G, level, tmin, tmax, S, clip);
-                t_first = tmin;
-                if (clip) miss = jump_ahead(o, d, G, level, tmin, tmax, S, t_first);
+            if constexpr (PREPPED) {
+                const uint4 a0 = __ldg(prepped + 4 * cand), a1 = __ldg(prepped + 4 * cand + 1),
+                            a2 = __ldg(prepped + 4 * cand + 2), a3 = __ldg(prepped + 4 * cand + 3);
+                w[0] = a0.x; w[1] = a0.y; w[2] = a0.z; w[3] = a0.w; w[4] = a1.x; w[5] = a1.y; w[6] = a1.z; w[7] = a1.w;
+                w[8] = a2.x; w[9] = a2.y; w[10] = a2.z; w[11] = a2.w; w[12] = a3.x; w[13] = a3.y; w[14] = a3.z; w[15] = a3.w;
+            } else {
+                prepare_ray(rays_o, rays_d, near_arr, near_s, far_arr, far_s, t_sorted, t_indices, hits, G, cand, clip, w);
             }
+            const bool found = w[0] & 1u, miss = w[0] & 2u;
             // A ray that cannot yield anything (no segment, or — one level — one that misses the
             // occupied box) is retired here: no marker in the event queue, no cell walked.
             if (!found || (miss && m == 1)) {
                 typename Policy::Sink s0 = P.begin(cand);
-                P.end(cand, s0, 0, 0, near);
+                P.end(cand, s0, 0, 0, near_arr ? __ldg(near_arr + cand) : near_s);
                 ok = false;
             }
         }
@@ -733,20 +771,8 @@ __device__ __forceinline__ void march_engine(const float* __restrict__ rays_o,
         if (ok) {
             uint32_t* __restrict__ e = pool + __popc(okm & lt_mask);
             e[0 * 32] = (uint32_t)(int)cand;
-            e[1 * 32] = (found ? 1u : 0u) | ((uint32_t)level << 1) | ((uint32_t)si << 8) |
-                        ((uint32_t)(S.stepi[0] + 1) << 16) | ((uint32_t)(S.stepi[1] + 1) << 18) |
-                        ((uint32_t)(S.stepi[2] + 1) << 20) | ((uint32_t)S.cm << 22);
-            if (found) {
-                e[2 * 32] = __float_as_uint(t_first);  // end of the (empty) stretch before the first cell walked
-                e[3 * 32] = __float_as_uint(tmax);
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    e[(4 + k) * 32] = __float_as_uint(S.tdist[k]);
-                    e[(7 + k) * 32] = __float_as_uint(S.delta[k]);
-                    e[(10 + k) * 32] = (uint32_t)S.cur[k];
-                    e[(13 + k) * 32] = (uint32_t)S.stop[k];
-                }
-            }
+            for (int k = 1; k < 16; ++k) e[k * 32] = w[k];
         }
         pool_head = 0;
         pool_cnt = __popc(okm);
