@@ -221,20 +221,30 @@ __global__ void __launch_bounds__(kPdfWarps * 32) importance_sampling_tile_kerne
                     if (u_floor > u) t = __fmul_rn(__fadd_rn(t_min, t_min), 0.5f);  // degenerate pair (0, 0): du = 0 < 1e-10
                     return t;
                 };
-                float carry_prev = 0.0f;  // centre of sample i0 - 1
-                for (int i0 = 0; i0 < n_out; i0 += L) {
-                    const int sid = i0 + ll;
-                    const float t = centre(sid);
-                    float t_prev = __shfl_up_sync(kFull, t, 1, L);
-                    if (ll == 0) t_prev = carry_prev;
-                    carry_prev = __shfl_sync(kFull, t, L - 1, L);
-                    const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
-                    if (sid < n_out && live) {
-                        if (CENTRES) gs[i0] = t;
-                        ge[i0] = e;  // (edge 0 is patched below)
-                        if (STOT) gt[i0] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
+                // the ordinary ray: a bin that is not flat and an increasing u (u_step >= 0 makes every
+                // u >= cdf[0]) — the two selects above cannot fire, so its loop does not carry them
+                auto centre_plain = [&](int k) {
+                    const float u = __fmaf_rn(__fadd_rn((float)k, b), u_step, u_floor);
+                    return __fmaf_rn(__fsub_rn(u, u_floor), slope1, t_min);
+                };
+                auto rounds = [&](auto&& centre_of) {
+                    float carry_prev = 0.0f;  // centre of sample i0 - 1
+                    for (int i0 = 0; i0 < n_out; i0 += L) {
+                        const int sid = i0 + ll;
+                        const float t = centre_of(sid);
+                        float t_prev = __shfl_up_sync(kFull, t, 1, L);
+                        if (ll == 0) t_prev = carry_prev;
+                        carry_prev = __shfl_sync(kFull, t, L - 1, L);
+                        const float e = __fmul_rn(__fadd_rn(t, t_prev), 0.5f);
+                        if (sid < n_out && live) {
+                            if (CENTRES) gs[i0] = t;
+                            ge[i0] = e;  // (edge 0 is patched below)
+                            if (STOT) gt[i0] = stot_apply(STOT, e, p.stot_c0, p.stot_c1);
+                        }
                     }
-                }
+                };
+                if (!flat1 && u_step >= 0.0f) rounds(centre_plain);
+                else rounds(centre);
                 t0 = centre(0); t1 = centre(1); tl = centre(n_out - 1); tl2 = centre(n_out - 2);
             } else {
                 if (BINS == 2) {
