@@ -153,7 +153,7 @@ __device__ __forceinline__ long long lookback_count(unsigned long long* st, int 
 }
 
 template <bool DENSITY>
-__global__ void __launch_bounds__(kThreads, 4) vis_compact_kernel(const VisCompactArgs q) {
+__global__ void __launch_bounds__(kThreads, 5) vis_compact_kernel(const VisCompactArgs q) {
     const WeightFwdArgs& p = q.w;
     __shared__ TileSmem sm;
     __shared__ uint32_t s_mask[kWarps][kVec][4];  // survivors of (warp, vector, component) by lane
