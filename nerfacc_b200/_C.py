@@ -295,7 +295,14 @@ def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+_RAW_STREAM = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device: torch.device) -> int:
+    """The current stream's handle on `device` (the raw accessor: a tenth of the cost of building a
+    torch.cuda.Stream object, and this runs before every native call)."""
+    if _RAW_STREAM is not None:
+        return _RAW_STREAM(device.index if device.index is not None else torch.cuda.current_device())
     return torch.cuda.current_stream(device).cuda_stream
 
 
@@ -318,8 +325,7 @@ _EPOCH_MAX = (1 << 30) - 2
 def workspace(device: torch.device, n_elements: int) -> Tuple[torch.Tensor, int, int]:
     """Returns (buffer, nbytes, epoch) for one flat-kernel launch on the current stream."""
     need = int(lib().nfb_workspace_bytes(max(int(n_elements), 1)))
-    key = (device.index if device.index is not None else torch.cuda.current_device(),
-           torch.cuda.current_stream(device).cuda_stream)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), stream_ptr(device))
     ws = _WS.get(key)
     if ws is None:
         ws = _WS[key] = _Workspace()
@@ -346,7 +352,7 @@ def scratch(device: torch.device, nbytes: int, tag: str = "ray") -> torch.Tensor
     """A persistent uint8 scratch buffer per (device, stream, tag), separate from the look-back
     workspace (kernels that clear their own scratch must not disturb its epochs)."""
     key = (device.index if device.index is not None else torch.cuda.current_device(),
-           torch.cuda.current_stream(device).cuda_stream, tag)
+           stream_ptr(device), tag)
     buf = _SCRATCH.get(key)
     if buf is None or buf.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing() and buf is not None:
