@@ -261,7 +261,8 @@ NFB_API int nfb_pack_occupancy(const uint8_t* binaries, int32_t n_grids, const i
 NFB_API int nfb_occupancy_bounds(const uint32_t* bits, int32_t n_grids, const int32_t* res_host,
                                  int32_t* bounds, nfb_stream_t stream);
 
-/* Scratch needed by the traversal entry points (per-ray scan status words + ray counters). */
+/* Scratch needed by the traversal entry points: per-ray scan status words, ray counters and 64 bytes
+ * per ray for the prepared-ray records of the plain single-level count pass (16-byte aligned). */
 NFB_API size_t nfb_traverse_scratch_bytes(int64_t n_rays);
 
 /* Pass 1 (csrc/grid.cu:413-438 + data_spec.hpp:90-93): per-ray counts -> complete, canonical

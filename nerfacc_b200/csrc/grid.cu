@@ -1050,7 +1050,8 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
         cudaMemsetAsync(counters + 1, 0, 2 * sizeof(unsigned long long), s);
         // (the engine's `clip`: constant dt folds empty cells; without termination planes the walk may stop
         // at the occupied box)
-        rc = launch_march(A, G, to_opts(march), P, counters, s, prepared_of(scratch, rays->n_rays),
+        rc = launch_march(A, G, to_opts(march), P, counters, s,
+                          aligned16(scratch) ? prepared_of(scratch, rays->n_rays) : nullptr,
                           /*clip=*/termination_planes == nullptr);
     } else {
         CountPolicy<0> P;
