@@ -198,7 +198,11 @@ NFB_API int nfb_composite_bwd(int from_density, const float* g_colors, const flo
 
 /* ------------------------------------------------------------------------------------
  * pack_info: ray_indices [n] -> packed_info [n_rays, 2] (nerfacc/pack.py:43-46: histogram of
- * the indices, starts = exclusive cumsum).  `workspace` needs 8 bytes per 2048 rays.
+ * the indices, starts = exclusive cumsum).  `workspace` needs 8 bytes per 2048 rays (rounded up)
+ * plus 8; packed_info must be 16-byte aligned.  Sorted indices — what every producer on this path
+ * emits — take two plain passes (run boundaries, then counts: no zero-fill, no atomics, no scan); an
+ * index that decreases is noticed on the device and the general pass (atomics per run + a scan over
+ * the rays) redoes the work behind it, without a host round trip.
  */
 NFB_API int nfb_pack_info(const int64_t* ray_indices, int64_t n, int64_t n_rays,
                           int64_t* packed_info, void* workspace, size_t workspace_bytes,

@@ -22,7 +22,7 @@
 namespace nfb {
 
 int launch_ray_scan(int64_t* packed_info, long long n_rays, long long* total_out, void* status,
-                    cudaStream_t s);
+                    cudaStream_t s, const unsigned long long* only_if = nullptr);
 size_t ray_scan_status_bytes(long long n_rays);
 
 struct RayArgs {

@@ -17,7 +17,8 @@ namespace nfb {
 constexpr int kHistPerThread = 4;
 __global__ void __launch_bounds__(kThreads)
 pack_hist_kernel(const int64_t* __restrict__ ray_indices, long long n, long long n_rays,
-                 int64_t* __restrict__ packed_info, bool vec_ok) {
+                 int64_t* __restrict__ packed_info, bool vec_ok, const unsigned long long* __restrict__ only_if) {
+    if (only_if != nullptr && *only_if == 0ull) return;  // the sorted pass has done the work
     const int lane = lane_id();
     const long long per_block = (long long)kThreads * kHistPerThread;
     for (long long base = (long long)blockIdx.x * per_block; base < n; base += (long long)gridDim.x * per_block) {
@@ -50,6 +51,66 @@ pack_hist_kernel(const int64_t* __restrict__ ray_indices, long long n, long long
                 atomicAdd(reinterpret_cast<unsigned long long*>(packed_info + 2 * r + 1), (unsigned long long)add);
         }
     }
+}
+
+// The same for SORTED ray_indices (what every producer on this path emits), without zero-filling,
+// atomics or a scan: at every position i where the index changes from a to b, the rays in (a, b] start
+// at i and the rays in [a, b) end at i — plain stores, each ray written once; pack_finish_kernel turns
+// (start, end) into (start, count) and fills in the rays after the last index.  An index that
+// decreases (or lies outside [0, n_rays)) raises *flag: pack_finish_kernel then zero-fills instead and
+// the general pass above (pack_hist_kernel + ray scan, launched behind with only_if = flag) takes over —
+// the caller never has to know, and no host round trip is needed to find out.
+constexpr int kRunsPerThread = 4;  // (8 per thread: no faster — the pass is bound by its scattered 8-byte stores)
+__global__ void __launch_bounds__(kThreads)
+pack_runs_kernel(const int64_t* __restrict__ ray_indices, long long n, long long n_rays,
+                 int64_t* __restrict__ packed_info, bool vec_ok, unsigned long long* __restrict__ flag) {
+    const int lane = lane_id();
+    const long long per_block = (long long)kThreads * kRunsPerThread;
+    for (long long base = (long long)blockIdx.x * per_block; base < n; base += (long long)gridDim.x * per_block) {
+        const long long i0 = base + (long long)threadIdx.x * kRunsPerThread;
+        long long v[kRunsPerThread];
+        if (vec_ok && i0 + kRunsPerThread <= n) {
+#pragma unroll
+            for (int c = 0; c < kRunsPerThread; c += 2) {
+                const longlong2 a = __ldg(reinterpret_cast<const longlong2*>(ray_indices + i0 + c));
+                v[c] = a.x; v[c + 1] = a.y;
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < kRunsPerThread; ++c) v[c] = (i0 + c < n) ? __ldg(ray_indices + i0 + c) : -1;
+        }
+        long long prev = __shfl_up_sync(kFull, v[kRunsPerThread - 1], 1);
+        if (lane == 0) prev = (i0 > 0 && i0 - 1 < n) ? __ldg(ray_indices + i0 - 1) : -1;
+#pragma unroll
+        for (int c = 0; c < kRunsPerThread; ++c) {
+            const long long i = i0 + c;
+            if (i >= n) break;
+            const long long r = v[c];
+            const long long before = c == 0 ? prev : v[c - 1];
+            if (r < 0 || r >= n_rays || before > r) { *flag = 1ull; continue; }
+            if (before != r) {
+                packed_info[2 * r] = i;                             // r starts here
+                if (before >= 0) packed_info[2 * before + 1] = i;   // `before` ends here
+                if (r > before + 1) {                               // rays without samples in between (rare)
+                    for (long long rr = before + 1; rr < r; ++rr)
+                        *reinterpret_cast<longlong2*>(packed_info + 2 * rr) = make_longlong2(i, i);
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+pack_finish_kernel(const int64_t* __restrict__ ray_indices, long long n, long long n_rays,
+                   int64_t* __restrict__ packed_info, const unsigned long long* __restrict__ flag) {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_rays) return;
+    longlong2* __restrict__ e = reinterpret_cast<longlong2*>(packed_info) + r;
+    if (*flag != 0ull) { *e = make_longlong2(0, 0); return; }  // zero-filled for the general pass
+    const long long r_last = n > 0 ? __ldg(ray_indices + n - 1) : -1;
+    if (r > r_last) { *e = make_longlong2(n, 0); return; }
+    const longlong2 se = *e;
+    *e = make_longlong2(se.x, (r == r_last ? n : se.y) - se.x);
 }
 
 // ---- sample positions (the callers' side of the callbacks) -----------------
@@ -122,7 +183,8 @@ sample_positions_kernel(const float* __restrict__ rays_o, const float* __restric
 constexpr int kRayTile = 2048;
 __global__ void __launch_bounds__(kThreads)
 ray_scan_kernel(int64_t* __restrict__ packed_info, long long n_rays, long long* __restrict__ total_out,
-                unsigned long long* status) {
+                unsigned long long* status, const unsigned long long* __restrict__ only_if) {
+    if (only_if != nullptr && *only_if == 0ull) return;
     __shared__ long long s_warp[kWarps];
     __shared__ long long s_carry;
     const long long tile = blockIdx.x;
@@ -174,20 +236,21 @@ ray_scan_kernel(int64_t* __restrict__ packed_info, long long n_rays, long long* 
     }
 }
 
+// one status word per tile of rays + one spare word (pack_info's "not sorted" flag)
 size_t ray_scan_status_bytes(long long n_rays) {
-    return (size_t)ceil_div<long long>(n_rays > 0 ? n_rays : 1, kRayTile) * sizeof(unsigned long long);
+    return (size_t)(ceil_div<long long>(n_rays > 0 ? n_rays : 1, kRayTile) + 1) * sizeof(unsigned long long);
 }
 
 // Launch the in-place per-ray scan; `status` must hold ray_scan_status_bytes(n_rays).
 int launch_ray_scan(int64_t* packed_info, long long n_rays, long long* total_out,
-                    void* status, cudaStream_t s) {
+                    void* status, cudaStream_t s, const unsigned long long* only_if) {
     const long long nt = ceil_div<long long>(n_rays, kRayTile);
     if (cudaMemsetAsync(status, 0, (size_t)nt * sizeof(unsigned long long), s) != cudaSuccess) {
         set_error("ray scan: memset failed");
         return NFB_ERR_CUDA;
     }
     ray_scan_kernel<<<(unsigned)nt, kThreads, 0, s>>>(packed_info, n_rays, total_out,
-                                                      static_cast<unsigned long long*>(status));
+                                                      static_cast<unsigned long long*>(status), only_if);
     count_launch();
     NFB_CHECK_LAUNCH("ray_scan");
     return NFB_OK;
@@ -207,17 +270,29 @@ NFB_API int nfb_pack_info(const int64_t* ray_indices, int64_t n, int64_t n_rays,
     NFB_CHECK_ARG(workspace != nullptr && workspace_bytes >= ray_scan_status_bytes(n_rays),
                   "workspace too small for %lld rays", (long long)n_rays);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    cudaMemsetAsync(packed_info, 0, sizeof(int64_t) * 2 * n_rays, s);
+    NFB_CHECK_ARG(aligned16(packed_info), "packed_info must be 16-byte aligned");
+    // sorted pass (pack_runs + pack_finish); the general pass behind it runs only if an index decreased
+    const long long nt = ceil_div<long long>(n_rays, kRayTile);
+    unsigned long long* flag = static_cast<unsigned long long*>(workspace) + nt;  // the status array's spare word
+    cudaMemsetAsync(flag, 0, sizeof(unsigned long long), s);
+    long long nb = ceil_div<long long>(n > 0 ? n : 1, (long long)kThreads * kHistPerThread);
+    const long long cap = (long long)sm_count() * 16;
+    if (nb > cap) nb = cap;
     if (n > 0) {
-        long long nb = ceil_div<long long>(n, (long long)kThreads * kHistPerThread);
-        const long long cap = (long long)sm_count() * 16;
-        if (nb > cap) nb = cap;
-        pack_hist_kernel<<<(unsigned)nb, kThreads, 0, s>>>(ray_indices, n, n_rays, packed_info,
-                                                           aligned16(ray_indices));
+        long long nr = ceil_div<long long>(n, (long long)kThreads * kRunsPerThread);
+        if (nr > cap) nr = cap;
+        pack_runs_kernel<<<(unsigned)nr, kThreads, 0, s>>>(ray_indices, n, n_rays, packed_info, aligned16(ray_indices), flag);
         count_launch();
-        NFB_CHECK_LAUNCH("pack_hist");
+        NFB_CHECK_LAUNCH("pack_runs");
     }
-    return launch_ray_scan(packed_info, n_rays, nullptr, workspace, s);
+    pack_finish_kernel<<<(unsigned)ceil_div<long long>(n_rays, 256), 256, 0, s>>>(ray_indices, n, n_rays, packed_info, flag);
+    count_launch();
+    NFB_CHECK_LAUNCH("pack_finish");
+    if (n == 0) return NFB_OK;
+    pack_hist_kernel<<<(unsigned)nb, kThreads, 0, s>>>(ray_indices, n, n_rays, packed_info, aligned16(ray_indices), flag);
+    count_launch();
+    NFB_CHECK_LAUNCH("pack_hist");
+    return launch_ray_scan(packed_info, n_rays, nullptr, workspace, s, flag);
 }
 
 NFB_API int nfb_sample_positions(const float* rays_o, const float* rays_d, const int64_t* ray_indices,

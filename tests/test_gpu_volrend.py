@@ -264,6 +264,43 @@ def test_pack_info(device):
     assert empty.tolist() == [[0, 0]] * 5
 
 
+def _pack_info_torch(ri, n_rays):
+    """The reference's formula (pack.py:43-46) in torch."""
+    cnt = torch.zeros((n_rays,), dtype=torch.long, device=ri.device)
+    cnt.index_add_(0, ri, torch.ones_like(ri))
+    return torch.stack([cnt.cumsum(0) - cnt, cnt], -1)
+
+
+@pytest.mark.parametrize("case", ["sorted", "gaps", "tail", "unsorted", "one_decrease", "single_ray"])
+def test_pack_info_sorted_pass_and_fallback(device, case):
+    """Sorted indices take the two plain passes; an index that decreases anywhere is noticed on the device
+    and the general pass redoes the work: either way the result is the reference's formula."""
+    import nerfacc_b200 as nf
+
+    g = torch.Generator().manual_seed(5)
+    n_rays = 50000
+    if case == "sorted":
+        ri = torch.sort(torch.randint(0, n_rays, (400003,), generator=g)).values
+    elif case == "gaps":  # a few far-apart rays: long stretches of empty rays before, between and after
+        ri = torch.sort(torch.tensor([7, 7, 7, 123, 30000, 30000, 30001, 49000])).values
+    elif case == "tail":  # nothing beyond ray 10: 49989 trailing empty rays; leading empty rays too
+        ri = torch.sort(torch.randint(5, 11, (1000,), generator=g)).values
+    elif case == "unsorted":
+        ri = torch.randint(0, n_rays, (400003,), generator=g)
+    elif case == "one_decrease":  # sorted except for the very last element
+        ri = torch.sort(torch.randint(0, n_rays, (100000,), generator=g)).values
+        ri[-1] = 3
+    else:
+        ri = torch.full((70000,), 42, dtype=torch.long)
+    ri = ri.to(device)
+    got = nf.pack_info(ri, n_rays)
+    assert torch.equal(got, _pack_info_torch(ri, n_rays))
+    # and again on the same workspace (the flag is reset every call): sorted after unsorted, unsorted after sorted
+    other = torch.sort(ri).values if case in ("unsorted", "one_decrease") else ri.flip(0).contiguous()
+    assert torch.equal(nf.pack_info(other, n_rays), _pack_info_torch(other, n_rays))
+    assert torch.equal(nf.pack_info(ri[:], n_rays), got)
+
+
 def test_rendering_end_to_end(device):
     import nerfacc_b200 as nf
 
