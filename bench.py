@@ -27,6 +27,7 @@ packed path) and prints the same line with "impl": "reference".
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -75,33 +76,88 @@ def workload_name(n_rays: int) -> str:
 
 # ------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock and throttle reasons sampled while the timed region runs.  Default: NVML in this
+    process from a thread, every 20 ms (the queries `nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,
+    clocks_event_reasons.*` makes, without a second process attaching to the device — that attach
+    and each of its polls stalled launches for 10-30 ms, one timed pass in five).
+    NFB_BENCH_CLOCKS=smi selects the nvidia-smi poll (every 200 ms), =off none."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
+    # nvml.h nvmlClocksEventReasons bits
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+            "sw_power_cap": 0x4, "hw_power_brake_slowdown": 0x80}
 
     def __init__(self, gpu_index: int) -> None:
         self.idx, self.proc, self.lines = gpu_index, None, []
+        self.mode = os.environ.get("NFB_BENCH_CLOCKS", "nvml")
+        self.samples, self.sm_max, self._stop, self.thr, self.how = [], None, threading.Event(), None, None
+
+    def ready(self) -> bool:
+        return self.how is None or bool(self.samples) or bool(self.lines)
 
     def start(self) -> None:
+        if self.mode == "off":
+            return
+        if self.mode == "nvml":
+            try:
+                import pynvml
+
+                import torch
+
+                pynvml.nvmlInit()
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(self.idx).uuid))
+                except Exception:
+                    h = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+                self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+                reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) \
+                    or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+
+                def poll():
+                    while not self._stop.is_set():
+                        try:
+                            self.samples.append((float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
+                                                 int(reasons(h))))
+                        except Exception:
+                            pass
+                        self._stop.wait(0.02)
+
+                self.how = "nvml"
+                self.thr = threading.Thread(target=poll, daemon=True)
+                self.thr.start()
+                return
+            except Exception:
+                self.how = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.FIELDS}",
                  "--format=csv,noheader,nounits", "-lms", "200"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.how = "nvidia-smi"
             self.thr = threading.Thread(target=self._read, daemon=True)
             self.thr.start()
         except Exception:
-            self.proc = None
+            self.proc, self.how = None, None
 
     def _read(self) -> None:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
     def stop(self) -> dict:
+        if self.how == "nvml":
+            self._stop.set()
+            self.thr.join(timeout=1)
+            sm = [a for a, _ in self.samples]
+            seen = 0
+            for _, r in self.samples:
+                seen |= r
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.sm_max,
+                    "samples": len(sm), "reasons": sorted(k for k, b in self.BITS.items() if seen & b),
+                    "how": "NVML in-process, every 20 ms"}
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampler unavailable"]}
         time.sleep(0.25)
         self.proc.terminate()
         try:
@@ -123,7 +179,7 @@ class ClockSampler:
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None,
                 "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
-                "reasons": sorted(reasons)}
+                "reasons": sorted(reasons), "how": "nvidia-smi -lms 200"}
 
 
 # ------------------------------------------------------------------------------- CPU arm
@@ -509,12 +565,23 @@ def run_ours(args) -> None:
     def timed(fn, k, first_step, join=()):
         """k calls of fn, device-timed between two events on the main stream; `join`: streams the
         main stream waits for before the closing event, so their work lies inside the interval."""
+        gc.collect()  # (a full collection falls before the timed region, not inside it)
         barrier()
         state["step"] = first_step
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        marks = []
         for _ in range(k):
             fn()
+            if os.environ.get("NFB_BENCH_STEP_TIMES"):  # diagnostic: where in the pass the time went
+                marks.append((torch.cuda.Event(enable_timing=True), time.perf_counter()))
+                marks[-1][0].record()
+        if marks:
+            torch.cuda.synchronize()
+            dev_ms = [a.elapsed_time(b[0]) for a, b in zip([e0] + [m[0] for m in marks], marks)]
+            host_ms = [(b[1] - a[1]) * 1e3 for a, b in zip(marks, marks[1:])]
+            print("step ms (device):", [round(v, 2) for v in dev_ms], "host gaps:", [round(v, 2) for v in host_ms],
+                  file=sys.stderr)
         main = torch.cuda.current_stream(dev)
         for st in join:
             main.wait_stream(st)
@@ -533,6 +600,14 @@ def run_ours(args) -> None:
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
+        # nvidia-smi attaching to the device stalls launches for some milliseconds: keep the GPU
+        # under load (steps without a grid update, so no collective) until its first sample is in,
+        # so that the attach does not land inside the timed region that follows
+        t_settle = time.time()
+        while not clocks.ready() and time.time() - t_settle < 3.0:
+            state["step"] = FIRST + 1
+            step(o_dev, d_dev)
+            torch.cuda.synchronize()
     launches0 = _C.launch_count()
     ms_local = timed(lambda: step(o_dev, d_dev), args.steps, FIRST)
     launches = _C.launch_count() - launches0
@@ -569,12 +644,21 @@ def run_ours(args) -> None:
         def step_overlapped():
             (ri, ts, te), ev = pipe["cur"]
             main_s.wait_event(ev)
-            for t in (ri, ts, te):
-                t.record_stream(main_s)
             sigmas.grad = None
             rgbs.grad = None
             colors, opac, depth, _ = nf.rendering(ts, te, ri, n_rays, rgb_sigma_fn=field)
             torch.autograd.backward([colors, opac, depth], [g_c, g_o, g_d])
+            # the samples were allocated on the side stream and read on the main one: they stay alive
+            # one more step and the side stream waits for the main stream's last read before their
+            # memory returns to its pool (record_stream defers that to an event poll at some later
+            # allocation, and the pool then grows by a cudaMalloc in the middle of a pass)
+            done = torch.cuda.Event()
+            done.record(main_s)
+            old = pipe.get("prev")
+            pipe["prev"] = ((ri, ts, te), done)
+            if old is not None:
+                side.wait_event(old[1])
+            del old, ri, ts, te
             pipe["cur"] = march_next()
 
         side.wait_stream(main_s)

@@ -408,6 +408,20 @@ NFB_API int nfb_occ_binarize(const float* occs, int64_t n_cells, float occ_thre,
 NFB_API int nfb_mark_invisible_cells(const float* cams, int64_t n_cams, const int32_t* res_host,
                                      int32_t levels, const float* aabbs, float width, float height,
                                      float near_plane, float* occs, nfb_stream_t stream);
+/* The two data-dependent cell selections of OccGridEstimator._sample_uniform_and_occupied_cells
+ * (nerfacc/estimators/occ_grid.py:344-365), one launch each, order preserved:
+ *   candidates != NULL: the drawn cells with occs[candidates[i]] >= 0 (`uniform[occs[uniform] >= 0]`;
+ *                       occs = that level's slice, binaries = NULL);
+ *   binaries   != NULL: the indices i of the n cells with binaries[i] != 0 (`nonzero(binaries)`;
+ *                       occs = candidates = NULL).
+ * out[(base ? *base : 0) + k] = the k-th kept cell; *total = kept cells of THIS call.  `base` and
+ * `total` are device-visible; passing the first call's `total` as the second call's `base` appends
+ * the occupied cells behind the uniform ones with no host step in between (the reference: two
+ * boolean selects, each with its own host read-back, and a cat).
+ * workspace: nfb_compact_workspace_bytes(n). */
+NFB_API int nfb_occ_select_cells(const float* occs, const int64_t* candidates, const uint8_t* binaries,
+                                 int64_t n, const int64_t* base, int64_t* out, int64_t* total,
+                                 void* workspace, size_t workspace_bytes, nfb_stream_t stream);
 /* Keep the samples with mask[i] != 0, order preserved; *total (device-visible) = how many. */
 NFB_API size_t nfb_compact_workspace_bytes(int64_t n);
 NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,

@@ -121,6 +121,7 @@ _PROTOS = {
     "nfb_occ_binarize_workspace_bytes": [],
     "nfb_occ_binarize": [c_ptr, c_i64, c_f32, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_mark_invisible_cells": [c_ptr, c_i64, c_ptr, C.c_int32, c_ptr, c_f32, c_f32, c_f32, c_ptr, c_ptr],
+    "nfb_occ_select_cells": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_size, c_ptr],
     "nfb_compact_workspace_bytes": [c_i64],
     "nfb_compact_samples": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                             c_size, c_ptr],

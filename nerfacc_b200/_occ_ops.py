@@ -41,7 +41,8 @@ def all_reduce_max(occs: Tensor, group=None) -> None:
 def cell_points(cells: Tensor, u: Tensor, resolution: Tensor, aabb: Tensor) -> Tensor:
     """World positions of jittered cell samples (occ_grid.py:385-392)."""
     n = cells.shape[0]
-    res = [int(v) for v in resolution.tolist()]
+    # (a host list from the caller: `.tolist()` on a device tensor is a host round trip per call)
+    res = [int(v) for v in (resolution.tolist() if isinstance(resolution, Tensor) else resolution)]
     dev = _C.require_cuda(cells, u, aabb)
     x = torch.empty((n, 3), dtype=torch.float32, device=dev)
     if n:
@@ -52,6 +53,33 @@ def cell_points(cells: Tensor, u: Tensor, resolution: Tensor, aabb: Tensor) -> T
                                               aabb.data_ptr(), x.data_ptr(), _C.stream_ptr(dev))
         _C.check(rc, "occ_cell_points")
     return x
+
+
+def select_cells(occs_lvl: Tensor, uniform: Tensor, binaries_lvl: Tensor) -> Tuple[Tensor, int, int]:
+    """(cells, k1, k2): cells[:k1] = uniform[occs_lvl[uniform] >= 0], cells[k1:k1+k2] =
+    nonzero(binaries_lvl.flatten()) — the two selections of occ_grid.py:344-365 in two launches and
+    ONE host read-back (the reference: two boolean selects with a read-back each)."""
+    dev = _C.require_cuda(occs_lvl, uniform, binaries_lvl)
+    n, n_cells = uniform.shape[0], binaries_lvl.numel()
+    assert occs_lvl.is_contiguous() and occs_lvl.dtype == torch.float32 and occs_lvl.numel() == n_cells
+    uniform = uniform.long().contiguous()
+    bins = binaries_lvl.contiguous()
+    assert bins.dtype == torch.bool
+    out = torch.empty((n + n_cells,), dtype=torch.long, device=dev)
+    totals = _pinned_totals(dev)
+    with torch.cuda.device(dev):
+        lib = _C.lib()
+        ws = _C.scratch(dev, int(lib.nfb_compact_workspace_bytes(max(n, n_cells))), "select")
+        st = _C.stream_ptr(dev)
+        t0, t1 = totals.data_ptr(), totals.data_ptr() + 8
+        if n:  # (an empty tensor has no address to tell the two modes apart)
+            _C.check(lib.nfb_occ_select_cells(occs_lvl.data_ptr(), uniform.data_ptr(), None, n, None,
+                                              out.data_ptr(), t0, ws.data_ptr(), ws.numel(), st), "occ_select_cells")
+        if n_cells:
+            _C.check(lib.nfb_occ_select_cells(None, None, bins.data_ptr(), n_cells, t0 if n else None,
+                                              out.data_ptr(), t1, ws.data_ptr(), ws.numel(), st), "occ_select_cells")
+        torch.cuda.current_stream(dev).synchronize()
+    return out, int(totals[0]) if n else 0, int(totals[1]) if n_cells else 0
 
 
 def ema_update(occs: Tensor, cell_ids: Tensor, occ: Tensor, lo: int, hi: int, decay: float) -> None:
@@ -148,7 +176,7 @@ def mark_invisible_cells(occs: Tensor, cams: Tensor, resolution: Tensor, levels:
     at -1 are left alone.  cams: [n_cams, 21] = (w2c_R | w2c_T | K) per camera."""
     dev = _C.require_cuda(occs, cams, aabbs)
     assert occs.is_contiguous() and occs.dtype == torch.float32 and cams.shape[-1] == 21
-    res_host = (C.c_int32 * 3)(*[int(v) for v in resolution.tolist()])
+    res_host = (C.c_int32 * 3)(*[int(v) for v in (resolution.tolist() if isinstance(resolution, Tensor) else resolution)])
     aabbs = aabbs.float().contiguous()
     with torch.cuda.device(dev):
         rc = _C.lib().nfb_mark_invisible_cells(cams.data_ptr(), cams.shape[0], res_host, int(levels),

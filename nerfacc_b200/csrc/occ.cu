@@ -105,25 +105,15 @@ occ_binarize_kernel(const float* __restrict__ occs, long long n, const double* _
 // One tile = 256 threads x 8 items.  status word: count << 2 | state.
 constexpr int kCompItems = 8;
 constexpr int kCompTile = kThreads * kCompItems;
-__global__ void __launch_bounds__(kThreads)
-compact_kernel(const uint8_t* __restrict__ mask, const int64_t* __restrict__ ray_indices,
-               const float* __restrict__ t_starts, const float* __restrict__ t_ends, long long n,
-               int64_t* __restrict__ o_ray, float* __restrict__ o_ts, float* __restrict__ o_te,
-               long long* __restrict__ total, unsigned long long* status) {
+// Order-preserving output position of this thread's first kept item: an intra-tile scan of the
+// per-thread counts, then the tile's carry by decoupled look-back over `status` (zeroed by the
+// caller).  The last tile writes the number of kept items to `total`.  All threads call it.
+__device__ __forceinline__ long long tile_lookback_position(int cnt, unsigned long long* status,
+                                                            long long* __restrict__ total,
+                                                            const long long* base = nullptr) {
     __shared__ int s_warp[kWarps];
     __shared__ long long s_carry;
     const long long tile = blockIdx.x;
-    const long long i0 = tile * kCompTile + (long long)threadIdx.x * kCompItems;
-    uint8_t m[kCompItems];
-    int cnt = 0;
-    if (i0 + kCompItems <= n && ((reinterpret_cast<uintptr_t>(mask + i0) & 7u) == 0)) {
-        const unsigned long long w = *reinterpret_cast<const unsigned long long*>(mask + i0);
-#pragma unroll
-        for (int k = 0; k < kCompItems; ++k) { m[k] = (uint8_t)((w >> (8 * k)) & 0xff); cnt += m[k] ? 1 : 0; }
-    } else {
-#pragma unroll
-        for (int k = 0; k < kCompItems; ++k) { m[k] = (i0 + k < n) ? mask[i0 + k] : 0; cnt += m[k] ? 1 : 0; }
-    }
     int t = cnt;
     const int lane = lane_id(), w = warp_id();
 #pragma unroll
@@ -152,11 +142,31 @@ compact_kernel(const uint8_t* __restrict__ mask, const int64_t* __restrict__ ray
             }
             st_relaxed_u64(status + tile, ((unsigned long long)(X + agg) << 2) | 2ull);
         }
-        s_carry = X;
+        s_carry = X + (base ? *base : 0);  // (one read per tile: `base` may live in pinned host memory)
         if (tile == (long long)gridDim.x - 1 && total) *total = X + agg;
     }
     __syncthreads();
-    long long pos = s_carry + before + (t - cnt);
+    return s_carry + before + (t - cnt);
+}
+
+__global__ void __launch_bounds__(kThreads)
+compact_kernel(const uint8_t* __restrict__ mask, const int64_t* __restrict__ ray_indices,
+               const float* __restrict__ t_starts, const float* __restrict__ t_ends, long long n,
+               int64_t* __restrict__ o_ray, float* __restrict__ o_ts, float* __restrict__ o_te,
+               long long* __restrict__ total, unsigned long long* status) {
+    const long long tile = blockIdx.x;
+    const long long i0 = tile * kCompTile + (long long)threadIdx.x * kCompItems;
+    uint8_t m[kCompItems];
+    int cnt = 0;
+    if (i0 + kCompItems <= n && ((reinterpret_cast<uintptr_t>(mask + i0) & 7u) == 0)) {
+        const unsigned long long w = *reinterpret_cast<const unsigned long long*>(mask + i0);
+#pragma unroll
+        for (int k = 0; k < kCompItems; ++k) { m[k] = (uint8_t)((w >> (8 * k)) & 0xff); cnt += m[k] ? 1 : 0; }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kCompItems; ++k) { m[k] = (i0 + k < n) ? mask[i0 + k] : 0; cnt += m[k] ? 1 : 0; }
+    }
+    long long pos = tile_lookback_position(cnt, status, total);
 #pragma unroll
     for (int k = 0; k < kCompItems; ++k) {
         if (m[k]) {
@@ -167,6 +177,45 @@ compact_kernel(const uint8_t* __restrict__ mask, const int64_t* __restrict__ ray
             ++pos;
         }
     }
+}
+
+// ---- cell selection of the update (occ_grid.py:344-365) -------------------------------------
+// The two data-dependent selections `_sample_uniform_and_occupied_cells` makes per level, each one
+// launch, appended to one list: CANDIDATES: keep the drawn cells whose occupancy is not negative
+// (`uniform[occs[uniform] >= 0]`); otherwise the indices of the occupied cells in order
+// (`nonzero(binaries)`).  `base` (device, may be null): where this call's output starts in `out`
+// — the first call's `total`, so the second selection lands behind the first with no host step
+// between them.  `total`: kept items of THIS call.
+template <bool CANDIDATES>
+__global__ void __launch_bounds__(kThreads)
+select_cells_kernel(const float* __restrict__ occs, const int64_t* __restrict__ candidates,
+                    const uint8_t* __restrict__ binaries, long long n, const long long* __restrict__ base,
+                    int64_t* __restrict__ out, long long* __restrict__ total, unsigned long long* status) {
+    const long long i0 = (long long)blockIdx.x * kCompTile + (long long)threadIdx.x * kCompItems;
+    int64_t v[kCompItems];
+    unsigned keep = 0;
+    if constexpr (CANDIDATES) {
+#pragma unroll
+        for (int k = 0; k < kCompItems; ++k) v[k] = (i0 + k < n) ? candidates[i0 + k] : -1;
+#pragma unroll
+        for (int k = 0; k < kCompItems; ++k)
+            if (v[k] >= 0 && __ldg(occs + v[k]) >= 0.0f) keep |= 1u << k;
+    } else {
+        if (i0 + kCompItems <= n && ((reinterpret_cast<uintptr_t>(binaries + i0) & 7u) == 0)) {
+            const unsigned long long w = *reinterpret_cast<const unsigned long long*>(binaries + i0);
+#pragma unroll
+            for (int k = 0; k < kCompItems; ++k) if ((w >> (8 * k)) & 0xff) keep |= 1u << k;
+        } else {
+#pragma unroll
+            for (int k = 0; k < kCompItems; ++k) if (i0 + k < n && binaries[i0 + k]) keep |= 1u << k;
+        }
+#pragma unroll
+        for (int k = 0; k < kCompItems; ++k) v[k] = i0 + k;
+    }
+    long long pos = tile_lookback_position(__popc(keep), status, total, base);
+#pragma unroll
+    for (int k = 0; k < kCompItems; ++k)
+        if (keep & (1u << k)) out[pos++] = v[k];
 }
 
 // ---- mark_invisible_cells (occ_grid.py:263-332) ------------------------------------------------
@@ -343,6 +392,31 @@ NFB_API int nfb_compact_samples(const uint8_t* mask, const int64_t* ray_indices,
                                                     static_cast<unsigned long long*>(workspace));
     count_launch();
     NFB_CHECK_LAUNCH("compact_samples");
+    return NFB_OK;
+}
+
+NFB_API int nfb_occ_select_cells(const float* occs, const int64_t* candidates, const uint8_t* binaries,
+                                 int64_t n, const int64_t* base, int64_t* out, int64_t* total,
+                                 void* workspace, size_t workspace_bytes, nfb_stream_t stream) {
+    using namespace nfb;
+    NFB_CHECK_ARG(n >= 0, "negative size");
+    NFB_CHECK_ARG(total, "null pointer");
+    NFB_CHECK_ARG((candidates != nullptr) != (binaries != nullptr), "give either candidates (+ occs) or binaries");
+    NFB_CHECK_ARG(!candidates || occs, "candidates need occs");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (n == 0) { cudaMemsetAsync(total, 0, sizeof(int64_t), s); return NFB_OK; }
+    NFB_CHECK_ARG(out, "null pointer");
+    const size_t need = nfb_compact_workspace_bytes(n);
+    NFB_CHECK_ARG(workspace && workspace_bytes >= need, "workspace too small");
+    cudaMemsetAsync(workspace, 0, need, s);
+    const unsigned nt = (unsigned)ceil_div<long long>(n, kCompTile);
+    auto* st = static_cast<unsigned long long*>(workspace);
+    auto* b = reinterpret_cast<const long long*>(base);
+    auto* t = reinterpret_cast<long long*>(total);
+    if (candidates) select_cells_kernel<true><<<nt, kThreads, 0, s>>>(occs, candidates, nullptr, n, b, out, t, st);
+    else select_cells_kernel<false><<<nt, kThreads, 0, s>>>(nullptr, nullptr, binaries, n, b, out, t, st);
+    count_launch();
+    NFB_CHECK_LAUNCH("occ_select_cells");
     return NFB_OK;
 }
 

@@ -291,7 +291,7 @@ class OccGridEstimator(AbstractEstimator):
         # one launch over cells x cameras (the reference: ~12 kernels + 2 matmuls per 32^3 chunk)
         cams = torch.cat([w2c_R.reshape(n_cams, 9), w2c_T.reshape(n_cams, 3),
                           K.expand(n_cams, 3, 3).reshape(n_cams, 9)], dim=-1).float().contiguous()
-        _occ_ops.mark_invisible_cells(self.occs, cams.to(self.device), self.resolution, self.levels,
+        _occ_ops.mark_invisible_cells(self.occs, cams.to(self.device), list(self.binaries.shape[1:]), self.levels,
                                       self.aabbs, width, height, near_plane)
         self._occ_mean_cache = None
 
@@ -310,6 +310,18 @@ class OccGridEstimator(AbstractEstimator):
         occs = self.occs.view(self.levels, self.cells_per_lvl)
         for lvl in range(self.levels):
             uniform = torch.randint(self.cells_per_lvl, (n,), device=self.device, generator=generator)
+            if uniform.is_cuda:
+                # both selections in two launches and one read-back, the occupied cells written
+                # straight behind the uniform ones
+                cells, k1, k2 = _occ_ops.select_cells(occs[lvl], uniform, self.binaries[lvl])
+                if n < k2:
+                    pick = torch.randint(k2, (n,), device=self.device, generator=generator)
+                    out.append(torch.cat([cells[:k1], cells[k1:k1 + k2][pick]], dim=0))
+                else:
+                    out.append(cells[:k1 + k2])
+                continue
+            # (host tensors: the gloo tests of the sharded update run this method on the CPU with
+            # stand-ins for the device calls)
             uniform = uniform[occs[lvl][uniform] >= 0.0]
             occupied = torch.nonzero(self.binaries[lvl].flatten())[:, 0]
             if n < len(occupied):
@@ -345,7 +357,8 @@ class OccGridEstimator(AbstractEstimator):
             cell_ids = lvl * self.cells_per_lvl + indices
             # every rank decays the full sample; only the field evaluations are sharded
             lo, hi = _occ_ops.shard_range(indices.shape[0], world, rank)
-            x = _occ_ops.cell_points(indices[lo:hi], u[lo:hi], self.resolution, self.aabbs[lvl])
+            # (the resolution as host ints: the shape of `binaries`, no device read)
+            x = _occ_ops.cell_points(indices[lo:hi], u[lo:hi], list(self.binaries.shape[1:]), self.aabbs[lvl])
             occ = occ_eval_fn(x).squeeze(-1) if hi > lo else x.new_empty((0,))
             _occ_ops.ema_update(self.occs, cell_ids, occ, lo, hi, ema_decay)
         if world > 1:

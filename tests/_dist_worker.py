@@ -28,6 +28,7 @@ def _cpu_standins():
     """CPU versions of the three device calls `_update` makes (nfb_occ_cell_points,
     nfb_occ_ema_update, nfb_occ_binarize), same semantics."""
     def cell_points(cells, u, resolution, aabb):
+        resolution = torch.as_tensor(resolution)  # host ints from `_update`, or a tensor
         res = resolution.to(torch.long)
         ijk = torch.stack([cells // (res[1] * res[2]), (cells // res[2]) % res[1], cells % res[2]], -1)
         g = (ijk.float() + u) / resolution.float()

@@ -431,6 +431,50 @@ def test_update_steady_state_vs_oracle(device):
         assert (est.occs[::11] == -1.0).all()
 
 
+@pytest.mark.parametrize("n_cells,n,frac_occ", [(32**3, 32**3 // 4, 0.05), (20 * 21 * 23, 777, 0.6),
+                                                (5000, 0, 0.3), (4099, 9000, 0.0), (2048, 2048, 1.0)])
+def test_select_cells_vs_torch(device, n_cells, n, frac_occ):
+    """nfb_occ_select_cells (two launches, one read-back) against the reference's formulation
+    (occ_grid.py:344-365): uniform[occs[uniform] >= 0] followed by nonzero(binaries), in order;
+    sizes that are not multiples of the tile, no draws, no occupied cells, everything occupied."""
+    from nerfacc_b200 import _occ_ops
+
+    g = torch.Generator(device=device).manual_seed(n_cells + n)
+    occs = torch.rand(n_cells, device=device, generator=g)
+    occs[torch.rand(n_cells, device=device, generator=g) < 0.2] = -1.0
+    bins = torch.rand(n_cells, device=device, generator=g) < frac_occ
+    uniform = torch.randint(n_cells, (n,), device=device, generator=g)
+    cells, k1, k2 = _occ_ops.select_cells(occs, uniform, bins)
+    want_u = uniform[occs[uniform] >= 0.0]
+    want_o = torch.nonzero(bins)[:, 0]
+    assert (k1, k2) == (want_u.numel(), want_o.numel())
+    assert torch.equal(cells[:k1], want_u) and torch.equal(cells[k1:k1 + k2], want_o)
+
+
+def test_sample_cells_more_occupied_than_draws(device):
+    """The branch of _sample_uniform_and_occupied_cells that subsamples the occupied cells
+    (n < len(occupied), occ_grid.py:358-362): same RNG stream, same cells as the torch formulation."""
+    import nerfacc_b200 as nf
+
+    res, levels = 16, 2
+    est = nf.OccGridEstimator([-1.0] * 3 + [1.0] * 3, resolution=res, levels=levels).to(device)
+    g = torch.Generator(device=device).manual_seed(5)
+    est.binaries = torch.rand((levels, res, res, res), device=device, generator=g) < 0.7
+    est.occs = torch.where(torch.rand(levels * res**3, device=device, generator=g) < 0.3, -1.0, 0.5)
+    n = res**3 // 4
+    torch.manual_seed(11)
+    got = est._sample_uniform_and_occupied_cells(n)
+    torch.manual_seed(11)
+    occs = est.occs.view(levels, -1)
+    for lvl in range(levels):
+        uniform = torch.randint(res**3, (n,), device=device)
+        uniform = uniform[occs[lvl][uniform] >= 0.0]
+        occupied = torch.nonzero(est.binaries[lvl].flatten())[:, 0]
+        assert n < len(occupied)
+        occupied = occupied[torch.randint(len(occupied), (n,), device=device)]
+        assert torch.equal(got[lvl], torch.cat([uniform, occupied]))
+
+
 def test_update_vs_reference_package(device):
     """OccGridEstimator._update, warm-up and steady state, against the reference's own estimator
     (baseline/_ref, pure torch on the same CUDA RNG stream): identical `occs` and `binaries`."""
