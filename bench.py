@@ -485,6 +485,7 @@ def run_ours(args) -> None:
             rgb_c.append(rgbs.detach()[s_cuts[i]:s_cuts[i + 1]].clone().requires_grad_(True))
 
     buf_ready = [None, None]
+    held = {}
 
     def copy_in(q):
         if buf_free[q] is not None:
@@ -532,15 +533,25 @@ def run_ours(args) -> None:
                 # backward carries all three gradients, as the device-timed step's does)
                 # loss = 1/2 sum (c - c*)^2 + 1e-3 (sum opacity + sum depth): its three gradients are the
                 # residual itself and two constant tensors, its three terms go out as three floats
+                # Only the residual (the backward's input) is on the main stream; the three reductions that
+                # only feed the read-back run on the output stream beside the backward.  Their inputs stay
+                # referenced until the main stream has waited for that stream's event two steps on (no
+                # record_stream: its deferred frees make the pool grow in the middle of a pass).
                 with torch.no_grad():
                     g_loss_c = colors - tgt_buf[p][i]
-                    terms = torch.stack([torch.dot(g_loss_c.view(-1), g_loss_c.view(-1)), opac.sum(), depth.sum()])
                 done = torch.cuda.Event()
                 done.record(main)
-                with torch.cuda.stream(s_out):
+                with torch.cuda.stream(s_out), torch.no_grad():
                     s_out.wait_event(done)
+                    terms = torch.stack([torch.dot(g_loss_c.view(-1), g_loss_c.view(-1)), opac.sum(), depth.sum()])
                     host_loss[3 * i:3 * i + 3].copy_(terms, non_blocking=True)
-                terms.record_stream(s_out)
+                    out_done = torch.cuda.Event()
+                    out_done.record(s_out)
+                old = held.get((p, i))
+                held[(p, i)] = (g_loss_c, opac.detach(), depth.detach(), terms, out_done)
+                if old is not None:
+                    main.wait_event(old[4])
+                del old
                 torch.autograd.backward([colors, opac, depth], [g_loss_c, g_mean[i], g_mean[i]])
                 continue
             done = torch.cuda.Event()  # the step's results exist after the forward: their D2H copy
@@ -620,6 +631,29 @@ def run_ours(args) -> None:
     for _ in range(2):
         step_e2e()
     ms_e2e_local = timed(step_e2e, args.steps, FIRST, join=(s_out, s_in))
+    e2e_result = None
+    if loss_out:
+        # what the last step read back, against the same three terms recomputed from that step's tensors
+        g_l, op_l, dp_l = held[((e2e_state["k"] - 1) & 1, n_chunks - 1)][:3]
+        want = [float(torch.dot(g_l.view(-1), g_l.view(-1))), float(op_l.sum()), float(dp_l.sum())]
+        got = [float(v) for v in host_loss[3 * (n_chunks - 1):3 * n_chunks]]
+        assert all(abs(a - b) <= 1e-4 * max(1.0, abs(b)) for a, b in zip(got, want)), (got, want)
+        e2e_result = {"loss_terms_read_back": got}
+    if os.environ.get("NFB_BENCH_TRACE"):  # diagnostic: the device timeline of three e2e steps
+        from torch.profiler import ProfilerActivity, profile
+        state["step"] = FIRST + 1
+        with profile(activities=[ProfilerActivity.CUDA]) as tr:
+            for _ in range(4):
+                step_e2e()
+            torch.cuda.synchronize()
+        evs = sorted((e for e in tr.events() if e.device_type == torch.autograd.DeviceType.CUDA),
+                     key=lambda e: e.time_range.start)
+        t0, last = evs[0].time_range.start, None
+        for e in evs:
+            gap = 0.0 if last is None else (e.time_range.start - last) / 1e3
+            print("trace %8.3f %7.3f %7.3f %s" % ((e.time_range.start - t0) / 1e3, (e.time_range.end - e.time_range.start) / 1e3,
+                                                gap, e.name[:80]), file=sys.stderr)
+            last = max(last or 0, e.time_range.end)
     ms_e2e = aggregate_over_ranks(ms_e2e_local, 0, dist, dev)[0]
     # fourth pass, reported beside `value` (not in it): consecutive batches overlapped on two streams —
     # step k renders the batch that step k-1 marched while the next batch is marched on a side stream
@@ -820,7 +854,7 @@ def run_ours(args) -> None:
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": (3 if loss_out else 2) * n_rays * 12 * world,
                 "d2h_bytes_per_step": (12 * n_chunks if loss_out else n_rays * 20) * world,
-                "output": args.e2e_output,
+                "output": args.e2e_output, "result": e2e_result,
                 "pipeline": f"{n_chunks} ray blocks/step through OccGridEstimator.sampling + rendering + backward; "
                             + ("pinned-host rays and target pixels in, the photometric loss out to pinned host, every step "
                                "(a training step's traffic; --e2e-output images sends colours/opacity/depth out instead: "
