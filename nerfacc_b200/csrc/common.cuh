@@ -111,6 +111,34 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
     return v;
 }
 
+// Decoupled look-back by one warp (all 32 lanes call it, tile > 0, the tile's own status word
+// already published as "aggregate"): the sum of everything before `tile`.  A status word is
+// value << 2 | state (0 not there yet, 1 the tile's aggregate, 2 its inclusive prefix); the array
+// starts zeroed.  The warp reads 32 predecessors per round, so a launch whose tiles are all resident
+// at once (a scan over rays: a few hundred tiles) resolves in a handful of dependent loads instead
+// of one per predecessor.
+__device__ __forceinline__ long long warp_lookback_u64(const unsigned long long* status, long long tile) {
+    const int lane = threadIdx.x & 31;
+    long long X = 0;
+    long long k = tile - 1;  // lane 0 looks at the nearest predecessor
+    while (true) {
+        const long long idx = k - lane;
+        // (before tile 0 there is nothing: an inclusive prefix of zero)
+        const unsigned long long s = idx >= 0 ? ld_relaxed_u64(status + idx) : 2ull;
+        const unsigned incl = __ballot_sync(0xffffffffu, (s & 3ull) == 2ull);
+        const unsigned ready = __ballot_sync(0xffffffffu, (s & 3ull) != 0ull);
+        // the lanes up to and including the first inclusive prefix must all be there
+        const unsigned need = incl ? (0xffffffffu >> (32 - __ffs(incl))) : 0xffffffffu;
+        if ((ready & need) != need) { __nanosleep(20); continue; }
+        long long v = ((need >> lane) & 1u) ? (long long)(s >> 2) : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        X += v;
+        if (incl) return X;
+        k -= 32;
+    }
+}
+
 // packed_info is int64 [n_rays, 2] = (start, count) interleaved: one 16-byte load.
 struct RayChunk { long long start, cnt; };
 __device__ __forceinline__ RayChunk load_chunk(const int64_t* packed_info, long long r) {

@@ -126,24 +126,19 @@ __device__ __forceinline__ long long tile_lookback_position(int cnt, unsigned lo
     int before = 0, agg = 0;
 #pragma unroll
     for (int j = 0; j < kWarps; ++j) { if (j == w) before = agg; agg += s_warp[j]; }
-    if (threadIdx.x == 0) {
+    if (w == 0) {  // the first warp looks back, 32 predecessors per round
         long long X = 0;
         if (tile == 0) {
-            st_relaxed_u64(status, ((unsigned long long)agg << 2) | 2ull);
+            if (lane == 0) st_relaxed_u64(status, ((unsigned long long)agg << 2) | 2ull);
         } else {
-            st_relaxed_u64(status + tile, ((unsigned long long)agg << 2) | 1ull);
-            long long k = tile - 1;
-            while (true) {
-                const unsigned long long s = ld_relaxed_u64(status + k);
-                if ((s & 3ull) == 0ull) { __nanosleep(40); continue; }
-                X += (long long)(s >> 2);
-                if ((s & 3ull) == 2ull) break;
-                --k;
-            }
-            st_relaxed_u64(status + tile, ((unsigned long long)(X + agg) << 2) | 2ull);
+            if (lane == 0) st_relaxed_u64(status + tile, ((unsigned long long)agg << 2) | 1ull);
+            X = warp_lookback_u64(status, tile);
+            if (lane == 0) st_relaxed_u64(status + tile, ((unsigned long long)(X + agg) << 2) | 2ull);
         }
-        s_carry = X + (base ? *base : 0);  // (one read per tile: `base` may live in pinned host memory)
-        if (tile == (long long)gridDim.x - 1 && total) *total = X + agg;
+        if (lane == 0) {
+            s_carry = X + (base ? *base : 0);
+            if (tile == (long long)gridDim.x - 1 && total) *total = X + agg;
+        }
     }
     __syncthreads();
     return s_carry + before + (t - cnt);
