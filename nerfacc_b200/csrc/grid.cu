@@ -269,9 +269,11 @@ template <bool DIRECT> constexpr int march_threads() { return DIRECT ? kConeThre
 // One thread per ray: the ray's first segment and its DDA state at the occupied box (prepare_ray), 64 bytes
 // per ray, for a march_kernel launched right behind it with `prepped` set.
 __global__ void __launch_bounds__(256)
-march_prepare_kernel(const RayArgs A, const GridSpec G, bool clip, uint4* __restrict__ out) {
+march_prepare_kernel(const RayArgs A, const GridSpec Gp, bool clip, uint4* __restrict__ out) {
     const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= A.n_rays) return;
+    GridSpec G = Gp;
+    G.n_grids = 1;  // (only launched for one level: the event arrays then unroll into registers)
     uint32_t w[16];
     prepare_ray(A.rays_o, A.rays_d, A.near_arr, A.near_s, A.far_arr, A.far_s, A.t_sorted, A.t_indices, A.hits, G, r, clip, w);
     out[4 * r] = make_uint4(w[0], w[1], w[2], w[3]);

@@ -189,9 +189,13 @@ NFB_HD float advance(float t, const float dt, const float target, const int cap,
             const float u = bits_f((uint32_t)(E - 23) << 23);   // ulp of t's binade
             const float top = bits_f((uint32_t)(E + 1) << 23);  // 2^(e+1)
             const float r = rn_sub(dt, q);                      // exact, |r| <= u/2
-            if (t1 <= top && rn_mul(fabsf(r), 2.0f) != u) {
+            const int ti = (int)((tb & 0x7fffffu) | 0x800000u);
+            // A tie (dt exactly halfway between two points of the binade's grid) rounds to the even
+            // mantissa: from an even mantissa every step adds the same even q (the stretch below is exact
+            // then too); from an odd one, a single literal step lands on an even one.  One (ray, axis) in
+            // 64 has such a delta at t in [2, 4), and stepping it literally held its whole warp back.
+            if (t1 <= top && (rn_mul(fabsf(r), 2.0f) != u || (ti & 1) == 0)) {
                 // linear regime: t_k = t + k*q for every k with t + k*q <= top
-                const int ti = (int)((tb & 0x7fffffu) | 0x800000u);
                 const int qi = f2i_rn(rn_mul(q, bits_f((uint32_t)(277 - E) << 23)));
                 int kmax = (0x1000000 - ti) / qi;  // >= 1 because t1 <= top
                 if (kmax > cap - steps) kmax = cap - steps;

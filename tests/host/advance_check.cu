@@ -49,6 +49,14 @@ int main(int argc, char** argv) {
         else if (tp == 1) t = (float)(-urand() * 3.0 * dt);
         else if (tp == 2) { t = (float)std::ldexp(1.0, (int)(rnd() % 12) - 6); t = std::nextafterf(t, 0.0f); for (int i = (int)(rnd() % 4); i > 0; --i) t = std::nextafterf(t, 0.0f); }
         else t = (float)(std::exp(urand() * 10.0 - 6.0));
+        if (rnd() % 8 == 0 && t > 0.0f) {
+            // dt exactly halfway between two points of t's grid: every step in t's binade is a
+            // rounding tie (to the even mantissa)
+            int e; std::frexp(t, &e);
+            const float u = (float)std::ldexp(1.0, e - 24);  // ulp of t's binade
+            const double n = (double)(rnd() % (1u << (4 + rnd() % 18)));
+            dt = (float)((n + 0.5) * u);
+        }
         const double span = (rnd() % 4 == 0) ? urand() * 3000.0 : urand() * 40.0;
         float target = (float)(t + span * dt + (urand() - 0.5) * dt);
         if (rnd() % 64 == 0) target = t;  // already there
