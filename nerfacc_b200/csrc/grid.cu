@@ -22,7 +22,8 @@
 namespace nfb {
 
 int launch_ray_scan(int64_t* packed_info, long long n_rays, long long* total_out, void* status,
-                    cudaStream_t s, const unsigned long long* only_if = nullptr);
+                    cudaStream_t s, const unsigned long long* only_if = nullptr,
+                    const unsigned long long* also_src = nullptr, long long* also_dst = nullptr);
 size_t ray_scan_status_bytes(long long n_rays);
 
 struct RayArgs {
@@ -920,9 +921,11 @@ static unsigned long long* counters_of(void* scratch, size_t scratch_bytes, long
 }
 
 static int scan_both(int64_t* sample_info, int64_t* interval_info, long long n_rays, int64_t* totals,
-                     void* scratch, cudaStream_t s) {
+                     void* scratch, cudaStream_t s, const unsigned long long* also_src = nullptr,
+                     long long* also_dst = nullptr) {
     const size_t one = (ray_scan_status_bytes(n_rays) + 63) & ~(size_t)63;
-    int rc = launch_ray_scan(sample_info, n_rays, reinterpret_cast<long long*>(totals), scratch, s);
+    int rc = launch_ray_scan(sample_info, n_rays, reinterpret_cast<long long*>(totals), scratch, s, nullptr,
+                             also_src, also_dst);
     if (rc != NFB_OK) return rc;
     if (interval_info != nullptr)
         rc = launch_ray_scan(interval_info, n_rays, totals ? reinterpret_cast<long long*>(totals) + 1 : nullptr,
@@ -1064,11 +1067,10 @@ NFB_API int nfb_traverse_count(const nfb_rays_t* rays, const nfb_grid_t* grid,
         rc = launch_march(A, G, to_opts(march), P, counters, s);
     }
     if (rc != NFB_OK) return rc;
-    rc = scan_both(sample_info, interval_info, rays->n_rays, totals, scratch, s);
-    if (rc != NFB_OK) return rc;
-    if (totals != nullptr)
-        cudaMemcpyAsync(totals + 2, counters + 1, sizeof(int64_t), cudaMemcpyDefault, s);
-    return NFB_OK;
+    // totals[2] (rays beyond the run buffer) goes out with the scan's own total, no copy on the stream
+    return scan_both(sample_info, interval_info, rays->n_rays, totals, scratch, s,
+                     totals != nullptr ? counters + 1 : nullptr,
+                     totals != nullptr ? reinterpret_cast<long long*>(totals) + 2 : nullptr);
 }
 
 // the expansion of the run buffer: traverse_expand_kernel + the pooled runs

@@ -177,14 +177,23 @@ sample_positions_kernel(const float* __restrict__ rays_o, const float* __restric
     }
 }
 
+__global__ void zero_words_kernel(unsigned long long* __restrict__ p, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = 0ull;
+}
+
 // Exclusive scan over rays, in place on packed_info: reads counts at [2r+1], writes starts
 // at [2r]; the grand total goes to *total_out.  2048 rays per CTA, int64 look-back
 // (status word = value << 2 | state; the status array must be zeroed before launch).
 constexpr int kRayTile = 2048;
 __global__ void __launch_bounds__(kThreads)
 ray_scan_kernel(int64_t* __restrict__ packed_info, long long n_rays, long long* __restrict__ total_out,
-                unsigned long long* status, const unsigned long long* __restrict__ only_if) {
+                unsigned long long* status, const unsigned long long* __restrict__ only_if,
+                const unsigned long long* __restrict__ also_src, long long* __restrict__ also_dst) {
     if (only_if != nullptr && *only_if == 0ull) return;
+    // a second word for the host, written beside the total (the caller's read-back then needs no copy
+    // on the stream: with a large H2D transfer in flight an 8-byte cudaMemcpyAsync took 25 us)
+    if (also_dst != nullptr && blockIdx.x == gridDim.x - 1 && threadIdx.x == 32) *also_dst = (long long)*also_src;
     __shared__ long long s_warp[kWarps];
     __shared__ long long s_carry;
     const long long tile = blockIdx.x;
@@ -238,15 +247,15 @@ size_t ray_scan_status_bytes(long long n_rays) {
 
 // Launch the in-place per-ray scan; `status` must hold ray_scan_status_bytes(n_rays).
 int launch_ray_scan(int64_t* packed_info, long long n_rays, long long* total_out,
-                    void* status, cudaStream_t s, const unsigned long long* only_if) {
+                    void* status, cudaStream_t s, const unsigned long long* only_if,
+                    const unsigned long long* also_src, long long* also_dst) {
     const long long nt = ceil_div<long long>(n_rays, kRayTile);
-    if (cudaMemsetAsync(status, 0, (size_t)nt * sizeof(unsigned long long), s) != cudaSuccess) {
-        set_error("ray scan: memset failed");
-        return NFB_ERR_CUDA;
-    }
+    // (a kernel, not cudaMemsetAsync: behind a large H2D transfer the memset of these few KB took 12 us)
+    zero_words_kernel<<<(unsigned)ceil_div<long long>(nt, 256), 256, 0, s>>>(static_cast<unsigned long long*>(status), nt);
     ray_scan_kernel<<<(unsigned)nt, kThreads, 0, s>>>(packed_info, n_rays, total_out,
-                                                      static_cast<unsigned long long*>(status), only_if);
-    count_launch();
+                                                      static_cast<unsigned long long*>(status), only_if,
+                                                      also_src, also_dst);
+    count_launch(2);
     NFB_CHECK_LAUNCH("ray_scan");
     return NFB_OK;
 }
@@ -287,7 +296,7 @@ NFB_API int nfb_pack_info(const int64_t* ray_indices, int64_t n, int64_t n_rays,
     pack_hist_kernel<<<(unsigned)nb, kThreads, 0, s>>>(ray_indices, n, n_rays, packed_info, aligned16(ray_indices), flag);
     count_launch();
     NFB_CHECK_LAUNCH("pack_hist");
-    return launch_ray_scan(packed_info, n_rays, nullptr, workspace, s, flag);
+    return launch_ray_scan(packed_info, n_rays, nullptr, workspace, s, flag, nullptr, nullptr);
 }
 
 NFB_API int nfb_sample_positions(const float* rays_o, const float* rays_d, const int64_t* ray_indices,
