@@ -541,6 +541,9 @@ def run_ours(args) -> None:
                     g_loss_c = colors - tgt_buf[p][i]
                 done = torch.cuda.Event()
                 done.record(main)
+                # (the backward is issued first: the host is the slower side between the forward and the
+                # backward, and the ten small launches of the reductions kept the main stream waiting)
+                torch.autograd.backward([colors, opac, depth], [g_loss_c, g_mean[i], g_mean[i]])
                 with torch.cuda.stream(s_out), torch.no_grad():
                     s_out.wait_event(done)
                     terms = torch.stack([torch.dot(g_loss_c.view(-1), g_loss_c.view(-1)), opac.sum(), depth.sum()])
@@ -552,7 +555,6 @@ def run_ours(args) -> None:
                 if old is not None:
                     main.wait_event(old[4])
                 del old
-                torch.autograd.backward([colors, opac, depth], [g_loss_c, g_mean[i], g_mean[i]])
                 continue
             done = torch.cuda.Event()  # the step's results exist after the forward: their D2H copy
             done.record(main)          # overlaps the backward
