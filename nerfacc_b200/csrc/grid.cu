@@ -810,7 +810,8 @@ static int launch_march(const RayArgs& A, const GridSpec& G, const MarchOpts& op
     {
         const long long n_work = A.ray_list ? A.n_work : A.n_rays;
         const long long warps = b * (threads / 32);
-        long long per = ceil_div<long long>(n_work, warps * 2);
+        // (the cone loop ties a lane to a ray: one round that fills the lanes beats two half-empty ones)
+        long long per = ceil_div<long long>(n_work, direct ? warps : warps * 2);
         o2.batch = (int)(per < 8 ? 8 : (per > 32 ? 32 : per));
     }
     const uint4* prepped = nullptr;
