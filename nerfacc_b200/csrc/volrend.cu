@@ -152,6 +152,34 @@ __device__ __forceinline__ long long lookback_count(unsigned long long* st, int 
     return acc;
 }
 
+// The same by one warp, 32 predecessors per round (all lanes call it and get the result).
+__device__ __forceinline__ long long warp_lookback_count(unsigned long long* st, int slot, long long tile,
+                                                         uint32_t epoch) {
+    const int lane = threadIdx.x & 31;
+    long long X = 0;
+    long long k = tile - 1;
+    while (true) {
+        const long long idx = k - lane;
+        uint32_t state = 2u, val = 0u;  // before tile 0: an inclusive prefix of zero
+        if (idx >= 0) {
+            const unsigned long long wd = ld_relaxed_u64(st + idx * kStatusPerTile + slot);
+            const uint32_t meta = (uint32_t)(wd >> 32);
+            state = (meta >> 2) == epoch ? (meta & 3u) : 0u;
+            val = (uint32_t)wd;
+        }
+        const unsigned incl = __ballot_sync(kFull, state == 2u);
+        const unsigned ready = __ballot_sync(kFull, state != 0u);
+        const unsigned need = incl ? (0xffffffffu >> (32 - __ffs(incl))) : 0xffffffffu;
+        if ((ready & need) != need) { __nanosleep(20); continue; }
+        long long v = ((need >> lane) & 1u) ? (long long)val : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(kFull, v, d);
+        X += v;
+        if (incl) return X;
+        k -= 32;
+    }
+}
+
 template <bool DENSITY>
 __global__ void __launch_bounds__(kThreads, 5) vis_compact_kernel(const VisCompactArgs q) {
     const WeightFwdArgs& p = q.w;
@@ -259,19 +287,21 @@ __global__ void __launch_bounds__(kThreads, 5) vis_compact_kernel(const VisCompa
 #pragma unroll
         for (int k = 0; k < kVec; ++k) { s_vbase[w][k] = run; run += vtot[k]; }
     }
-    if (threadIdx.x == 0) {
+    if (w == 0) {
         const long long tile = blockIdx.x;
         unsigned long long* mine = p.status + tile * kStatusPerTile + 1;
         long long X = 0;
         if (tile == 0) {
-            st_relaxed_u64(mine, pack_count((uint32_t)agg, p.epoch, 2u));
+            if (lane == 0) st_relaxed_u64(mine, pack_count((uint32_t)agg, p.epoch, 2u));
         } else {
-            st_relaxed_u64(mine, pack_count((uint32_t)agg, p.epoch, 1u));
-            X = lookback_count(p.status, 1, tile, p.epoch);
-            st_relaxed_u64(mine, pack_count((uint32_t)(X + agg), p.epoch, 2u));
+            if (lane == 0) st_relaxed_u64(mine, pack_count((uint32_t)agg, p.epoch, 1u));
+            X = warp_lookback_count(p.status, 1, tile, p.epoch);
+            if (lane == 0) st_relaxed_u64(mine, pack_count((uint32_t)(X + agg), p.epoch, 2u));
         }
-        s_tile_base = X;
-        if (tile == (long long)gridDim.x - 1 && q.total) *q.total = X + agg;
+        if (lane == 0) {
+            s_tile_base = X;
+            if (tile == (long long)gridDim.x - 1 && q.total) *q.total = X + agg;
+        }
     }
     __syncthreads();
     const long long tile_base = s_tile_base;
