@@ -639,8 +639,10 @@ def run_ours(args) -> None:
         g_l, op_l, dp_l = held[((e2e_state["k"] - 1) & 1, n_chunks - 1)][:3]
         want = [float(torch.dot(g_l.view(-1), g_l.view(-1))), float(op_l.sum()), float(dp_l.sum())]
         got = [float(v) for v in host_loss[3 * (n_chunks - 1):3 * n_chunks]]
-        assert all(abs(a - b) <= 1e-4 * max(1.0, abs(b)) for a, b in zip(got, want)), (got, want)
-        e2e_result = {"loss_terms_read_back": got}
+        same = all(abs(a - b) <= 1e-4 * max(1.0, abs(b)) for a, b in zip(got, want))
+        e2e_result = {"loss_terms_read_back": got, "check": "equal to the device's own" if same else f"MISMATCH: device {want}"}
+        if not same:
+            print(f"bench.py: e2e read-back {got} differs from the device's loss terms {want}", file=sys.stderr)
     if os.environ.get("NFB_BENCH_TRACE"):  # diagnostic: the device timeline of three e2e steps
         from torch.profiler import ProfilerActivity, profile
         state["step"] = FIRST + 1
