@@ -136,23 +136,8 @@ __device__ __forceinline__ unsigned long long pack_count(uint32_t v, uint32_t ep
     return ((unsigned long long)((epoch << 2) | state) << 32) | (unsigned long long)v;
 }
 
-// Survivors before `tile`: walk back to the nearest tile that has published its inclusive prefix.
-__device__ __forceinline__ long long lookback_count(unsigned long long* st, int slot, long long tile,
-                                                    uint32_t epoch) {
-    long long acc = 0;
-    long long k = tile - 1;
-    while (true) {
-        const unsigned long long w = ld_relaxed_u64(st + k * kStatusPerTile + slot);
-        const uint32_t meta = (uint32_t)(w >> 32);
-        if ((meta >> 2) != epoch || (meta & 3u) == 0u) { __nanosleep(40); continue; }
-        acc += (long long)(uint32_t)w;
-        if ((meta & 3u) == 2u) break;
-        --k;  // tile 0 always publishes state 2
-    }
-    return acc;
-}
-
-// The same by one warp, 32 predecessors per round (all lanes call it and get the result).
+// Survivors before `tile`: look back to the nearest tile that has published its inclusive prefix
+// (tile 0 always has), one warp reading 32 predecessors per round; all lanes call it and get the result.
 __device__ __forceinline__ long long warp_lookback_count(unsigned long long* st, int slot, long long tile,
                                                          uint32_t epoch) {
     const int lane = threadIdx.x & 31;
